@@ -1,0 +1,81 @@
+"""Seeded parity cases (shapes x poses x options) shared by the oracle validation, the golden-vector
+generator and the GPU parity tests.  Pure numpy."""
+import numpy as np
+
+from robustmvd_b200 import synthetic as syn
+
+
+def _ps(name, h, w, C, transforms, S=16, seed=0, hs=None, ws=None, n=1, K_key=None, K_src=None,
+        kwargs=None, **opts):
+    hs = h if hs is None else hs
+    ws = w if ws is None else ws
+    V = len(transforms)
+    c = dict(
+        name=name,
+        feat_key=syn.features((n, C, h, w), seed),
+        intrinsics_key=syn.relative_intrinsics(h, w, n=n) if K_key is None else K_key,
+        feat_sources=[syn.features((n, C, hs, ws), seed + 1 + v) for v in range(V)],
+        transforms=transforms,
+        intrinsics_sources=K_src,
+        kwargs=kwargs if kwargs is not None else dict(num_sampling_points=S, min_depth=0.4, max_depth=1000.0),
+    )
+    c.update(opts)
+    return c
+
+
+def planesweep_cases(include_large=True):
+    T = syn.make_transform
+    cases = []
+    # degenerate poses
+    cases.append(_ps("identity_6x10", 6, 10, 8, [T()], seed=1))
+    cases.append(_ps("stereo_x_12x20", 12, 20, 8, [T(t=(-0.54, 0, 0)), T(t=(0.54, 0, 0))], seed=2))
+    cases.append(_ps("forward_12x20", 12, 20, 8, [T(t=(0, 0, 0.5)), T(t=(0, 0, -0.5))], seed=3))
+    cases.append(_ps("rot90_fw_12x20", 12, 20, 8, [T(syn.rot_y(90), (0.3, 0, 0.2))], seed=4))
+    cases.append(_ps("behind_12x20", 12, 20, 8, [T(syn.rot_y(180), (0, 0, 1.0)), T(t=(0, 0, -3.0))], seed=5))
+    cases.append(_ps("roll_pitch_12x20", 12, 20, 8,
+                     [T(syn.rot_z(12) @ syn.rot_x(6), (0.2, -0.1, 0.03))], seed=6))
+    # non-square intrinsics, off-centre principal point, source resolution != key resolution, own source K
+    Kk = syn.relative_intrinsics(12, 20, fx_rel=0.7, fy_rel=1.1, cx_rel=0.45, cy_rel=0.55)
+    Ks = syn.relative_intrinsics(9, 14, fx_rel=0.62, fy_rel=1.0, cx_rel=0.52, cy_rel=0.48)
+    cases.append(_ps("src_res_differs", 12, 20, 8, [T(syn.rot_y(3), (0.3, 0.02, 0.01)), T(syn.rot_y(-4), (-0.4, 0, 0.05))],
+                     hs=9, ws=14, K_key=Kk, K_src=[Ks, Ks], seed=7))
+    # batch of 2 with per-sample depth ranges (compute_sampling_invdepths with arrays)
+    cases.append(_ps("batch2_ranges", 12, 20, 8,
+                     [T(syn.rot_y(2), (0.3, 0, 0), n=2), T(syn.rot_y(-2), (-0.3, 0.05, 0.02), n=2)], n=2, seed=8,
+                     kwargs=dict(num_sampling_points=12, min_depth=np.array([0.5, 1.0], np.float32),
+                                 max_depth=np.array([50.0, 200.0], np.float32))))
+    cases.append(_ps("linear_depth", 12, 20, 8, [T(t=(0.3, 0, 0))], seed=9,
+                     kwargs=dict(num_sampling_points=10, min_depth=0.5, max_depth=20.0, sampling_type="linear_depth")))
+    # explicit inverse depths of rank 2, 3, 4
+    rng = np.random.default_rng(10)
+    for rank, shape in ((2, (1, 9)), (3, (1, 9, 12)), (4, (1, 9, 12, 20))):
+        inv = (rng.random(shape, dtype=np.float32) * np.float32(2.0) + np.float32(0.01))
+        cases.append(_ps(f"explicit_inv_rank{rank}", 12, 20, 8, [T(syn.rot_y(2), (0.3, 0, 0.02))], seed=10 + rank,
+                         kwargs=dict(sampling_invdepths=inv)))
+    # zero and negative inverse depths (zs = inf / negative: visible_in_key false)
+    inv = np.array([[0.0, -0.5, 1e-12, 0.3, 3.0]], np.float32)
+    cases.append(_ps("inv_zero_negative", 12, 20, 8, [T(t=(0.3, 0, 0.1))], seed=15, kwargs=dict(sampling_invdepths=inv)))
+    # normalisation variants
+    for nm in (False, True, "before"):
+        cases.append(_ps(f"normalize_{nm}", 12, 20, 8, [T(syn.rot_y(2), (0.3, 0, 0.02))], seed=20, normalize=nm))
+    # warp only
+    for nm in (False, "before", "after", "dim"):
+        cases.append(_ps(f"warp_only_{nm}", 12, 20, 8, [T(syn.rot_y(2), (0.3, 0, 0.02)), T(t=(-0.3, 0, 0))], seed=21,
+                         warp_only=True, normalize=nm))
+    # C not a multiple of 4, odd sizes
+    cases.append(_ps("odd_sizes", 7, 11, 5, [T(syn.rot_y(1), (0.2, 0, 0))], S=7, seed=22))
+    if include_large:
+        # KITTI-like geometry at reduced channel count, full plane count
+        cases.append(_ps("kitti_like_c32", 48, 160, 32, syn.kitti_like_views(2), S=256, seed=30))
+        cases.append(_ps("eth3d_like_c16", 96, 144, 16, syn.kitti_like_views(3), S=64, seed=31))
+    return cases
+
+
+def mvs_cases(include_large=True):
+    cases = []
+    cases.append(dict(name="mvs_small", **syn.mvs_inputs(12, 16, 8, 3, 8, seed=40, fx=20.0, min_depth=0.5, max_depth=1.5)))
+    cases.append(dict(name="mvs_batch2", **syn.mvs_inputs(10, 14, 4, 4, 6, n=2, seed=41, fx=18.0)))
+    cases.append(dict(name="mvs_odd", **syn.mvs_inputs(7, 9, 5, 2, 5, seed=42, fx=10.0)))
+    if include_large:
+        cases.append(dict(name="mvs_dtu_quarter", **syn.mvs_inputs(56, 76, 32, 5, 48, seed=43, fx=90.0)))
+    return cases
