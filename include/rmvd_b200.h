@@ -1,0 +1,168 @@
+/*
+ * rmvd_b200.h -- C ABI of the B200-native plane-sweep cost-volume path.
+ *
+ * The reference (saiprasadbarke/robustmvd) has no FFI layer: its boundary for this path is the Python
+ * call signature of the blocks.  Every entry point below replaces one of those Python call sites (cited as
+ * reference file:line) and is what a reference-side binding (ctypes stub) would bind.
+ *
+ * Conventions
+ *   - all tensors float32, contiguous, NCHW unless stated; pointers are DEVICE pointers unless the name
+ *     ends in `_host` or the comment says "host array";
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*), re-entrant, and holds no
+ *     global mutable state; scratch memory is passed in by the caller (`workspace`);
+ *   - return value: 0 ok, <0 invalid argument (RMVD_E_*), >0 a cudaError_t; nothing throws across the ABI;
+ *   - there is no CPU fallback: without a CUDA device the calls return a cudaError_t.
+ */
+#ifndef RMVD_B200_H_
+#define RMVD_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RMVD_ABI_VERSION 1
+
+#define RMVD_OK 0
+#define RMVD_E_NULL (-1)      /* required pointer is NULL */
+#define RMVD_E_SHAPE (-2)     /* non-positive or inconsistent size */
+#define RMVD_E_MODE (-3)      /* unknown enum value */
+#define RMVD_E_WORKSPACE (-4) /* workspace too small */
+#define RMVD_E_RANGE (-5)     /* plane range outside [0, S] */
+
+/* normalize= of TorchCorr / WarpOnlyCorr (planesweep_corr.py:108-114, :144-150) */
+#define RMVD_NORM_NONE 0   /* False */
+#define RMVD_NORM_DIM 1    /* "dim": corr / sqrt(C) (TorchCorr); no-op for WarpOnlyCorr */
+#define RMVD_NORM_BEFORE 2 /* True or "before": L2-normalise features along C first */
+#define RMVD_NORM_AFTER 3  /* WarpOnlyCorr only ("after" or True): L2-normalise the warped features */
+
+int rmvd_abi_version(void);
+/* Human-readable name of a status returned by the calls below (static storage). */
+const char* rmvd_status_string(int status);
+
+/* ---------------------------------------------------------------------------------------------------
+ * robust_mvd family
+ * ------------------------------------------------------------------------------------------------- */
+
+/* Scratch bytes rmvd_psweep_corr_fwd needs (channels-last copies of the V source feature maps). */
+size_t rmvd_psweep_workspace_bytes(int N, int C, int V, const int* hs_host, const int* ws_host);
+
+/*
+ * PlanesweepCorrelation.forward with warp_only=False (planesweep_corr.py:396-427 -> :436-521) fused into one
+ * pass per source view: EpipolarCoeffs.from_calib (:228-300), us_from_ds/vs_from_ds (:333-349),
+ * get_plane_sweep_sampling_points (:489-512), TorchCorr.forward (:152-195) and warp's grid_sample + sampling
+ * mask (:85-102).  The all-pairs matrix of :174 is never formed: corr = mask/sqrt(C) * <key, bilinear(src)>.
+ *
+ *   feat_key        [N,C,h,w]
+ *   feat_src        host array of V device pointers, view v is [N,C,hs[v],ws[v]]
+ *   intrinsics_key  [N,3,3] RELATIVE intrinsics (fx/W ...), robust_mvd.py:117-120
+ *   intrinsics_src  host array of V device pointers to [N,3,3]
+ *   src_to_key      host array of V device pointers to [N,4,4] (p_src = T p_key)
+ *   invdepths       sampling inverse depths; element (n,s,y,x) is read at
+ *                   invdepths[n*inv_stride[0] + s*inv_stride[1] + y*inv_stride[2] + x*inv_stride[3]]
+ *                   (strides in elements, 0 for broadcast dims: covers (1|N, S), (N,S,H), (N,S,H,W), :483-485)
+ *   planes [s_begin, s_end) of the S hypotheses are computed (depth-slab partition); plane s is written at
+ *   index out_s0 + (s - s_begin) of outputs shaped [V,N,out_S,h,w].
+ *   corr, mask      float32 [V,N,out_S,h,w]; mask holds 0/1 like the reference's corr_mask (:189-193)
+ *   dbg_ix0,dbg_iy0 optional int32 [V,N,out_S,h,w]: floor of the unnormalised sampling coordinate,
+ *                   saturated to [-2, ws] / [-2, hs]; dbg_geom optional uint8: geometric mask (:499-506)
+ */
+int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* feat_src, const float* intrinsics_key,
+                         const float* const* intrinsics_src, const float* const* src_to_key,
+                         const float* invdepths, const int64_t* inv_stride_host, int N, int C, int h, int w,
+                         int V, const int* hs_host, const int* ws_host, int S, int s_begin, int s_end,
+                         int normalize_mode, float* corr, float* mask, int out_S, int out_s0,
+                         int32_t* dbg_ix0, int32_t* dbg_iy0, uint8_t* dbg_geom, void* workspace,
+                         size_t workspace_bytes, void* stream);
+
+/*
+ * PlanesweepCorrelation.forward with warp_only=True: WarpOnlyCorr.forward + warp_multi
+ * (planesweep_corr.py:107-140, :13-46).  One source view per call.
+ *   warped [N,out_S,C,h,w], mask [N,out_S,h,w] (sampling mask only: the geometric mask is ignored, :116-140)
+ */
+int rmvd_psweep_warp_fwd(const float* feat_src, const float* intrinsics_key, const float* intrinsics_src,
+                         const float* src_to_key, const float* invdepths, const int64_t* inv_stride_host,
+                         int N, int C, int h, int w, int hs, int ws, int S, int s_begin, int s_end,
+                         int normalize_mode, float* warped, float* mask, int out_S, int out_s0, void* stream);
+
+/*
+ * TorchCorr.forward on caller-supplied sampling grids (planesweep_corr.py:152-195): grids [N,S,2,h,w] in
+ * source pixels, geom_mask optional uint8 [N,S,h,w].  Outputs corr, mask float32 [N,S,h,w].
+ */
+int rmvd_corr_grid_fwd(const float* feat_key, const float* feat_src, const float* grids,
+                       const uint8_t* geom_mask, int N, int C, int h, int w, int hs, int ws, int S,
+                       int normalize_mode, float* corr, float* mask, void* workspace, size_t workspace_bytes,
+                       void* stream);
+
+/*
+ * warp() grid branch (planesweep_corr.py:49-104): x [K,C,hs,ws], grid [K,2,ho,wo] in source pixels,
+ * padding_border: 0 = "zeros", 1 = "border".  out [K,C,ho,wo], mask [K,1,ho,wo].
+ */
+int rmvd_warp_grid_fwd(const float* x, const float* grid, int K, int C, int hs, int ws, int ho, int wo,
+                       int padding_border, float* out, float* mask, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * MVSNet family
+ * ------------------------------------------------------------------------------------------------- */
+
+/*
+ * MVSNet cost-volume assembly (mvsnet.py:123-136) with homo_warp (blocks/utils.py:222-268) fused in: the
+ * warped source volumes are never written.  feats [B,Vt,C,h,w] (view 0 = key), proj [B,Vt,4,4] (view 0
+ * already inverted, mvsnet.py:85-86), depths [B,D].  Planes [d_begin,d_end) -> variance [B,C,out_D,h,w] at
+ * plane index out_d0 + (d - d_begin).
+ */
+int rmvd_mvs_variance_fwd(const float* feats, const float* proj, const float* depths, int B, int Vt, int C,
+                          int h, int w, int D, int d_begin, int d_end, float* variance, int out_D, int out_d0,
+                          void* stream);
+
+/*
+ * homo_warp (blocks/utils.py:222-268), materialising: src_feat [B,C,H,W], src_proj/ref_proj_inv [B,4,4],
+ * depths [B,D] -> warped [B,C,D,H,W]; dbg_ix0/dbg_iy0 optional int32 [B,D,H,W] (saturated to [-2,W]/[-2,H]).
+ */
+int rmvd_homo_warp_fwd(const float* src_feat, const float* src_proj, const float* ref_proj_inv,
+                       const float* depths, int B, int C, int H, int W, int D, float* warped,
+                       int32_t* dbg_ix0, int32_t* dbg_iy0, void* stream);
+
+/*
+ * softmax over D + depth_regression + 4-bin confidence (mvsnet.py:140-160, blocks/utils.py:271-274) in one
+ * pass.  cost [B,D,h,w], depths [B,D].  Outputs (each optional) depth, confidence float32 [B,h,w],
+ * depth_index int64 [B,h,w] (= trunc(sum_d p_d * d), clamped to [0,D-1]), expected_index float32 [B,h,w],
+ * prob float32 [B,D,h,w].
+ */
+int rmvd_mvs_regress_fwd(const float* cost, const float* depths, int B, int D, int h, int w, float* depth,
+                         float* confidence, int64_t* depth_index, float* expected_index, float* prob,
+                         void* stream);
+
+/*
+ * Depth-slab softargmax.  Step 1 on each rank: partials over planes [d_begin,d_end) of a
+ * slab cost [B,Dl,h,w] (Dl = d_end - d_begin), depths_slab [B,Dl]:
+ *   partial [4,B,h,w] = (m = max, Z = sum exp(x-m), A = sum exp(x-m)*depth, I = sum exp(x-m)*index).
+ */
+int rmvd_softargmax_partial(const float* cost_slab, const float* depths_slab, int B, int Dl, int h, int w,
+                            int d_begin, float* partial, void* stream);
+/*
+ * Step 2: merge G gathered partials [G,4,B,h,w] -> merged [4,B,h,w] = (m, Z, depth = A/Z, eidx = I/Z).
+ */
+int rmvd_softargmax_combine(const float* partials, int G, int B, int h, int w, float* merged, void* stream);
+/*
+ * Step 3: this rank's share of the 4-bin confidence around the global index (mvsnet.py:143-158):
+ *   conf_part [B,h,w] = sum over d in {idx-1..idx+2} intersect [d_begin,d_end) of exp(x_d - m)/Z, idx = trunc(eidx).
+ * The ranks' conf_part are then summed (all-reduce).
+ */
+int rmvd_softargmax_confidence(const float* cost_slab, const float* merged, int B, int Dl, int h, int w,
+                               int D, int d_begin, float* conf_part, void* stream);
+
+/*
+ * soft_argmin / entropy of Vis-MVSNet (blocks/utils.py:51-68) along dim 1: volume [B,D,h,w] ->
+ * prob [B,D,h,w] (optional), expected index [B,h,w], prob_map [B,h,w] (optional; mass within |d - E| <= window,
+ * window < 0 disables), entropy [B,h,w] of the probabilities (optional).
+ */
+int rmvd_soft_argmin_fwd(const float* volume, int B, int D, int h, int w, float window, float* prob,
+                         float* expected_index, float* prob_map, float* entropy, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RMVD_B200_H_ */

@@ -1,0 +1,99 @@
+"""ctypes binding of the C ABI declared in ``include/rmvd_b200.h``.
+
+The shared library is the product; this module only extracts pointers, sizes and the current CUDA stream from
+torch tensors.  There is no CPU fallback: a missing library or a non-CUDA tensor raises.
+"""
+import ctypes
+import os
+from ctypes import c_char_p, c_float, c_int, c_int64, c_size_t, c_void_p, POINTER
+
+from . import _build
+
+_lib = None
+
+EXPORTS = (
+    "rmvd_abi_version", "rmvd_status_string", "rmvd_psweep_workspace_bytes", "rmvd_psweep_corr_fwd",
+    "rmvd_psweep_warp_fwd", "rmvd_corr_grid_fwd", "rmvd_warp_grid_fwd", "rmvd_mvs_variance_fwd",
+    "rmvd_homo_warp_fwd", "rmvd_mvs_regress_fwd", "rmvd_softargmax_partial", "rmvd_softargmax_combine",
+    "rmvd_softargmax_confidence", "rmvd_soft_argmin_fwd",
+)
+
+
+class RmvdError(RuntimeError):
+    pass
+
+
+def _declare(lib):
+    P = c_void_p
+    PP = POINTER(c_void_p)
+    PI = POINTER(c_int)
+    PL = POINTER(c_int64)
+    lib.rmvd_abi_version.restype = c_int
+    lib.rmvd_status_string.restype = c_char_p
+    lib.rmvd_status_string.argtypes = [c_int]
+    lib.rmvd_psweep_workspace_bytes.restype = c_size_t
+    lib.rmvd_psweep_workspace_bytes.argtypes = [c_int, c_int, c_int, PI, PI]
+    lib.rmvd_psweep_corr_fwd.argtypes = [P, PP, P, PP, PP, P, PL] + [c_int] * 5 + [PI, PI] + [c_int] * 4 + \
+        [P, P, c_int, c_int, P, P, P, P, c_size_t, P]
+    lib.rmvd_psweep_warp_fwd.argtypes = [P, P, P, P, P, PL] + [c_int] * 10 + [P, P, c_int, c_int, P]
+    lib.rmvd_corr_grid_fwd.argtypes = [P, P, P, P] + [c_int] * 8 + [P, P, P, c_size_t, P]
+    lib.rmvd_warp_grid_fwd.argtypes = [P, P] + [c_int] * 7 + [P, P, P]
+    lib.rmvd_mvs_variance_fwd.argtypes = [P, P, P] + [c_int] * 8 + [P, c_int, c_int, P]
+    lib.rmvd_homo_warp_fwd.argtypes = [P, P, P, P] + [c_int] * 5 + [P, P, P, P]
+    lib.rmvd_mvs_regress_fwd.argtypes = [P, P] + [c_int] * 4 + [P, P, P, P, P, P]
+    lib.rmvd_softargmax_partial.argtypes = [P, P] + [c_int] * 5 + [P, P]
+    lib.rmvd_softargmax_combine.argtypes = [P] + [c_int] * 4 + [P, P]
+    lib.rmvd_softargmax_confidence.argtypes = [P, P] + [c_int] * 6 + [P, P]
+    lib.rmvd_soft_argmin_fwd.argtypes = [P] + [c_int] * 4 + [c_float, P, P, P, P, P]
+    for name in EXPORTS:
+        if name not in ("rmvd_abi_version", "rmvd_status_string", "rmvd_psweep_workspace_bytes"):
+            getattr(lib, name).restype = c_int
+
+
+def load():
+    """Load (once) ``csrc/librmvd_b200.so``.  Raises RmvdError when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_build.LIB):
+            raise RmvdError(f"{_build.LIB} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                            "(robustmvd_b200 has no CPU or PyTorch fallback)")
+        lib = ctypes.CDLL(_build.LIB)
+        _declare(lib)
+        _lib = lib
+    return _lib
+
+
+def check(status, what):
+    if status != 0:
+        raise RmvdError(f"{what}: {load().rmvd_status_string(status).decode()} (status {status})")
+
+
+def ptr(t):
+    """Device pointer of a contiguous float32/int CUDA tensor (None -> NULL)."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RmvdError("robustmvd_b200 kernels need CUDA tensors (there is no CPU path)")
+    if not t.is_contiguous():
+        raise RmvdError("tensor must be contiguous")
+    return c_void_p(t.data_ptr())
+
+
+def ptr_array(tensors):
+    arr = (c_void_p * len(tensors))()
+    for i, t in enumerate(tensors):
+        arr[i] = ptr(t).value
+    return arr
+
+
+def int_array(vals):
+    return (c_int * len(vals))(*vals)
+
+
+def i64_array(vals):
+    return (c_int64 * len(vals))(*vals)
+
+
+def stream_ptr():
+    import torch
+    return c_void_p(torch.cuda.current_stream().cuda_stream)

@@ -1,0 +1,274 @@
+"""Drop-in for ``rmvd/models/blocks/planesweep_corr.py`` on top of the sm_100a C ABI.
+
+Same names, constructor and ``forward`` signatures, return values and assertions as the reference
+(``PlanesweepCorrelation`` :371-521, ``TorchCorr`` :143-195, ``WarpOnlyCorr`` :107-140, ``warp`` :49-104,
+``warp_multi`` :13-46, ``compute_sampling_invdepths`` :524-555).  All arithmetic runs in the CUDA library
+(``include/rmvd_b200.h``); there is no PyTorch or CPU fallback.  Forward only: outputs carry no autograd graph
+(the reference's backward is SURVEY.md row f-4).
+"""
+import numpy as np
+import torch
+import torch.nn as nn
+
+from .. import _lib
+
+NORM_NONE, NORM_DIM, NORM_BEFORE, NORM_AFTER = 0, 1, 2, 3
+
+
+def _to_torch(x, device=None):
+    if isinstance(x, np.ndarray):
+        x = torch.from_numpy(x)
+    if isinstance(x, torch.Tensor) and device is not None:
+        x = x.to(device)
+    return x
+
+
+def _f32c(t):
+    return t.detach().to(torch.float32).contiguous()
+
+
+def _corr_norm_mode(normalize):
+    """TorchCorr semantics (:170-179): "dim" -> /sqrt(C); True / "before" -> L2-normalise both inputs."""
+    if normalize == "dim":
+        return NORM_DIM
+    return NORM_BEFORE if normalize else NORM_NONE
+
+
+def _warp_norm_mode(normalize):
+    """WarpOnlyCorr semantics (:128-136): "before" -> normalise source; True / "after" -> normalise warped."""
+    if normalize == "before":
+        return NORM_BEFORE
+    if normalize and normalize != "dim":
+        return NORM_AFTER
+    return NORM_NONE
+
+
+def _workspace(nbytes, device):
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+
+
+def compute_sampling_invdepths(min_depth, max_depth, num_samples, sampling_type="linear_invdepth"):
+    """planesweep_corr.py:524-555: ``[1 or N, S]`` inverse depths (host-side schedule, S values per sample).
+
+    Runs on the device the inputs live on with the reference's own operation order; scalars stay on the CPU.
+    """
+    if isinstance(min_depth, (np.float32, float)):
+        min_depth = torch.tensor([min_depth])
+    if isinstance(max_depth, (np.float32, float)):
+        max_depth = torch.tensor([max_depth])
+    min_depth = _to_torch(min_depth)[..., None]
+    max_depth = _to_torch(max_depth)[..., None]
+    min_invdepth = 1 / max_depth
+    max_invdepth = 1 / min_depth
+    steps = torch.arange(0, num_samples, dtype=min_invdepth.dtype, device=min_invdepth.device)[None, ...]
+    if sampling_type == "linear_invdepth":
+        return min_invdepth + steps * (max_invdepth - min_invdepth) / (num_samples - 1)
+    elif sampling_type == "linear_depth":
+        inv = 1 / (min_depth + steps * (max_depth - min_depth) / (num_samples - 1))
+        return inv.flip(1)
+    raise ValueError(f"unknown sampling_type {sampling_type}")
+
+
+def _inv_strides(inv, N):
+    """Element strides (n, s, y, x) of a contiguous 4-D inverse-depth tensor with broadcast dims -> 0."""
+    assert inv.ndim == 4
+    st = list(inv.stride())
+    for k in range(4):
+        if inv.shape[k] == 1:
+            st[k] = 0
+    assert inv.shape[0] in (1, N), "sampling_invdepths batch must be 1 or N"
+    return st
+
+
+def warp(x, offset=None, grid=None, padding_mode="border"):
+    """planesweep_corr.py:49-104.  ``x [N,C,H,W]``; ``grid [N,2,h_out,w_out]`` in source pixels (or ``offset``
+    relative to pixel centres).  Returns ``(output [N,C,h_out,w_out], mask [N,1,h_out,w_out])``."""
+    assert (offset is None and grid is not None) or (grid is None and offset is not None)
+    assert padding_mode in ("border", "zeros")
+    if offset is not None:
+        h_ref, w_ref = offset.shape[-2:]
+        yy, xx = torch.meshgrid(torch.arange(h_ref, device=x.device), torch.arange(w_ref, device=x.device),
+                                indexing="ij")
+        grid = torch.stack((xx + 0.5, yy + 0.5), 0).float().unsqueeze(0).repeat(x.shape[0], 1, 1, 1) + offset
+    x = _f32c(x)
+    grid = _f32c(grid)
+    K, C, hs, ws = x.shape
+    ho, wo = grid.shape[-2:]
+    out = torch.empty((K, C, ho, wo), dtype=torch.float32, device=x.device)
+    mask = torch.empty((K, 1, ho, wo), dtype=torch.float32, device=x.device)
+    lib = _lib.load()
+    # gridDim.y carries K: chunk very large K (TorchCorr-style K = N*h*w use)
+    for k0 in range(0, K, 65535):
+        k1 = min(K, k0 + 65535)
+        st = lib.rmvd_warp_grid_fwd(_lib.ptr(x[k0:k1]), _lib.ptr(grid[k0:k1]), k1 - k0, C, hs, ws, ho, wo,
+                                    1 if padding_mode == "border" else 0, _lib.ptr(out[k0:k1]),
+                                    _lib.ptr(mask[k0:k1]), _lib.stream_ptr())
+        _lib.check(st, "rmvd_warp_grid_fwd")
+    return out, mask
+
+
+def warp_multi(x, offsets=None, grids=None, padding_mode="border"):
+    """planesweep_corr.py:13-46: ``x [N,C,hs,ws]``, ``grids [N,S,2,h,w]`` -> ``[N,S,C,h,w]``, ``[N,S,h,w]``.
+    The S-fold repeat of the source (:33) is not materialised: each plane samples the same source map."""
+    assert (offsets is None and grids is not None) or (grids is None and offsets is not None)
+    loc = offsets if offsets is not None else grids
+    N, S, _, H, W = loc.shape
+    outs, masks = [], []
+    for s in range(S):
+        o, m = warp(x, offset=None if offsets is None else loc[:, s], grid=None if grids is None else loc[:, s],
+                    padding_mode=padding_mode)
+        outs.append(o)
+        masks.append(m[:, 0])
+    return torch.stack(outs, 1), torch.stack(masks, 1)
+
+
+class WarpOnlyCorr(nn.Module):
+    """planesweep_corr.py:107-140 on caller-supplied grids (zeros or border padding)."""
+
+    def __init__(self, normalize=False, padding_mode="zeros"):
+        super().__init__()
+        self.normalize = normalize
+        self.padding_mode = padding_mode
+        if isinstance(self.normalize, str):
+            assert self.normalize in ["dim", "before", "after"]
+
+    def forward(self, feat_ref, feat_src, grids=None, mask=None):
+        if self.normalize == "before":
+            feat_src = feat_src / (torch.linalg.norm(feat_src, dim=1, keepdim=True) + 1e-9)
+        warped, warping_mask = warp_multi(x=feat_src, grids=grids, padding_mode=self.padding_mode)
+        if self.normalize and self.normalize != "before" and self.normalize != "dim":
+            warped = warped / (torch.linalg.norm(warped, dim=2, keepdim=True) + 1e-9)
+        return warped * warping_mask.unsqueeze(2), warping_mask
+
+
+class TorchCorr(nn.Module):
+    """planesweep_corr.py:143-195 on caller-supplied grids: ``rmvd_corr_grid_fwd`` (zeros padding)."""
+
+    def __init__(self, normalize=False, padding_mode="zeros"):
+        super().__init__()
+        self.normalize = normalize
+        self.padding_mode = padding_mode
+        if isinstance(self.normalize, str):
+            assert self.normalize in ["dim", "before"]
+        assert padding_mode == "zeros", "the fused correlation kernel implements zeros padding (the block's only use)"
+
+    def forward(self, feat_ref, feat_src, grids=None, mask=None):
+        feat_ref, feat_src, grids = _f32c(feat_ref), _f32c(feat_src), _f32c(grids)
+        N, C, h, w = feat_ref.shape
+        S = grids.shape[1]
+        hs, ws = feat_src.shape[-2:]
+        dev = feat_ref.device
+        m8 = None if mask is None else (mask != 0).to(torch.uint8).expand(N, S, h, w).contiguous()
+        corr = torch.empty((N, S, h, w), dtype=torch.float32, device=dev)
+        cmask = torch.empty_like(corr)
+        lib = _lib.load()
+        nb = lib.rmvd_psweep_workspace_bytes(N, C, 1, _lib.int_array([hs]), _lib.int_array([ws]))
+        wsp = _workspace(nb, dev)
+        st = lib.rmvd_corr_grid_fwd(_lib.ptr(feat_ref), _lib.ptr(feat_src), _lib.ptr(grids), _lib.ptr(m8), N, C, h, w,
+                                    hs, ws, S, _corr_norm_mode(self.normalize), _lib.ptr(corr), _lib.ptr(cmask),
+                                    _lib.ptr(wsp), wsp.numel(), _lib.stream_ptr())
+        _lib.check(st, "rmvd_corr_grid_fwd")
+        return corr, cmask
+
+
+class PlanesweepCorrelation(nn.Module):
+    """planesweep_corr.py:371-521.  ``forward`` returns ``(corrs, masks, sampling_invdepths)`` like the reference.
+
+    ``plane_range=(s_begin, s_end)`` (extension, default all planes) restricts the call to a depth slab; outputs
+    then hold only those planes.  ``debug=True`` additionally keeps ``self.debug`` with the integer
+    sampling indices and the geometric mask of every view.
+    """
+
+    @torch.no_grad()
+    def __init__(self, warp_only=False, normalize="dim"):
+        super().__init__()
+        self.warp_only = warp_only
+        self.normalize = normalize
+        if isinstance(normalize, str):
+            assert normalize in (["dim", "before", "after"] if warp_only else ["dim", "before"])
+        self.corrs = []
+        self.masks = []
+        self.debug = None
+
+    def reset(self):
+        self.corrs = []
+        self.masks = []
+        self.debug = None
+
+    @torch.no_grad()
+    def get_sampling_invdepths(self, num_sampling_points=None, min_depth=None, max_depth=None,
+                               sampling_invdepths=None, sampling_type="linear_invdepth", device=None):
+        if min_depth is not None and max_depth is not None:  # :473-480
+            assert sampling_invdepths is None
+            assert num_sampling_points is not None
+            assert sampling_type is not None
+            sampling_invdepths = compute_sampling_invdepths(min_depth, max_depth, num_sampling_points, sampling_type)
+        else:
+            assert num_sampling_points is None and min_depth is None and max_depth is None
+            assert sampling_invdepths is not None
+        sampling_invdepths = _to_torch(sampling_invdepths).to(device)
+        assert sampling_invdepths.ndim >= 2  # (N, S) or (N, S, H) or (N, S, H, W)
+        while sampling_invdepths.ndim < 4:
+            sampling_invdepths = sampling_invdepths.unsqueeze(-1)
+        return sampling_invdepths
+
+    @torch.no_grad()
+    def forward(self, feat_key, intrinsics_key, feat_sources, source_to_key_transforms, intrinsics_sources=None,
+                num_sampling_points=None, min_depth=None, max_depth=None, sampling_invdepths=None,
+                sampling_type="linear_invdepth", plane_range=None, debug=False):
+        self.reset()
+        dev = feat_key.device
+        if intrinsics_sources is None:  # :441-442
+            intrinsics_sources = [intrinsics_key] * len(feat_sources)
+        assert len(feat_sources) == len(source_to_key_transforms) == len(intrinsics_sources)  # :444
+        inv = self.get_sampling_invdepths(num_sampling_points, min_depth, max_depth, sampling_invdepths,
+                                          sampling_type, device=dev)
+        inv_c = _f32c(inv)
+        feat_key = _f32c(feat_key)
+        N, C, h, w = feat_key.shape
+        S = inv_c.shape[1]
+        assert inv_c.shape[2] in (1, h) and inv_c.shape[3] in (1, w)
+        V = len(feat_sources)
+        s0, s1 = (0, S) if plane_range is None else plane_range
+        Sl = s1 - s0
+        srcs = [_f32c(f) for f in feat_sources]
+        Kk = _f32c(intrinsics_key)
+        Ks = [_f32c(k) for k in intrinsics_sources]
+        Ts = [_f32c(t) for t in source_to_key_transforms]
+        hs = [f.shape[2] for f in srcs]
+        ws = [f.shape[3] for f in srcs]
+        ist = _lib.i64_array(_inv_strides(inv_c, N))
+        lib = _lib.load()
+        if V == 0:
+            return self.corrs, self.masks, inv
+        if not self.warp_only:
+            corr = torch.empty((V, N, Sl, h, w), dtype=torch.float32, device=dev)
+            mask = torch.empty_like(corr)
+            dbg = [None, None, None]
+            if debug:
+                dbg = [torch.empty((V, N, Sl, h, w), dtype=torch.int32, device=dev) for _ in range(2)]
+                dbg.append(torch.empty((V, N, Sl, h, w), dtype=torch.uint8, device=dev))
+            nb = lib.rmvd_psweep_workspace_bytes(N, C, V, _lib.int_array(hs), _lib.int_array(ws))
+            wsp = _workspace(nb, dev)
+            st = lib.rmvd_psweep_corr_fwd(
+                _lib.ptr(feat_key), _lib.ptr_array(srcs), _lib.ptr(Kk), _lib.ptr_array(Ks), _lib.ptr_array(Ts),
+                _lib.ptr(inv_c), ist, N, C, h, w, V, _lib.int_array(hs), _lib.int_array(ws), S, s0, s1,
+                _corr_norm_mode(self.normalize), _lib.ptr(corr), _lib.ptr(mask), Sl, 0, _lib.ptr(dbg[0]),
+                _lib.ptr(dbg[1]), _lib.ptr(dbg[2]), _lib.ptr(wsp), wsp.numel(), _lib.stream_ptr())
+            _lib.check(st, "rmvd_psweep_corr_fwd")
+            self.corrs = list(corr.unbind(0))
+            self.masks = list(mask.unbind(0))
+            if debug:
+                self.debug = dict(ix0=dbg[0], iy0=dbg[1], geom=dbg[2])
+        else:
+            for v in range(V):
+                warped = torch.empty((N, Sl, C, h, w), dtype=torch.float32, device=dev)
+                mask = torch.empty((N, Sl, h, w), dtype=torch.float32, device=dev)
+                st = lib.rmvd_psweep_warp_fwd(
+                    _lib.ptr(srcs[v]), _lib.ptr(Kk), _lib.ptr(Ks[v]), _lib.ptr(Ts[v]), _lib.ptr(inv_c), ist, N, C, h,
+                    w, hs[v], ws[v], S, s0, s1, _warp_norm_mode(self.normalize), _lib.ptr(warped), _lib.ptr(mask),
+                    Sl, 0, _lib.stream_ptr())
+                _lib.check(st, "rmvd_psweep_warp_fwd")
+                self.corrs.append(warped)
+                self.masks.append(mask)
+        return self.corrs, self.masks, inv

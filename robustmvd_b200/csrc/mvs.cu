@@ -1,0 +1,416 @@
+// MVSNet cost-volume path for sm_100a: homography warp fused with the multi-view variance, and the
+// softmax / expected-depth / confidence regression in one pass.
+//
+// Replaces homo_warp + the volume assembly (blocks/utils.py:222-268, mvsnet.py:123-136) and
+// softmax + depth_regression + 4-bin confidence (mvsnet.py:140-160, blocks/utils.py:271-274).
+//
+// Data layout in HBM: features [B,Vt,C,h,w] and cost volumes [B,D,h,w] exactly as the reference holds them;
+// the variance volume [B,C,D,h,w] is written once with 128-byte coalesced rows along w; the warped source
+// volumes (1.67 GB per view at DTU size) are never materialised.
+#include "common.cuh"
+
+namespace rmvd {
+
+constexpr int kMaxMvsViews = 16;  // source views per launch
+
+// transform = src_proj @ ref_proj_inv (utils.py:234): k-ascending, every multiply and add rounded (oracle/mvsnet.py:_matmul4)
+__device__ __forceinline__ float matmul4_elem(const float* a, const float* b, int i, int j) {
+  float acc = fmul(a[i * 4 + 0], b[0 * 4 + j]);
+#pragma unroll
+  for (int k = 1; k < 4; ++k) acc = fadd(acc, fmul(a[i * 4 + k], b[k * 4 + j]));
+  return acc;
+}
+
+// Source-view sampling coordinate of key pixel (xi, yi) at depth d (utils.py:240-264): returns the ATen-unnormalised
+// coordinate whose floor is the corner index.  M = rows 0..2 of the 4x4 transform (R | T), row-major 3x4.
+__device__ __forceinline__ void homo_coord(const float* M, int xi, int yi, float d, int H, int W, float& ix, float& iy) {
+  const float gx = fmul((float)xi, d), gy = fmul((float)yi, d), gz = d;  // :248
+  float p[3];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    float acc = fmul(M[r * 4 + 0], gx);
+    acc = __fmaf_rn(M[r * 4 + 1], gy, acc);
+    acc = __fmaf_rn(M[r * 4 + 2], gz, acc);
+    p[r] = fadd(acc, M[r * 4 + 3]);  // :251
+  }
+  const float sx = fdiv(p[0], p[2]), sy = fdiv(p[1], p[2]);       // :253
+  const float xn = fsub(fdiv(sx, (float)(W - 1) * 0.5f), 1.0f);   // :256
+  const float yn = fsub(fdiv(sy, (float)(H - 1) * 0.5f), 1.0f);   // :257
+  ix = grid_unnormalize(xn, W);                                    // grid_sample, align_corners=False (:262)
+  iy = grid_unnormalize(yn, H);
+}
+
+struct Gather {
+  int o_nw, o_ne, o_sw, o_se;
+  float nw, ne, sw, se;
+};
+__device__ __forceinline__ Gather make_gather(float ix, float iy, int H, int W, int* dbg_x0 = nullptr, int* dbg_y0 = nullptr) {
+  const Bilinear b = bilinear_setup(ix, iy, H, W);
+  const int x0 = isnan(b.x0f) ? -2 : sat_index(b.x0f, W), y0 = isnan(b.y0f) ? -2 : sat_index(b.y0f, H);
+  if (dbg_x0) { *dbg_x0 = x0; *dbg_y0 = y0; }
+  const int x0c = clampi(x0, 0, W - 1), x1c = clampi(x0 + 1, 0, W - 1);
+  const int y0c = clampi(y0, 0, H - 1), y1c = clampi(y0 + 1, 0, H - 1);
+  Gather g;
+  g.o_nw = y0c * W + x0c; g.o_ne = y0c * W + x1c; g.o_sw = y1c * W + x0c; g.o_se = y1c * W + x1c;
+  g.nw = b.nw; g.ne = b.ne; g.sw = b.sw; g.se = b.se;
+  return g;
+}
+__device__ __forceinline__ float gather_val(const float* __restrict__ img, const Gather& g) {
+  float acc = fmul(__ldg(img + g.o_nw), g.nw);
+  acc = fadd(acc, fmul(__ldg(img + g.o_ne), g.ne));
+  acc = fadd(acc, fmul(__ldg(img + g.o_sw), g.sw));
+  acc = fadd(acc, fmul(__ldg(img + g.o_se), g.se));
+  return acc;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Fused variance volume.  Thread = one voxel (d, y, x) with x fastest; blockIdx.y = group of kCh channels.
+// Per source view the thread derives its sampling footprint once and gathers kCh channels, keeping the running
+// sum and sum of squares in registers (mvsnet.py:124-133); variance = sq/V - (sum/V)^2 (:135).
+// ---------------------------------------------------------------------------------------------------------
+template <int kCh>
+__global__ void __launch_bounds__(256) mvs_variance_kernel(const float* __restrict__ feats, const float* __restrict__ proj,
+                                                           const float* __restrict__ depths, int B, int Vt, int C,
+                                                           int h, int w, int D, int d_begin, int d_end,
+                                                           float* __restrict__ variance, int out_D, int out_d0) {
+  __shared__ float s_M[kMaxMvsViews][12];
+  const int b = blockIdx.z;
+  const int P = h * w;
+  const int c0 = blockIdx.y * kCh;
+  // per-view transforms (view v >= 1): rows 0..2 of proj[b,v] @ proj[b,0]
+  for (int e = threadIdx.x; e < (Vt - 1) * 12; e += blockDim.x) {
+    const int v = 1 + e / 12, i = (e % 12) / 4, j = e % 4;
+    s_M[v - 1][i * 4 + j] = matmul4_elem(proj + ((size_t)b * Vt + v) * 16, proj + ((size_t)b * Vt) * 16, i, j);
+  }
+  __syncthreads();
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int Dl = d_end - d_begin;
+  if (idx >= (long long)Dl * P) return;
+  const int dl = (int)(idx / P), p = (int)(idx - (long long)dl * P);
+  const int d = d_begin + dl;
+  const int yi = p / w, xi = p - yi * w;
+  const float depth = depths[(size_t)b * D + d];
+
+  float sum[kCh], sq[kCh];
+  const float* ref = feats + ((size_t)b * Vt) * C * P + p;
+#pragma unroll
+  for (int k = 0; k < kCh; ++k) {
+    const float r = (c0 + k < C) ? __ldg(ref + (size_t)(c0 + k) * P) : 0.f;
+    sum[k] = r;               // volume_sum = ref_volume (:125)
+    sq[k] = fmul(r, r);       // ref_volume ** 2 (:126)
+  }
+  for (int v = 1; v < Vt; ++v) {
+    float ix, iy;
+    homo_coord(s_M[v - 1], xi, yi, depth, h, w, ix, iy);
+    const Gather g = make_gather(ix, iy, h, w);
+    const float* src = feats + ((size_t)b * Vt + v) * C * P;
+#pragma unroll
+    for (int k = 0; k < kCh; ++k) {
+      if (c0 + k < C) {
+        const float val = gather_val(src + (size_t)(c0 + k) * P, g);
+        sum[k] = fadd(sum[k], val);
+        sq[k] = fadd(sq[k], fmul(val, val));
+      }
+    }
+  }
+  const float Vf = (float)Vt;
+  float* out = variance + (((size_t)b * C + c0) * out_D + out_d0 + dl) * P + p;
+#pragma unroll
+  for (int k = 0; k < kCh; ++k) {
+    if (c0 + k < C) {
+      const float mean = fdiv(sum[k], Vf);
+      out[(size_t)k * out_D * P] = fsub(fdiv(sq[k], Vf), fmul(mean, mean));  // :135
+    }
+  }
+}
+
+// homo_warp, materialising (blocks/utils.py:222-268): thread = voxel (d,y,x), loops channels.
+__global__ void __launch_bounds__(256) homo_warp_kernel(const float* __restrict__ src_feat, const float* __restrict__ src_proj,
+                                                        const float* __restrict__ ref_proj_inv, const float* __restrict__ depths,
+                                                        int C, int H, int W, int D, float* __restrict__ warped,
+                                                        int32_t* __restrict__ dbg_ix0, int32_t* __restrict__ dbg_iy0) {
+  __shared__ float s_M[12];
+  const int b = blockIdx.y;
+  const int P = H * W;
+  if (threadIdx.x < 12) s_M[threadIdx.x] = matmul4_elem(src_proj + (size_t)b * 16, ref_proj_inv + (size_t)b * 16,
+                                                       threadIdx.x / 4, threadIdx.x % 4);
+  __syncthreads();
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)D * P) return;
+  const int d = (int)(idx / P), p = (int)(idx - (long long)d * P);
+  const int yi = p / W, xi = p - yi * W;
+  float ix, iy;
+  homo_coord(s_M, xi, yi, depths[(size_t)b * D + d], H, W, ix, iy);
+  int x0, y0;
+  const Gather g = make_gather(ix, iy, H, W, &x0, &y0);
+  if (dbg_ix0) {
+    dbg_ix0[((size_t)b * D + d) * P + p] = x0;
+    dbg_iy0[((size_t)b * D + d) * P + p] = y0;
+  }
+  const float* src = src_feat + (size_t)b * C * P;
+  float* out = warped + (((size_t)b * C) * D + d) * P + p;
+  for (int c = 0; c < C; ++c) out[(size_t)c * D * P] = gather_val(src + (size_t)c * P, g);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Softmax over D + expected depth + expected index + 4-bin confidence, one pass over the cost volume.
+// CTA = 32 pixels x 8 plane groups: warp g streams planes g, g+8, ... for 32 adjacent pixels (128-byte rows),
+// keeping the online-softmax state (m, Z, A = sum e*depth, I = sum e*index); the 8 states are merged through
+// shared memory (the same merge the depth-slab partition uses across GPUs).
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kRegWarps = 8;
+
+struct SoftState {
+  float m, Z, A, I;
+};
+__device__ __forceinline__ void soft_push(SoftState& s, float x, float depth, float index) {
+  if (x > s.m) {
+    const float r = expf(s.m - x);  // exp(-inf) = 0 on the first element
+    s.Z *= r; s.A *= r; s.I *= r;
+    s.m = x;
+  }
+  const float e = expf(x - s.m);
+  s.Z += e;
+  s.A = fmaf(e, depth, s.A);
+  s.I = fmaf(e, index, s.I);
+}
+__device__ __forceinline__ void soft_merge(SoftState& a, const SoftState& b) {
+  const float m = fmaxf(a.m, b.m);
+  const float ra = (a.m == -INFINITY) ? 0.f : expf(a.m - m);
+  const float rb = (b.m == -INFINITY) ? 0.f : expf(b.m - m);
+  a.Z = a.Z * ra + b.Z * rb;
+  a.A = a.A * ra + b.A * rb;
+  a.I = a.I * ra + b.I * rb;
+  a.m = m;
+}
+
+// mode 0: full regression (depth, confidence, index, expected index, optional prob)
+// mode 1: slab partials -> partial[4,B,P]
+__global__ void __launch_bounds__(kRegWarps * 32) mvs_regress_kernel(const float* __restrict__ cost, const float* __restrict__ depths,
+                                                                     int B, int D, int P, int index0, int mode,
+                                                                     float* __restrict__ depth_out, float* __restrict__ conf_out,
+                                                                     long long* __restrict__ index_out, float* __restrict__ eidx_out,
+                                                                     float* __restrict__ prob_out, float* __restrict__ partial) {
+  __shared__ SoftState s_state[kRegWarps][32];
+  __shared__ float s_m[32], s_Z[32];
+  const int b = blockIdx.y;
+  const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int p = blockIdx.x * 32 + lane;
+  const bool act = p < P;
+  const float* x = cost + (size_t)b * D * P + p;
+  const float* dv = depths + (size_t)b * D;
+  SoftState st{-INFINITY, 0.f, 0.f, 0.f};
+  if (act) {
+    int d = g;
+    for (; d + 3 * kRegWarps < D; d += 4 * kRegWarps) {  // four independent loads in flight
+      const float x0 = __ldg(x + (size_t)d * P), x1 = __ldg(x + (size_t)(d + kRegWarps) * P);
+      const float x2 = __ldg(x + (size_t)(d + 2 * kRegWarps) * P), x3 = __ldg(x + (size_t)(d + 3 * kRegWarps) * P);
+      soft_push(st, x0, __ldg(dv + d), (float)(index0 + d));
+      soft_push(st, x1, __ldg(dv + d + kRegWarps), (float)(index0 + d + kRegWarps));
+      soft_push(st, x2, __ldg(dv + d + 2 * kRegWarps), (float)(index0 + d + 2 * kRegWarps));
+      soft_push(st, x3, __ldg(dv + d + 3 * kRegWarps), (float)(index0 + d + 3 * kRegWarps));
+    }
+    for (; d < D; d += kRegWarps) soft_push(st, __ldg(x + (size_t)d * P), __ldg(dv + d), (float)(index0 + d));
+  }
+  s_state[g][lane] = st;
+  __syncthreads();
+  if (g == 0) {
+#pragma unroll
+    for (int k = 1; k < kRegWarps; ++k) soft_merge(st, s_state[k][lane]);
+    s_m[lane] = st.m;
+    s_Z[lane] = st.Z;
+    if (act) {
+      const size_t o = (size_t)b * P + p;
+      if (mode == 1) {
+        const size_t BP = (size_t)B * P;
+        partial[o] = st.m; partial[BP + o] = st.Z; partial[2 * BP + o] = st.A; partial[3 * BP + o] = st.I;
+      } else {
+        const float depth = st.A / st.Z, eidx = st.I / st.Z;
+        if (depth_out) depth_out[o] = depth;
+        if (eidx_out) eidx_out[o] = eidx;
+        int idx = (int)eidx;  // .long() truncates (mvsnet.py:153-156)
+        idx = idx < 0 ? 0 : (idx > D - 1 ? D - 1 : idx);
+        if (index_out) index_out[o] = idx;
+        if (conf_out) {  // prob_volume_sum4[idx] = p[idx-1] + p[idx] + p[idx+1] + p[idx+2], zero padded (:145-158)
+          float acc = 0.f;
+#pragma unroll
+          for (int k = -1; k <= 2; ++k) {
+            const int dd = idx + k;
+            if (dd >= 0 && dd < D) acc += expf(__ldg(x + (size_t)dd * P) - st.m);
+          }
+          conf_out[o] = acc / st.Z;
+        }
+      }
+    }
+  }
+  if (mode == 0 && prob_out) {
+    __syncthreads();
+    if (act) {
+      const float m = s_m[lane], Z = s_Z[lane];
+      float* po = prob_out + (size_t)b * D * P + p;
+      for (int d = g; d < D; d += kRegWarps) po[(size_t)d * P] = expf(__ldg(x + (size_t)d * P) - m) / Z;
+    }
+  }
+}
+
+// merge G slab partials [G,4,B*P] -> merged [4,B*P] = (m, Z, depth, eidx)
+__global__ void softargmax_combine_kernel(const float* __restrict__ parts, int G, long long BP, float* __restrict__ merged) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= BP) return;
+  SoftState st{-INFINITY, 0.f, 0.f, 0.f};
+  for (int g = 0; g < G; ++g) {
+    const float* q = parts + (size_t)g * 4 * BP + i;
+    SoftState o{q[0], q[BP], q[2 * BP], q[3 * BP]};
+    soft_merge(st, o);
+  }
+  merged[i] = st.m;
+  merged[BP + i] = st.Z;
+  merged[2 * BP + i] = st.A / st.Z;
+  merged[3 * BP + i] = st.I / st.Z;
+}
+
+// this rank's part of the 4-bin confidence around the global index
+__global__ void softargmax_confidence_kernel(const float* __restrict__ cost_slab, const float* __restrict__ merged, int B,
+                                             int Dl, int P, int D, int d_begin, float* __restrict__ conf_part) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = blockIdx.y;
+  if (p >= P) return;
+  const size_t BP = (size_t)B * P, o = (size_t)b * P + p;
+  const float m = merged[o], Z = merged[BP + o], eidx = merged[3 * BP + o];
+  int idx = (int)eidx;
+  idx = idx < 0 ? 0 : (idx > D - 1 ? D - 1 : idx);
+  float acc = 0.f;
+#pragma unroll
+  for (int k = -1; k <= 2; ++k) {
+    const int dd = idx + k;
+    if (dd >= 0 && dd < D && dd >= d_begin && dd < d_begin + Dl)
+      acc += expf(cost_slab[((size_t)b * Dl + (dd - d_begin)) * P + p] - m);
+  }
+  conf_part[o] = acc / Z;
+}
+
+// soft_argmin + entropy (blocks/utils.py:51-68): thread = pixel, three sweeps over D (the volume stays in L2).
+__global__ void __launch_bounds__(256) soft_argmin_kernel(const float* __restrict__ vol, int D, int P, float window,
+                                                          float* __restrict__ prob, float* __restrict__ eidx_out,
+                                                          float* __restrict__ prob_map, float* __restrict__ entropy) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = blockIdx.y;
+  if (p >= P) return;
+  const float* x = vol + (size_t)b * D * P + p;
+  SoftState st{-INFINITY, 0.f, 0.f, 0.f};
+  for (int d = 0; d < D; ++d) soft_push(st, __ldg(x + (size_t)d * P), 0.f, (float)d);
+  const float E = st.I / st.Z;
+  const size_t o = (size_t)b * P + p;
+  eidx_out[o] = E;
+  if (!prob && !prob_map && !entropy) return;
+  float pm = 0.f, ent = 0.f;
+  for (int d = 0; d < D; ++d) {
+    const float pd = expf(__ldg(x + (size_t)d * P) - st.m) / st.Z;
+    if (prob) prob[(size_t)b * D * P + (size_t)d * P + p] = pd;
+    if (fabsf((float)d - E) <= window) pm += pd;
+    ent = fmaf(-pd, logf(fminf(fmaxf(pd, 1e-9f), 1.0f)), ent);
+  }
+  if (prob_map) prob_map[o] = pm;
+  if (entropy) entropy[o] = ent;
+}
+
+}  // namespace rmvd
+
+using namespace rmvd;
+
+extern "C" int rmvd_mvs_variance_fwd(const float* feats, const float* proj, const float* depths, int B, int Vt, int C,
+                                     int h, int w, int D, int d_begin, int d_end, float* variance, int out_D,
+                                     int out_d0, void* stream) {
+  if (!feats || !proj || !depths || !variance) return RMVD_E_NULL;
+  if (B <= 0 || Vt <= 0 || C <= 0 || h <= 0 || w <= 0 || D <= 0 || out_D <= 0 || B > 65535) return RMVD_E_SHAPE;
+  if (Vt - 1 > kMaxMvsViews) return RMVD_E_SHAPE;
+  if (d_begin < 0 || d_end > D || d_begin > d_end || out_d0 < 0 || out_d0 + (d_end - d_begin) > out_D)
+    return RMVD_E_RANGE;
+  if (d_begin == d_end) return RMVD_OK;
+  const long long tot = (long long)(d_end - d_begin) * h * w;
+  constexpr int kCh = 8;
+  dim3 grid((unsigned)((tot + 255) / 256), (C + kCh - 1) / kCh, B);
+  mvs_variance_kernel<kCh><<<grid, 256, 0, (cudaStream_t)stream>>>(feats, proj, depths, B, Vt, C, h, w, D, d_begin,
+                                                                    d_end, variance, out_D, out_d0);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int rmvd_homo_warp_fwd(const float* src_feat, const float* src_proj, const float* ref_proj_inv,
+                                  const float* depths, int B, int C, int H, int W, int D, float* warped,
+                                  int32_t* dbg_ix0, int32_t* dbg_iy0, void* stream) {
+  if (!src_feat || !src_proj || !ref_proj_inv || !depths || !warped) return RMVD_E_NULL;
+  if ((dbg_ix0 == nullptr) != (dbg_iy0 == nullptr)) return RMVD_E_NULL;
+  if (B <= 0 || C <= 0 || H <= 0 || W <= 0 || D <= 0 || B > 65535) return RMVD_E_SHAPE;
+  const long long tot = (long long)D * H * W;
+  dim3 grid((unsigned)((tot + 255) / 256), B);
+  homo_warp_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src_feat, src_proj, ref_proj_inv, depths, C, H, W, D, warped,
+                                                          dbg_ix0, dbg_iy0);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int rmvd_mvs_regress_fwd(const float* cost, const float* depths, int B, int D, int h, int w, float* depth,
+                                    float* confidence, int64_t* depth_index, float* expected_index, float* prob,
+                                    void* stream) {
+  if (!cost || !depths) return RMVD_E_NULL;
+  if (B <= 0 || D <= 0 || h <= 0 || w <= 0 || B > 65535) return RMVD_E_SHAPE;
+  const int P = h * w;
+  dim3 grid((P + 31) / 32, B);
+  mvs_regress_kernel<<<grid, kRegWarps * 32, 0, (cudaStream_t)stream>>>(cost, depths, B, D, P, 0, 0, depth, confidence,
+                                                                        (long long*)depth_index, expected_index, prob,
+                                                                        nullptr);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int rmvd_softargmax_partial(const float* cost_slab, const float* depths_slab, int B, int Dl, int h, int w,
+                                       int d_begin, float* partial, void* stream) {
+  if (!cost_slab || !depths_slab || !partial) return RMVD_E_NULL;
+  if (B <= 0 || Dl <= 0 || h <= 0 || w <= 0 || d_begin < 0 || B > 65535) return RMVD_E_SHAPE;
+  const int P = h * w;
+  dim3 grid((P + 31) / 32, B);
+  mvs_regress_kernel<<<grid, kRegWarps * 32, 0, (cudaStream_t)stream>>>(cost_slab, depths_slab, B, Dl, P, d_begin, 1,
+                                                                        nullptr, nullptr, nullptr, nullptr, nullptr,
+                                                                        partial);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int rmvd_softargmax_combine(const float* partials, int G, int B, int h, int w, float* merged, void* stream) {
+  if (!partials || !merged) return RMVD_E_NULL;
+  if (G <= 0 || B <= 0 || h <= 0 || w <= 0) return RMVD_E_SHAPE;
+  const long long BP = (long long)B * h * w;
+  softargmax_combine_kernel<<<(unsigned)((BP + 255) / 256), 256, 0, (cudaStream_t)stream>>>(partials, G, BP, merged);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int rmvd_softargmax_confidence(const float* cost_slab, const float* merged, int B, int Dl, int h, int w,
+                                          int D, int d_begin, float* conf_part, void* stream) {
+  if (!cost_slab || !merged || !conf_part) return RMVD_E_NULL;
+  if (B <= 0 || Dl <= 0 || h <= 0 || w <= 0 || D <= 0 || d_begin < 0 || B > 65535) return RMVD_E_SHAPE;
+  const int P = h * w;
+  dim3 grid((P + 255) / 256, B);
+  softargmax_confidence_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(cost_slab, merged, B, Dl, P, D, d_begin, conf_part);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int rmvd_soft_argmin_fwd(const float* volume, int B, int D, int h, int w, float window, float* prob,
+                                    float* expected_index, float* prob_map, float* entropy, void* stream) {
+  if (!volume || !expected_index) return RMVD_E_NULL;
+  if (B <= 0 || D <= 0 || h <= 0 || w <= 0 || B > 65535) return RMVD_E_SHAPE;
+  const int P = h * w;
+  dim3 grid((P + 255) / 256, B);
+  soft_argmin_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(volume, D, P, window, prob, expected_index, prob_map, entropy);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int rmvd_abi_version(void) { return RMVD_ABI_VERSION; }
+
+extern "C" const char* rmvd_status_string(int status) {
+  switch (status) {
+    case RMVD_OK: return "ok";
+    case RMVD_E_NULL: return "required pointer is NULL";
+    case RMVD_E_SHAPE: return "non-positive or inconsistent size";
+    case RMVD_E_MODE: return "unknown mode";
+    case RMVD_E_WORKSPACE: return "workspace missing or too small";
+    case RMVD_E_RANGE: return "plane range outside the schedule";
+    default: return status > 0 ? cudaGetErrorString((cudaError_t)status) : "unknown status";
+  }
+}

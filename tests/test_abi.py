@@ -1,0 +1,68 @@
+"""CPU: the C-ABI library builds for sm_100a, loads, and exports every symbol include/rmvd_b200.h declares.
+No compute call is made here (there is no GPU); argument validation that returns before any CUDA call is."""
+import ctypes
+import os
+import re
+import shutil
+
+import pytest
+
+from robustmvd_b200 import _build, _lib
+
+HEADER = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "rmvd_b200.h")
+
+
+@pytest.fixture(scope="module")
+def lib():
+    if _build.is_stale() and (shutil.which("nvcc") or os.path.exists("/usr/local/cuda/bin/nvcc")):
+        _build.build()
+    return _lib.load()
+
+
+def declared_functions():
+    text = open(HEADER).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(rmvd_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_and_binding_agree():
+    assert declared_functions() == sorted(_lib.EXPORTS)
+
+
+def test_every_declared_symbol_is_exported(lib):
+    for name in declared_functions():
+        assert hasattr(lib, name), name
+    assert lib.rmvd_abi_version() == 1
+
+
+def test_only_sm100a_code_is_embedded():
+    exe = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(exe):
+        pytest.skip("cuobjdump not available")
+    import subprocess
+    out = subprocess.run([exe, "-lelf", _build.LIB], capture_output=True, text=True).stdout
+    archs = set(re.findall(r"sm_\d+a?", out))
+    assert archs == {"sm_100a"}, archs
+
+
+def test_argument_validation_needs_no_device(lib):
+    null = ctypes.c_void_p(None)
+    assert lib.rmvd_softargmax_combine(null, 2, 1, 4, 4, null, null) == -1          # RMVD_E_NULL
+    one = ctypes.c_void_p(1)
+    assert lib.rmvd_softargmax_combine(one, 0, 1, 4, 4, one, null) == -2            # RMVD_E_SHAPE
+    assert lib.rmvd_mvs_variance_fwd(one, one, one, 1, 3, 8, 4, 4, 8, 2, 9, one, 8, 0, null) == -5  # RMVD_E_RANGE
+    assert lib.rmvd_warp_grid_fwd(one, one, 1, 1, 4, 4, 4, 4, 7, one, one, null) == -3  # RMVD_E_MODE
+    assert lib.rmvd_status_string(-4).decode().startswith("workspace")
+
+
+def test_missing_library_fails_loudly(monkeypatch, tmp_path):
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(_build, "LIB", str(tmp_path / "nope.so"))
+    with pytest.raises(_lib.RmvdError):
+        _lib.load()
+
+
+def test_cpu_tensors_are_rejected():
+    import torch
+    with pytest.raises(_lib.RmvdError):
+        _lib.ptr(torch.zeros(4))

@@ -1,0 +1,147 @@
+"""GPU parity: the CUDA plane-sweep correlation (through the C ABI) against the numpy oracle and the golden vectors
+frozen from the unmodified reference.  Bars: masks, geometric masks and integer sampling indices bit-exact; corr within
+1e-4 of max|ref| (BASELINE.json north_star)."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from tools import cases
+from robustmvd_b200 import synthetic as syn
+from golden_util import load_golden, check_planesweep_against_golden
+
+pytestmark = pytest.mark.gpu
+PS = cases.planesweep_cases(include_large=True)
+TOL = 1e-4  # relative to max|corr| of the view
+
+
+def _run_cuda(case, plane_range=None, debug=True):
+    from robustmvd_b200.blocks.planesweep_corr import PlanesweepCorrelation
+    dev = "cuda:0"
+    t = lambda a: None if a is None else torch.from_numpy(np.asarray(a)).to(dev)  # noqa: E731
+    kw = {k: (t(v) if isinstance(v, np.ndarray) else v) for k, v in case["kwargs"].items()}
+    blk = PlanesweepCorrelation(warp_only=case.get("warp_only", False), normalize=case.get("normalize", "dim"))
+    corrs, masks, inv = blk(
+        feat_key=t(case["feat_key"]), intrinsics_key=t(case["intrinsics_key"]),
+        feat_sources=[t(f) for f in case["feat_sources"]], source_to_key_transforms=[t(x) for x in case["transforms"]],
+        intrinsics_sources=None if case["intrinsics_sources"] is None else [t(x) for x in case["intrinsics_sources"]],
+        plane_range=plane_range, debug=debug and not case.get("warp_only", False), **kw)
+    torch.cuda.synchronize()
+    dbg = blk.debug
+    return ([c.cpu().numpy() for c in corrs], [m.cpu().numpy() for m in masks], inv.cpu().numpy(),
+            None if dbg is None else {k: v.cpu().numpy() for k, v in dbg.items()})
+
+
+@pytest.mark.parametrize("case", PS, ids=[c["name"] for c in PS])
+def test_cuda_matches_oracle_and_golden(cuda_lib, case):
+    corrs, masks, inv, dbg = _run_cuda(case)
+    ocorrs, omasks, oinv, odbg = oracle.planesweep_correlation(
+        case["feat_key"], case["intrinsics_key"], case["feat_sources"], case["transforms"], case["intrinsics_sources"],
+        warp_only=case.get("warp_only", False), normalize=case.get("normalize", "dim"), return_debug=True,
+        **case["kwargs"])
+    assert np.array_equal(inv, oinv)
+    for v in range(len(corrs)):
+        assert np.array_equal(masks[v], omasks[v]), f"mask view {v}: {(masks[v] != omasks[v]).sum()} mismatches"
+        scale = max(float(np.abs(ocorrs[v]).max()), 1e-30)
+        err = float(np.abs(corrs[v] - ocorrs[v]).max()) / scale
+        assert err <= TOL, f"corr view {v}: {err}"
+        if dbg is not None:
+            assert np.array_equal(dbg["ix0"][v], odbg[v]["ix0"])
+            assert np.array_equal(dbg["iy0"][v], odbg[v]["iy0"])
+            assert np.array_equal(dbg["geom"][v].astype(bool), odbg[v]["geom_mask"])
+    g = load_golden("ps", case["name"])
+    if dbg is not None:
+        check_planesweep_against_golden(g, corrs, masks, inv, list(dbg["ix0"]), list(dbg["iy0"]), list(dbg["geom"]), TOL)
+    else:
+        check_planesweep_against_golden(g, corrs, masks, inv, tol=TOL)
+
+
+def test_depth_slabs_concatenate_to_full_volume(cuda_lib):
+    case = [c for c in PS if c["name"] == "kitti_like_c32"][0]
+    full_c, full_m, _, _ = _run_cuda(case, debug=False)
+    S = case["kwargs"]["num_sampling_points"]
+    cuts = [0, 37, 128, 129, S]
+    for v in range(len(full_c)):
+        parts_c, parts_m = [], []
+        for lo, hi in zip(cuts[:-1], cuts[1:]):
+            c, m, _, _ = _run_cuda(case, plane_range=(lo, hi), debug=False)
+            parts_c.append(c[v])
+            parts_m.append(m[v])
+        assert np.array_equal(np.concatenate(parts_c, 1), full_c[v])
+        assert np.array_equal(np.concatenate(parts_m, 1), full_m[v])
+
+
+def test_cfg2_full_size_against_oracle(cuda_lib):
+    """BASELINE.json config 2 at full size: KITTI 48x160 features, C=256, S=256, 2 source views."""
+    cfg = syn.CFG2
+    inp = syn.planesweep_inputs(cfg["h"], cfg["w"], cfg["C"], cfg["V"])
+    case = dict(name="cfg2", feat_key=inp["feat_key"], intrinsics_key=inp["intrinsics_key"],
+                feat_sources=inp["feat_sources"], transforms=inp["transforms"], intrinsics_sources=None,
+                kwargs=dict(num_sampling_points=cfg["S"], min_depth=cfg["min_depth"], max_depth=cfg["max_depth"]))
+    corrs, masks, inv, dbg = _run_cuda(case)
+    ocorrs, omasks, oinv, odbg = oracle.planesweep_correlation(
+        case["feat_key"], case["intrinsics_key"], case["feat_sources"], case["transforms"], None, return_debug=True,
+        **case["kwargs"])
+    for v in range(2):
+        assert np.array_equal(masks[v], omasks[v])
+        assert np.array_equal(dbg["ix0"][v], odbg[v]["ix0"]) and np.array_equal(dbg["iy0"][v], odbg[v]["iy0"])
+        scale = float(np.abs(ocorrs[v]).max())
+        assert float(np.abs(corrs[v] - ocorrs[v]).max()) <= TOL * scale
+        assert 0.3 < masks[v].mean() < 0.95  # the synthetic geometry keeps a useful share of samples in view
+
+
+def test_linearity_and_mask_invariance_at_eth3d_size(cuda_lib):
+    """Size-independent properties at BASELINE config 4 (96x144, C=256, S=256): corr is linear in the key features and
+    the mask does not depend on the features at all."""
+    cfg = syn.CFG4
+    inp = syn.planesweep_inputs(cfg["h"], cfg["w"], cfg["C"], 2, seed=77)
+    base = dict(name="cfg4", intrinsics_key=inp["intrinsics_key"], feat_sources=inp["feat_sources"],
+                transforms=inp["transforms"], intrinsics_sources=None,
+                kwargs=dict(num_sampling_points=cfg["S"], min_depth=cfg["min_depth"], max_depth=cfg["max_depth"]))
+    k1 = inp["feat_key"]
+    k2 = syn.features(k1.shape, 991)
+    c1, m1, _, _ = _run_cuda(dict(base, feat_key=k1), debug=False)
+    c2, m2, _, _ = _run_cuda(dict(base, feat_key=k2), debug=False)
+    c3, m3, _, _ = _run_cuda(dict(base, feat_key=(2.0 * k1 - 0.5 * k2).astype(np.float32)), debug=False)
+    for v in range(2):
+        assert np.array_equal(m1[v], m2[v]) and np.array_equal(m1[v], m3[v])
+        ref = 2.0 * c1[v] - 0.5 * c2[v]
+        assert np.abs(c3[v] - ref).max() <= 1e-4 * np.abs(ref).max()
+        assert (c1[v][m1[v] == 0] == 0).all()
+
+
+def test_torchcorr_on_explicit_grids(cuda_lib):
+    from robustmvd_b200.blocks.planesweep_corr import TorchCorr
+    case = [c for c in PS if c["name"] == "src_res_differs"][0]
+    _, _, _, odbg = oracle.planesweep_correlation(
+        case["feat_key"], case["intrinsics_key"], case["feat_sources"], case["transforms"], case["intrinsics_sources"],
+        return_debug=True, **case["kwargs"])
+    for nm in ("dim", False, True):
+        for v in range(2):
+            us, vs, gm = odbg[v]["us"], odbg[v]["vs"], odbg[v]["geom_mask"]
+            oc, om = oracle.torch_corr(case["feat_key"], case["feat_sources"][v], us, vs, mask=gm, normalize=nm)
+            grids = torch.from_numpy(np.stack([us, vs], 2)).cuda()
+            c, m = TorchCorr(normalize=nm)(torch.from_numpy(case["feat_key"]).cuda(),
+                                           torch.from_numpy(case["feat_sources"][v]).cuda(), grids,
+                                           torch.from_numpy(gm).cuda())
+            assert np.array_equal(m.cpu().numpy(), om)
+            assert np.abs(c.cpu().numpy() - oc).max() <= TOL * np.abs(oc).max()
+
+
+def test_warp_function_zeros_and_border(cuda_lib):
+    from robustmvd_b200.blocks.planesweep_corr import warp
+    rng = np.random.default_rng(5)
+    x = rng.standard_normal((3, 5, 9, 14), dtype=np.float32)
+    grid = np.stack([rng.uniform(-3, 17, (3, 6, 8)), rng.uniform(-3, 12, (3, 6, 8))], 1).astype(np.float32)
+    b = oracle.bilinear_setup(grid[:, 0], grid[:, 1], 9, 14)
+    from oracle.planesweep import grid_sample_bilinear_zeros
+    ref = grid_sample_bilinear_zeros(x, b)
+    out, mask = warp(torch.from_numpy(x).cuda(), grid=torch.from_numpy(grid).cuda(), padding_mode="zeros")
+    assert np.abs(out.cpu().numpy() - ref).max() < 1e-5
+    assert np.array_equal(mask.cpu().numpy()[:, 0], b["samp_mask"])
+    ref_b = torch.nn.functional.grid_sample(
+        torch.from_numpy(x), torch.from_numpy(np.stack([2 * grid[:, 0] / 14 - 1, 2 * grid[:, 1] / 9 - 1], -1)),
+        padding_mode="border", align_corners=False).numpy()
+    out_b, mask_b = warp(torch.from_numpy(x).cuda(), grid=torch.from_numpy(grid).cuda(), padding_mode="border")
+    assert np.abs(out_b.cpu().numpy() - ref_b).max() < 1e-4
+    assert (mask_b.cpu().numpy() == 1).all()

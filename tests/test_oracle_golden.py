@@ -1,0 +1,61 @@
+"""CPU: the numpy oracle against the golden vectors frozen from the UNMODIFIED reference (tools/make_golden.py)."""
+import numpy as np
+import pytest
+
+import oracle
+from tools import cases
+from golden_util import (load_golden, check_planesweep_against_golden, check_mvs_variance_against_golden,
+                         check_warp_against_golden, check_regress_against_golden)
+
+PS = cases.planesweep_cases(include_large=True)
+MVS = cases.mvs_cases(include_large=True)
+
+
+@pytest.mark.parametrize("case", PS, ids=[c["name"] for c in PS])
+def test_planesweep_oracle_matches_golden(case):
+    g = load_golden("ps", case["name"])
+    corrs, masks, inv, dbg = oracle.planesweep_correlation(
+        case["feat_key"], case["intrinsics_key"], case["feat_sources"], case["transforms"], case["intrinsics_sources"],
+        warp_only=case.get("warp_only", False), normalize=case.get("normalize", "dim"), return_debug=True,
+        **case["kwargs"])
+    check_planesweep_against_golden(g, corrs, masks, inv, [d["ix0"] for d in dbg], [d["iy0"] for d in dbg],
+                                    [d["geom_mask"] for d in dbg], tol=1e-5)
+
+
+@pytest.mark.parametrize("case", MVS, ids=[c["name"] for c in MVS])
+def test_mvs_oracle_matches_golden(case):
+    g = load_golden("mvs", case["name"])
+    var = oracle.mvs_variance(case["feats"], case["proj"], case["depth"])
+    check_mvs_variance_against_golden(g, var, tol=1e-5)
+    w1 = oracle.homo_warp(case["feats"][:, 1], case["proj"][:, 1], case["proj"][:, 0], case["depth"])
+    check_warp_against_golden(g, w1, tol=1e-5)
+    d, c, i, e = oracle.mvs_regress(case["cost"], case["depth"])
+    check_regress_against_golden(g, d, c, i, e, rtol=1e-5)
+    p, sa, pm = oracle.soft_argmin(case["cost"], 1, keepdim=True, window=2)
+    assert np.abs(sa - g["soft_argmin"]).max() < 1e-3
+    assert np.abs(pm - g["prob_map"]).max() < 1e-4
+    assert np.abs(oracle.entropy(p, 1, keepdim=True) - g["entropy"]).max() < 1e-4
+
+
+def test_slab_partials_combine_to_full_regression():
+    c = MVS[0]
+    D = c["cost"].shape[1]
+    d, conf, idx, eidx = oracle.mvs_regress(c["cost"], c["depth"])
+    parts = []
+    for lo, hi in ((0, 3), (3, D)):
+        parts.append(oracle.softargmax_partials(c["cost"][:, lo:hi], c["depth"][:, lo:hi], lo))
+    _, _, dep, ei = oracle.softargmax_combine(parts)
+    assert np.allclose(dep, d, rtol=1e-5) and np.allclose(ei, eidx, rtol=1e-5, atol=1e-5)
+
+
+def test_torch_cpu_baseline_port_matches_oracle():
+    """The multi-threaded CPU baseline that bench.py times (oracle/torch_cpu.py) computes the same thing."""
+    from oracle import torch_cpu
+    case = [c for c in PS if c["name"] == "kitti_like_c32"][0]
+    g = load_golden("ps", case["name"])
+    corrs, masks, inv = torch_cpu.planesweep_correlation(
+        case["feat_key"], case["intrinsics_key"], case["feat_sources"], case["transforms"], **case["kwargs"])
+    check_planesweep_against_golden(g, corrs, masks, inv, tol=1e-5)
+    m = MVS[0]
+    var = torch_cpu.mvs_variance(m["feats"], m["proj"], m["depth"])
+    check_mvs_variance_against_golden(load_golden("mvs", m["name"]), var, tol=1e-5)
