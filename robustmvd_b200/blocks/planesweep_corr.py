@@ -50,14 +50,15 @@ def _workspace(nbytes, device):
 def compute_sampling_invdepths(min_depth, max_depth, num_samples, sampling_type="linear_invdepth"):
     """planesweep_corr.py:524-555: ``[1 or N, S]`` inverse depths (host-side schedule, S values per sample).
 
-    Runs on the device the inputs live on with the reference's own operation order; scalars stay on the CPU.
+    Evaluated on the HOST with the reference's own operation order (S values per sample): torch's CUDA division
+    by a scalar multiplies by the reciprocal, which would move the last bit of the schedule.
     """
     if isinstance(min_depth, (np.float32, float)):
         min_depth = torch.tensor([min_depth])
     if isinstance(max_depth, (np.float32, float)):
         max_depth = torch.tensor([max_depth])
-    min_depth = _to_torch(min_depth)[..., None]
-    max_depth = _to_torch(max_depth)[..., None]
+    min_depth = _to_torch(min_depth).cpu()[..., None]
+    max_depth = _to_torch(max_depth).cpu()[..., None]
     min_invdepth = 1 / max_depth
     max_invdepth = 1 / min_depth
     steps = torch.arange(0, num_samples, dtype=min_invdepth.dtype, device=min_invdepth.device)[None, ...]
