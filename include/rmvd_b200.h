@@ -46,8 +46,8 @@ const char* rmvd_status_string(int status);
  * robust_mvd family
  * ------------------------------------------------------------------------------------------------- */
 
-/* Scratch bytes rmvd_psweep_corr_fwd needs (channels-last copies of the V source feature maps). */
-size_t rmvd_psweep_workspace_bytes(int N, int C, int V, const int* hs_host, const int* ws_host);
+/* Scratch bytes rmvd_psweep_corr_fwd needs (channels-last copies of the key and the V source feature maps). */
+size_t rmvd_psweep_workspace_bytes(int N, int C, int h, int w, int V, const int* hs_host, const int* ws_host);
 
 /*
  * PlanesweepCorrelation.forward with warp_only=False (planesweep_corr.py:396-427 -> :436-521) fused into one

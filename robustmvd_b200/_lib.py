@@ -32,7 +32,7 @@ def _declare(lib):
     lib.rmvd_status_string.restype = c_char_p
     lib.rmvd_status_string.argtypes = [c_int]
     lib.rmvd_psweep_workspace_bytes.restype = c_size_t
-    lib.rmvd_psweep_workspace_bytes.argtypes = [c_int, c_int, c_int, PI, PI]
+    lib.rmvd_psweep_workspace_bytes.argtypes = [c_int, c_int, c_int, c_int, c_int, PI, PI]
     lib.rmvd_psweep_corr_fwd.argtypes = [P, PP, P, PP, PP, P, PL] + [c_int] * 5 + [PI, PI] + [c_int] * 4 + \
         [P, P, c_int, c_int, P, P, P, P, c_size_t, P]
     lib.rmvd_psweep_warp_fwd.argtypes = [P, P, P, P, P, PL] + [c_int] * 10 + [P, P, c_int, c_int, P]

@@ -163,7 +163,7 @@ class TorchCorr(nn.Module):
         corr = torch.empty((N, S, h, w), dtype=torch.float32, device=dev)
         cmask = torch.empty_like(corr)
         lib = _lib.load()
-        nb = lib.rmvd_psweep_workspace_bytes(N, C, 1, _lib.int_array([hs]), _lib.int_array([ws]))
+        nb = lib.rmvd_psweep_workspace_bytes(N, C, h, w, 1, _lib.int_array([hs]), _lib.int_array([ws]))
         wsp = _workspace(nb, dev)
         st = lib.rmvd_corr_grid_fwd(_lib.ptr(feat_ref), _lib.ptr(feat_src), _lib.ptr(grids), _lib.ptr(m8), N, C, h, w,
                                     hs, ws, S, _corr_norm_mode(self.normalize), _lib.ptr(corr), _lib.ptr(cmask),
@@ -249,7 +249,7 @@ class PlanesweepCorrelation(nn.Module):
             if debug:
                 dbg = [torch.empty((V, N, Sl, h, w), dtype=torch.int32, device=dev) for _ in range(2)]
                 dbg.append(torch.empty((V, N, Sl, h, w), dtype=torch.uint8, device=dev))
-            nb = lib.rmvd_psweep_workspace_bytes(N, C, V, _lib.int_array(hs), _lib.int_array(ws))
+            nb = lib.rmvd_psweep_workspace_bytes(N, C, h, w, V, _lib.int_array(hs), _lib.int_array(ws))
             wsp = _workspace(nb, dev)
             st = lib.rmvd_psweep_corr_fwd(
                 _lib.ptr(feat_key), _lib.ptr_array(srcs), _lib.ptr(Kk), _lib.ptr_array(Ks), _lib.ptr_array(Ts),

@@ -9,33 +9,12 @@
 //   source features repacked once per call to channels-last [N, hs*ws, C] in the caller's workspace, so one
 //                  source texel is one contiguous C-vector (1 KB at C = 256) fetched with 128-bit loads.
 //   corr, mask     [V, N, S, h, w] written once, 128-byte coalesced rows staged through shared memory.
-#include "common.cuh"
+#include <cstdlib>
+#include <cstring>
+
+#include "psweep.cuh"
 
 namespace rmvd {
-
-constexpr int kMaxViews = 16;   // source views per launch (more views: the host loops)
-constexpr int kTilePx = 32;     // key pixels per CTA
-constexpr int kWarps = 8;       // warps per CTA; each owns kTilePx / kWarps pixels
-constexpr int kPxPerWarp = kTilePx / kWarps;
-
-struct PsweepArgs {
-  const float* key;                  // [N,C,h,w]
-  const float* src[kMaxViews];       // channels-last copies [N,hs*ws,C]
-  const float* Kk;                   // [N,3,3]
-  const float* Ks[kMaxViews];        // [N,3,3]
-  const float* T[kMaxViews];         // [N,4,4]
-  const float* invd;
-  long long ist[4];                  // element strides of invd for (n,s,y,x)
-  const float* grids;                // kFromGrid: [N,S,2,h,w] sampling positions in source pixels
-  const uint8_t* grid_mask;          // kFromGrid: optional [N,S,h,w]
-  int hs[kMaxViews], ws[kMaxViews];
-  int N, C, h, w, S, s_begin, s_end, norm, out_S, out_s0, v0;
-  float* corr;                       // [V,N,out_S,h,w]
-  float* mask;
-  int32_t* dbg_ix0;
-  int32_t* dbg_iy0;
-  uint8_t* dbg_geom;
-};
 
 // ---------------------------------------------------------------------------------------------------------
 // NCHW -> channels-last repack of one source feature map, optionally L2-normalised along C
@@ -381,8 +360,8 @@ static int repack(const float* src, float* dst, int N, int C, int P, int l2norm,
 
 using namespace rmvd;
 
-extern "C" size_t rmvd_psweep_workspace_bytes(int N, int C, int V, const int* hs, const int* ws) {
-  size_t tot = 0;
+extern "C" size_t rmvd_psweep_workspace_bytes(int N, int C, int h, int w, int V, const int* hs, const int* ws) {
+  size_t tot = (((size_t)N * C * h * w * sizeof(float)) + 255) / 256 * 256;  // channels-last key copy
   for (int v = 0; v < V; ++v) tot += (((size_t)N * C * hs[v] * ws[v] * sizeof(float)) + 255) / 256 * 256;
   return tot;
 }
@@ -407,11 +386,23 @@ extern "C" int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* f
     if (!feat_src[v] || !intrinsics_src[v] || !src_to_key[v]) return RMVD_E_NULL;
     if (hs[v] <= 0 || ws[v] <= 0 || hs[v] >= 32768 || ws[v] >= 32768) return RMVD_E_SHAPE;
   }
-  if (workspace_bytes < rmvd_psweep_workspace_bytes(N, C, V, hs, ws) || !workspace) return RMVD_E_WORKSPACE;
+  if (workspace_bytes < rmvd_psweep_workspace_bytes(N, C, h, w, V, hs, ws) || !workspace) return RMVD_E_WORKSPACE;
   if (s_begin == s_end) return RMVD_OK;
   cudaStream_t st = (cudaStream_t)stream;
 
+  // kernel choice: the banded-GEMM kernel whenever the shape qualifies (C % 32 == 0, source map <= 65536 texels);
+  // RMVD_PSWEEP_KERNEL=direct forces the general direct kernel (A/B measurements only).
+  const char* force = getenv("RMVD_PSWEEP_KERNEL");
+  bool band = (C % 32 == 0) && !(force && strcmp(force, "direct") == 0);
+  for (int v = 0; v < V; ++v) band = band && ((long long)hs[v] * ws[v] <= 65536);
+
   char* wsp = (char*)workspace;
+  float* key_nhwc = (float*)wsp;
+  wsp += (((size_t)N * C * h * w * sizeof(float)) + 255) / 256 * 256;
+  if (band) {
+    int rc = repack(feat_key, key_nhwc, N, C, h * w, normalize_mode == RMVD_NORM_BEFORE, st);
+    if (rc) return rc;
+  }
   for (int v0 = 0; v0 < V; v0 += kMaxViews) {
     const int nv = (V - v0 < kMaxViews) ? (V - v0) : kMaxViews;
     PsweepArgs A{};
@@ -434,7 +425,7 @@ extern "C" int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* f
     A.N = N; A.C = C; A.h = h; A.w = w; A.S = S; A.s_begin = s_begin; A.s_end = s_end;
     A.norm = normalize_mode; A.out_S = out_S; A.out_s0 = out_s0; A.v0 = v0;
     A.corr = corr; A.mask = mask; A.dbg_ix0 = dbg_ix0; A.dbg_iy0 = dbg_iy0; A.dbg_geom = dbg_geom;
-    int rc = dispatch_corr<false>(A, nv, st);
+    int rc = band ? launch_psweep_band(A, key_nhwc, nv, st) : dispatch_corr<false>(A, nv, st);
     if (rc) return rc;
   }
   return RMVD_OK;
@@ -449,7 +440,7 @@ extern "C" int rmvd_corr_grid_fwd(const float* feat_key, const float* feat_src, 
     return RMVD_E_SHAPE;
   if (normalize_mode != RMVD_NORM_NONE && normalize_mode != RMVD_NORM_DIM && normalize_mode != RMVD_NORM_BEFORE)
     return RMVD_E_MODE;
-  if (!workspace || workspace_bytes < rmvd_psweep_workspace_bytes(N, C, 1, &hs, &ws)) return RMVD_E_WORKSPACE;
+  if (!workspace || workspace_bytes < rmvd_psweep_workspace_bytes(N, C, h, w, 1, &hs, &ws)) return RMVD_E_WORKSPACE;
   cudaStream_t st = (cudaStream_t)stream;
   int rc = repack(feat_src, (float*)workspace, N, C, hs * ws, normalize_mode == RMVD_NORM_BEFORE, st);
   if (rc) return rc;

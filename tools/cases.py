@@ -64,6 +64,29 @@ def planesweep_cases(include_large=True):
                          warp_only=True, normalize=nm))
     # C not a multiple of 4, odd sizes
     cases.append(_ps("odd_sizes", 7, 11, 5, [T(syn.rot_y(1), (0.2, 0, 0))], S=7, seed=22))
+    # banded-GEMM kernel (C % 32 == 0) over the same pose zoo, plus geometries that overflow its band capacity
+    cases.append(_ps("band_stereo_c32", 24, 40, 32, [T(t=(-0.54, 0, 0)), T(t=(0.54, 0, 0))], S=64, seed=50))
+    cases.append(_ps("band_forward_c32", 24, 40, 32, [T(t=(0, 0, 0.5)), T(t=(0.02, 0.01, -0.5))], S=64, seed=51))
+    cases.append(_ps("band_roll_c64", 20, 36, 64, [T(syn.rot_z(25) @ syn.rot_x(6), (0.3, -0.1, 0.03))], S=48, seed=52))
+    cases.append(_ps("band_rot90_behind_c32", 16, 24, 32,
+                     [T(syn.rot_y(90), (0.3, 0, 0.2)), T(syn.rot_y(180), (0, 0, 1.0)), T(t=(0, 0, -3.0))], S=24, seed=53))
+    Kk2 = syn.relative_intrinsics(24, 40, fx_rel=0.7, fy_rel=1.1, cx_rel=0.45, cy_rel=0.55, n=2)
+    Ks2 = syn.relative_intrinsics(18, 28, fx_rel=0.62, fy_rel=1.0, cx_rel=0.52, cy_rel=0.48, n=2)
+    cases.append(_ps("band_srcres_batch2_c32", 24, 40, 32,
+                     [T(syn.rot_y(3), (0.3, 0.02, 0.01), n=2), T(syn.rot_y(-4), (-0.4, 0, 0.05), n=2)], hs=18, ws=28,
+                     K_key=Kk2, K_src=[Ks2, Ks2], n=2, seed=54,
+                     kwargs=dict(num_sampling_points=40, min_depth=np.array([0.5, 1.0], np.float32),
+                                 max_depth=np.array([50.0, 200.0], np.float32))))
+    rng = np.random.default_rng(55)
+    inv4 = (rng.random((1, 20, 24, 40), dtype=np.float32) * np.float32(2.0) + np.float32(0.01))
+    cases.append(_ps("band_perpixel_inv_direct_c32", 24, 40, 32, [T(syn.rot_y(2), (2.5, 0, 0.02))], seed=56,
+                     kwargs=dict(sampling_invdepths=inv4)))
+    inv5 = (np.random.default_rng(60).random((1, 16, 24, 160), dtype=np.float32) * np.float32(1.2) + np.float32(0.01))
+    cases.append(_ps("band_scatter_direct_c32", 24, 160, 32, [T(t=(1.0, 0.1, 0.0))], seed=60,
+                     kwargs=dict(sampling_invdepths=inv5)))
+    cases.append(_ps("band_split_forward_c32", 48, 96, 32, [T(syn.rot_z(8), (0.1, 0.05, 1.2))], S=256, seed=57))
+    cases.append(_ps("band_norm_before_c32", 24, 40, 32, [T(syn.rot_y(2), (0.3, 0, 0.02))], S=32, seed=58, normalize=True))
+    cases.append(_ps("band_ragged_tile_c32", 7, 11, 32, [T(syn.rot_y(1), (0.2, 0, 0))], S=37, seed=59))
     if include_large:
         # KITTI-like geometry at reduced channel count, full plane count
         cases.append(_ps("kitti_like_c32", 48, 160, 32, syn.kitti_like_views(2), S=256, seed=30))
