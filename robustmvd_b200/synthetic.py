@@ -101,3 +101,31 @@ def mvs_inputs(h, w, C, V, D, n=1, seed=4321, min_depth=0.425, max_depth=0.935, 
     depth = np.repeat(np.linspace(min_depth, max_depth, D, dtype=np.float32)[None], n, 0)
     cost = rng.standard_normal((n, D, h, w), dtype=np.float32) * np.float32(3.0)
     return dict(feats=feats, proj=proj, depth=depth, cost=cost)
+
+
+def model_sample(H, W, num_sources, seed=2024, batch=None, depth_range=None):
+    """A synthetic ``model.run`` sample in the reference's data format (rmvd/data/README.md): list of ``3xHxW`` float32
+    images in [0,255] (key view first), ``3x3`` pixel intrinsics, ``4x4`` key->view poses, ``keyview_idx = 0``.
+    Smooth random textures so the encoders see image-like input; KITTI-like intrinsics and baselines.
+    ``batch=None`` -> un-batched sample; ``batch=n`` -> every entry gets a leading dimension n."""
+    rng = np.random.default_rng(seed)
+    n = 1 if batch is None else batch
+    ys, xs = np.meshgrid(np.linspace(0, 1, H, dtype=np.float32), np.linspace(0, 1, W, dtype=np.float32), indexing="ij")
+    images = []
+    for v in range(num_sources + 1):
+        im = np.zeros((n, 3, H, W), np.float32)
+        for k in range(6):
+            fx, fy, ph = rng.uniform(1, 9, (n, 3, 1, 1)), rng.uniform(1, 9, (n, 3, 1, 1)), rng.uniform(0, 6.28, (n, 3, 1, 1))
+            im += (np.sin(6.28 * (fx * xs + fy * ys) + ph) / (k + 1)).astype(np.float32)
+        im = 127.5 + 50.0 * im + rng.normal(0, 4.0, im.shape).astype(np.float32)
+        images.append(np.clip(im, 0, 255).astype(np.float32))
+    K = np.array([[0.58 * W, 0, 0.5 * W], [0, 0.58 * W, 0.5 * H], [0, 0, 1]], np.float32)
+    intrinsics = [np.repeat(K[None], n, 0) for _ in range(num_sources + 1)]
+    poses = [make_transform(n=n)] + kitti_like_views(num_sources, n)
+    sample = dict(images=images, intrinsics=intrinsics, poses=poses, keyview_idx=0 if batch is None else np.zeros(n, np.int64))
+    if depth_range is not None:
+        sample["depth_range"] = tuple(np.float32(d) if batch is None else np.full(n, d, np.float32) for d in depth_range)
+    if batch is None:
+        for key in ("images", "intrinsics", "poses"):
+            sample[key] = [a[0] for a in sample[key]]
+    return sample

@@ -102,3 +102,27 @@ def mvs_cases(include_large=True):
     if include_large:
         cases.append(dict(name="mvs_dtu_quarter", **syn.mvs_inputs(56, 76, 32, 5, 48, seed=43, fx=90.0)))
     return cases
+
+
+# ---------------------------------------------------------------------------------------------------------
+# model-level cases (tools/make_model_golden.py, tests/test_gpu_models.py)
+# ---------------------------------------------------------------------------------------------------------
+MODEL_SEED = 1234            # torch.manual_seed before create_model: both sides draw identical weights
+MVSNET_PROB_GAIN = 3.0e5     # cost_regularization.prob.weight *= gain after the seeded init: with untrained weights the
+                             # regularised cost is ~1e-5 and the softmax flat; the gain makes depth / confidence depend
+                             # on the cost volume (std of depth ~ 5 m over a 2..40 m range)
+MODEL_CASES = {
+    "robust_mvd": dict(model="robust_mvd", sample=dict(H=128, W=192, num_sources=2, seed=11)),
+    "robust_mvd_batch2": dict(model="robust_mvd", sample=dict(H=64, W=128, num_sources=3, seed=12, batch=2)),
+    "mvsnet_train": dict(model="mvsnet_train", sample=dict(H=64, W=96, num_sources=2, seed=13, depth_range=(2.0, 40.0))),
+    "mvsnet_train_default_range": dict(model="mvsnet_train", sample=dict(H=64, W=96, num_sources=3, seed=14)),
+}
+
+
+def prepare_model_for_case(model, model_name):
+    """Test-only weight tweak applied identically to the reference model and to the candidate."""
+    import torch
+    if model_name == "mvsnet_train":
+        with torch.no_grad():
+            model.cost_regularization.prob.weight *= MVSNET_PROB_GAIN
+    return model
