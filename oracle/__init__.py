@@ -40,6 +40,7 @@ from .mvsnet import (  # noqa: F401
     mvs_regress,
     softargmax_partials,
     softargmax_combine,
+    softargmax_confidence_part,
     soft_argmin,
     entropy,
 )

@@ -215,3 +215,19 @@ def entropy(volume, dim=1, keepdim=False):
     """utils.py:67-68."""
     v = _f32(volume)
     return np.sum(-v * np.log(np.clip(v, F32(1e-9), F32(1.0))), axis=dim, keepdims=keepdim, dtype=np.float32)
+
+
+def softargmax_confidence_part(cost_slab, merged_m, merged_Z, merged_eidx, num_planes, d_begin):
+    """One slab's share of the 4-bin confidence (mvsnet.py:143-158) around the GLOBAL index ``trunc(eidx)``:
+    ``sum_{d in {idx-1..idx+2} & slab} exp(x_d - m) / Z``; the shares of all slabs sum to the confidence."""
+    x = _f32(cost_slab)
+    B, Dl, h, w = x.shape
+    idx = np.clip(merged_eidx.astype(np.int64), 0, num_planes - 1)
+    out = np.zeros((B, h, w), np.float32)
+    for k in (-1, 0, 1, 2):
+        d = idx + k
+        inside = (d >= max(d_begin, 0)) & (d < min(d_begin + Dl, num_planes))
+        local = np.clip(d - d_begin, 0, Dl - 1)
+        val = np.exp(np.take_along_axis(x, local[:, None], axis=1)[:, 0] - merged_m, dtype=np.float32)
+        out = out + np.where(inside, val, F32(0.0))
+    return (out / merged_Z).astype(np.float32)

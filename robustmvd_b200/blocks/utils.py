@@ -104,3 +104,39 @@ def entropy(volume, dim, keepdim=False):
                                           _lib.ptr(eidx), None, _lib.ptr(ent), _lib.stream_ptr())
     _lib.check(st, "rmvd_soft_argmin_fwd")
     return ent.unsqueeze(1) if keepdim else ent
+
+
+# ---------------------------------------------------------------------------------------------------------
+# depth-slab softargmax: the three local steps of the multi-GPU regression
+# ---------------------------------------------------------------------------------------------------------
+def softargmax_partial(cost_slab, depth_slab, d_begin):
+    """Online-softmax partials of a slab ``cost_slab [B,Dl,h,w]`` holding planes ``[d_begin, d_begin + Dl)``:
+    ``[4,B,h,w] = (m, Z = sum exp(x-m), A = sum exp(x-m)*depth, I = sum exp(x-m)*index)``."""
+    cost_slab, depth_slab = _f32c(cost_slab), _f32c(depth_slab)
+    B, Dl, h, w = cost_slab.shape
+    out = torch.empty((4, B, h, w), dtype=torch.float32, device=cost_slab.device)
+    st = _lib.load().rmvd_softargmax_partial(_lib.ptr(cost_slab), _lib.ptr(depth_slab), B, Dl, h, w, int(d_begin),
+                                             _lib.ptr(out), _lib.stream_ptr())
+    _lib.check(st, "rmvd_softargmax_partial")
+    return out
+
+
+def softargmax_combine(partials):
+    """Merge gathered partials ``[G,4,B,h,w]`` -> ``[4,B,h,w] = (m, Z, depth, expected index)``."""
+    partials = _f32c(partials)
+    G, _, B, h, w = partials.shape
+    out = torch.empty((4, B, h, w), dtype=torch.float32, device=partials.device)
+    st = _lib.load().rmvd_softargmax_combine(_lib.ptr(partials), G, B, h, w, _lib.ptr(out), _lib.stream_ptr())
+    _lib.check(st, "rmvd_softargmax_combine")
+    return out
+
+
+def softargmax_confidence(cost_slab, merged, D, d_begin):
+    """This slab's share of the 4-bin confidence around the global index (mvsnet.py:143-158): ``[B,h,w]``."""
+    cost_slab, merged = _f32c(cost_slab), _f32c(merged)
+    B, Dl, h, w = cost_slab.shape
+    out = torch.empty((B, h, w), dtype=torch.float32, device=cost_slab.device)
+    st = _lib.load().rmvd_softargmax_confidence(_lib.ptr(cost_slab), _lib.ptr(merged), B, Dl, h, w, int(D),
+                                                int(d_begin), _lib.ptr(out), _lib.stream_ptr())
+    _lib.check(st, "rmvd_softargmax_confidence")
+    return out
