@@ -1,0 +1,99 @@
+"""Per-kernel timing of every entry point of the path at the BASELINE.json shapes (1 GPU), against the HBM roofline.
+
+    python tools/bench_kernels.py [--reps 20] [--only NAME]
+
+Each kernel is timed with CUDA events on the launching stream, one event pair per repetition, with a 256 MB scratch
+write between repetitions so that nothing is served from the 126 MB L2 (cold = `ms_cold`; `ms_warm` = back-to-back
+without the flush).  `frac` = algorithmic bytes / ms_cold / MEASURED_PEAKS.json hbm_gbs.  One JSON line per kernel.
+"""
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from robustmvd_b200 import synthetic as syn  # noqa: E402
+from robustmvd_b200.blocks import utils as bu  # noqa: E402
+from robustmvd_b200.blocks.planesweep_corr import PlanesweepCorrelation  # noqa: E402
+
+cu = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
+
+
+def time_fn(fn, reps, flush):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    cold = []
+    for _ in range(reps):
+        flush.fill_(1)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        cold.append(a.elapsed_time(b))
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return float(np.mean(cold)), float(np.min(cold)), a.elapsed_time(b) / reps
+
+
+def psweep_case(cfg, V, frames, S=None):
+    S = S or cfg["S"]
+    inp = syn.planesweep_inputs(cfg["h"], cfg["w"], cfg["C"], V, n=frames)
+    kw = dict(feat_key=cu(inp["feat_key"]), intrinsics_key=cu(inp["intrinsics_key"]),
+              feat_sources=[cu(f) for f in inp["feat_sources"]], source_to_key_transforms=[cu(t) for t in inp["transforms"]],
+              num_sampling_points=S, min_depth=cfg["min_depth"], max_depth=cfg["max_depth"])
+    P = cfg["h"] * cfg["w"]
+    nbytes = 4 * frames * cfg["C"] * P * (1 + V) + 8 * frames * V * S * P
+    return kw, nbytes, frames * V * S * P
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--reps", type=int, default=20)
+    ap.add_argument("--only", default=None)
+    args = ap.parse_args()
+    peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) \
+        else {"hbm_gbs": 6650.0}
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    jobs = []
+
+    def add(name, fn, nbytes, units, unit_name):
+        if args.only is None or args.only in name:
+            jobs.append((name, fn, nbytes, units, unit_name))
+
+    blk = PlanesweepCorrelation()
+    for label, cfg, V, frames in (("cfg2_kitti_1frame", syn.CFG2, 2, 1), ("cfg2_kitti_8frames", syn.CFG2, 2, 8),
+                                  ("cfg4_eth3d_1frame_v2", syn.CFG4, 2, 1), ("cfg4_eth3d_1frame_v10", syn.CFG4, 10, 1)):
+        kw, nb, vox = psweep_case(cfg, V, frames)
+        add(f"psweep_corr_{label}", (lambda kw=kw: blk(**kw)), nb, vox, "voxels")
+    c3 = syn.CFG3
+    m = syn.mvs_inputs(c3["h"], c3["w"], c3["C"], c3["V"], c3["D"])
+    feats, proj, depth, cost = cu(m["feats"]), cu(m["proj"]), cu(m["depth"]), cu(m["cost"])
+    P3 = c3["h"] * c3["w"]
+    add("mvs_variance_cfg3", lambda: bu.mvs_variance_volume(feats, proj, depth),
+        4 * c3["C"] * P3 * c3["V"] + 4 * c3["C"] * c3["D"] * P3, c3["D"] * P3, "voxels")
+    add("mvs_regress_cfg3", lambda: bu.mvs_regress(cost, depth), 4 * c3["D"] * P3 + 8 * P3, c3["D"] * P3, "voxels")
+    add("homo_warp_cfg3", lambda: bu.homo_warp(feats[:, 1], proj[:, 1], proj[:, 0], depth),
+        4 * c3["C"] * P3 + 4 * c3["C"] * c3["D"] * P3, c3["D"] * P3, "voxels")
+    add("soft_argmin_cfg3", lambda: bu.soft_argmin(cost, 1), 8 * c3["D"] * P3, c3["D"] * P3, "voxels")
+    wblk = PlanesweepCorrelation(warp_only=True, normalize=False)
+    kww, _, _ = psweep_case(syn.CFG2, 1, 1, S=64)
+    add("psweep_warp_only_cfg2_S64", lambda: wblk(**kww), 4 * 256 * 7680 + 4 * 64 * 257 * 7680, 64 * 7680, "voxels")
+    for name, fn, nbytes, units, unit_name in jobs:
+        cold, best, warm = time_fn(fn, args.reps, flush)
+        print(json.dumps({"kernel": name, "ms_cold": cold, "ms_cold_min": best, "ms_warm": warm, "algorithmic_bytes": nbytes,
+                          "achieved_gbs": nbytes / cold / 1e6, "frac_of_measured_hbm": nbytes / cold / 1e6 / peaks["hbm_gbs"],
+                          f"{unit_name}_per_s": units / (cold * 1e-3)}), flush=True)
+
+
+if __name__ == "__main__":
+    main()
