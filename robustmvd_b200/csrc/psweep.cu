@@ -390,17 +390,30 @@ extern "C" int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* f
   if (s_begin == s_end) return RMVD_OK;
   cudaStream_t st = (cudaStream_t)stream;
 
-  // kernel choice: the banded-GEMM kernel whenever the shape qualifies (C % 32 == 0, source map <= 65536 texels);
-  // RMVD_PSWEEP_KERNEL=direct forces the general direct kernel (A/B measurements only).
+  // kernel choice: tcgen05 kernel (C % 32 == 0, per-plane hypotheses) > banded fp32 kernel (C % 32 == 0, source map
+  // <= 65536 texels) > general direct kernel.  RMVD_PSWEEP_KERNEL=tc|band|direct restricts the choice (A/B runs only).
   const char* force = getenv("RMVD_PSWEEP_KERNEL");
-  bool band = (C % 32 == 0) && !(force && strcmp(force, "direct") == 0);
+  const bool allow_tc = !force || strcmp(force, "tc") == 0;
+  const bool allow_band = !force || strcmp(force, "band") == 0;
+  bool band = (C % 32 == 0) && allow_band;
   for (int v = 0; v < V; ++v) band = band && ((long long)hs[v] * ws[v] <= 65536);
+  bool tc = allow_tc;
+  {
+    PsweepArgs T{};
+    T.C = C;
+    for (int k = 0; k < 4; ++k) T.ist[k] = inv_stride[k];
+    tc = tc && psweep_tc_eligible(T, 0);
+  }
 
   char* wsp = (char*)workspace;
   float* key_nhwc = (float*)wsp;
   wsp += (((size_t)N * C * h * w * sizeof(float)) + 255) / 256 * 256;
-  if (band) {
-    int rc = repack(feat_key, key_nhwc, N, C, h * w, normalize_mode == RMVD_NORM_BEFORE, st);
+  const int l2 = normalize_mode == RMVD_NORM_BEFORE;
+  if (tc) {
+    int rc = repack_split(feat_key, key_nhwc, N, C, h * w, l2, st);
+    if (rc) return rc;
+  } else if (band) {
+    int rc = repack(feat_key, key_nhwc, N, C, h * w, l2, st);
     if (rc) return rc;
   }
   for (int v0 = 0; v0 < V; v0 += kMaxViews) {
@@ -414,7 +427,8 @@ extern "C" int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* f
       const int v = v0 + j;
       float* dst = (float*)wsp;
       wsp += (((size_t)N * C * hs[v] * ws[v] * sizeof(float)) + 255) / 256 * 256;
-      int rc = repack(feat_src[v], dst, N, C, hs[v] * ws[v], normalize_mode == RMVD_NORM_BEFORE, st);
+      int rc = tc ? repack_split(feat_src[v], dst, N, C, hs[v] * ws[v], l2, st)
+                  : repack(feat_src[v], dst, N, C, hs[v] * ws[v], l2, st);
       if (rc) return rc;
       A.src[j] = dst;
       A.Ks[j] = intrinsics_src[v];
@@ -425,7 +439,8 @@ extern "C" int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* f
     A.N = N; A.C = C; A.h = h; A.w = w; A.S = S; A.s_begin = s_begin; A.s_end = s_end;
     A.norm = normalize_mode; A.out_S = out_S; A.out_s0 = out_s0; A.v0 = v0;
     A.corr = corr; A.mask = mask; A.dbg_ix0 = dbg_ix0; A.dbg_iy0 = dbg_iy0; A.dbg_geom = dbg_geom;
-    int rc = band ? launch_psweep_band(A, key_nhwc, nv, st) : dispatch_corr<false>(A, nv, st);
+    int rc = tc ? launch_psweep_tc(A, key_nhwc, nv, st)
+                : band ? launch_psweep_band(A, key_nhwc, nv, st) : dispatch_corr<false>(A, nv, st);
     if (rc) return rc;
   }
   return RMVD_OK;
