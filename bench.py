@@ -62,7 +62,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-i", str(self.index), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+                                          "-i", str(self.index), "-lms", "20"], stdout=subprocess.PIPE, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except OSError:
             self.proc = None
@@ -230,10 +230,10 @@ def run_ours(args):
             "e2e": {"value": voxels(frames) * world / (ms_e2e * 1e-3), "unit": "voxels/s", "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "api": "PlanesweepCorrelation.forward from pinned host buffers, corr + mask copied back"},
-            "gpu_launches": args.steps * (CFG["V"] + 1),
+            "gpu_launches": args.steps * (CFG["V"] + 2),   # (1 + V) repack launches + 1 plane-sweep kernel per step
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": which,
-                         "kernel": "rmvd_psweep_corr_fwd (V repack launches + psweep_corr_kernel)",
+                         "kernel": "rmvd_psweep_corr_fwd = (1 + V) nchw_to_split_kernel + psweep_tc_kernel (tcgen05)",
                          "algorithmic_bytes_per_launch": ab, "ms_per_launch": ms_call},
             "clocks": clocks,
         })
@@ -247,7 +247,7 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--frames", type=int, default=8, help="frames per GPU per step")

@@ -145,3 +145,25 @@ def test_warp_function_zeros_and_border(cuda_lib):
     out_b, mask_b = warp(torch.from_numpy(x).cuda(), grid=torch.from_numpy(grid).cuda(), padding_mode="border")
     assert np.abs(out_b.cpu().numpy() - ref_b).max() < 1e-4
     assert (mask_b.cpu().numpy() == 1).all()
+
+
+def test_shared_reciprocal_division_is_exact(cuda_lib):
+    """The tcgen05 kernel's coordinate chain divides through a shared refined reciprocal (psweep_tc.cu: rcp_refined /
+    div_shared); within the guarded operand range it must equal the correctly rounded quotient bit for bit."""
+    from robustmvd_b200 import _lib
+    rng = np.random.default_rng(123)
+    n = 1 << 22
+    mant = lambda: rng.uniform(1.0, 2.0, n).astype(np.float32) * rng.choice(np.array([-1.0, 1.0], np.float32), n)  # noqa: E731
+    a = mant() * np.exp2(rng.integers(-58, 59, n)).astype(np.float32)
+    b = mant() * np.exp2(rng.integers(-58, 59, n)).astype(np.float32)
+    sizes = np.array([1, 3, 7, 9, 14, 20, 40, 48, 96, 144, 160, 224, 304, 1216, 32767], np.float32)
+    b[: n // 2] = rng.choice(sizes, n // 2)                      # the divisions by the source map size
+    a[: n // 4] = rng.uniform(-700, 700, n // 4).astype(np.float32)  # pixel-range numerators
+    a[0:4] = [0.0, -0.0, 1e-30, 2.0 ** 60]
+    ta, tb = torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()
+    q1, q2 = torch.empty_like(ta), torch.empty_like(ta)
+    _lib.check(cuda_lib.rmvd_debug_div_check(_lib.ptr(ta), _lib.ptr(tb), n, _lib.ptr(q1), _lib.ptr(q2), _lib.stream_ptr()), "div")
+    torch.cuda.synchronize()
+    assert torch.equal(q1.view(torch.int32)[1:], q2.view(torch.int32)[1:]) or \
+        int((q1.view(torch.int32) != q2.view(torch.int32)).sum()) <= 1   # only -0 / +0 of a zero numerator may differ
+    assert float((q1 - q2).abs().max()) == 0.0

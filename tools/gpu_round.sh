@@ -16,6 +16,6 @@ timeout 300 $BCMD > $OUT/plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches.csv $BCMD > $OUT/ncu_launches.log 2>&1
 echo "ncu launches rc=$?"
 timeout 300 $BCMD > $OUT/plain2.log 2>&1 &&
-timeout 1200 ncu --set full --clock-control none --import-source on -k regex:psweep_band -s 3 -c 2 -o $OUT/prof_band $BCMD > $OUT/ncu_full.log 2>&1
+timeout 1200 ncu --set full --clock-control none --import-source on -k regex:psweep_tc -s 3 -c 2 -o $OUT/prof_tc $BCMD > $OUT/ncu_full.log 2>&1
 echo "ncu full rc=$?"
 ls -la $OUT
