@@ -7,6 +7,8 @@
 // Data layout in HBM: features [B,Vt,C,h,w] and cost volumes [B,D,h,w] exactly as the reference holds them;
 // the variance volume [B,C,D,h,w] is written once with 128-byte coalesced rows along w; the warped source
 // volumes (1.67 GB per view at DTU size) are never materialised.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace rmvd {
@@ -124,6 +126,134 @@ __global__ void __launch_bounds__(256) mvs_variance_kernel(const float* __restri
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Fused variance volume, staged form.  CTA = 64 consecutive key pixels of one row x 4 consecutive depth planes,
+// thread = one voxel x kCh channels (sum and sum of squares stay in registers across the views).  Per source view:
+//   1. every thread locates its sample once with the exact chain (homo_coord + bilinear_setup);
+//   2. the CTA reduces the bounding rectangle of all corners that carry weight -- exact, so nothing can fall outside;
+//   3. the rectangle of all kCh channels is copied NCHW -> shared memory with coalesced row segments
+//      ([channel][kVarCap] floats, row pitch = rectangle width), so each source element leaves L2 once per CTA
+//      instead of once per voxel that touches it;
+//   4. the 4 corners x kCh channels are read from shared memory: adjacent lanes read adjacent words.
+// A view whose rectangle does not fit (strong rotation between the views) is gathered straight from global memory.
+// Bound: 16 shared-memory words per output word -> at 128 B/clk/SM about a third of the HBM write roofline.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kVarPx = 64;       // key pixels per CTA (one row segment)
+constexpr int kVarDB = 4;        // depth planes per CTA
+constexpr int kVarCap = 768;     // staged floats per channel (rectangle area limit)
+constexpr int kVarThreads = kVarPx * kVarDB;
+
+template <int kCh>
+__global__ void __launch_bounds__(kVarThreads, 2) mvs_variance_tile_kernel(
+    const float* __restrict__ feats, const float* __restrict__ proj, const float* __restrict__ depths, int B, int Vt, int C,
+    int h, int w, int D, int d_begin, int d_end, float* __restrict__ variance, int out_D, int out_d0, int tiles_x, int ncg) {
+  extern __shared__ __align__(16) float s_tile[];   // [kCh][kVarCap]
+  __shared__ float s_M[kMaxMvsViews][12];
+  __shared__ int4 s_red[kVarThreads / 32];
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int b = blockIdx.z;
+  const int P = h * w;
+  const int yi = blockIdx.x / tiles_x, bx = blockIdx.x - yi * tiles_x;
+  const int dblk = blockIdx.y / ncg, cg = blockIdx.y - dblk * ncg;
+  const int c0 = cg * kCh;
+  for (int e = t; e < (Vt - 1) * 12; e += kVarThreads) {
+    const int v = 1 + e / 12, i = (e % 12) / 4, j = e % 4;
+    s_M[v - 1][i * 4 + j] = matmul4_elem(proj + ((size_t)b * Vt + v) * 16, proj + ((size_t)b * Vt) * 16, i, j);
+  }
+  __syncthreads();
+  const int xi = bx * kVarPx + (t & (kVarPx - 1));
+  const int dl = dblk * kVarDB + (t / kVarPx);
+  const int d = d_begin + dl;
+  const bool active = (xi < w) && (d < d_end);
+  const int p = yi * w + min(xi, w - 1);
+  const float depth = depths[(size_t)b * D + min(d, D - 1)];
+
+  float sum[kCh], sq[kCh];
+  {
+    const float* ref = feats + ((size_t)b * Vt) * C * P + p;
+#pragma unroll
+    for (int k = 0; k < kCh; ++k) {
+      const float r = (active && c0 + k < C) ? __ldg(ref + (size_t)(c0 + k) * P) : 0.f;
+      sum[k] = r;               // volume_sum = ref_volume (:125)
+      sq[k] = r * r;            // ref_volume ** 2 (:126)
+    }
+  }
+  for (int v = 1; v < Vt; ++v) {
+    float ix, iy;
+    homo_coord(s_M[v - 1], xi, yi, depth, h, w, ix, iy);
+    const Bilinear bl = bilinear_setup(ix, iy, h, w);
+    const int x0 = isnan(bl.x0f) ? -2 : sat_index(bl.x0f, w), y0 = isnan(bl.y0f) ? -2 : sat_index(bl.y0f, h);
+    const bool left = (bl.nw != 0.f) || (bl.sw != 0.f), right = (bl.ne != 0.f) || (bl.se != 0.f);
+    const bool top = (bl.nw != 0.f) || (bl.ne != 0.f), bottom = (bl.sw != 0.f) || (bl.se != 0.f);
+    const bool needed = active && (left || right);
+    // bounding rectangle of the corners that carry weight (a non-zero weight implies the corner is inside the map)
+    int xlo = needed ? (left ? x0 : x0 + 1) : 0x7fffffff, xhi = needed ? (right ? x0 + 1 : x0) : -0x7fffffff;
+    int ylo = needed ? (top ? y0 : y0 + 1) : 0x7fffffff, yhi = needed ? (bottom ? y0 + 1 : y0) : -0x7fffffff;
+    xlo = __reduce_min_sync(kFullMask, xlo); xhi = __reduce_max_sync(kFullMask, xhi);
+    ylo = __reduce_min_sync(kFullMask, ylo); yhi = __reduce_max_sync(kFullMask, yhi);
+    if (lane == 0) s_red[warp] = make_int4(xlo, xhi, ylo, yhi);
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < kVarThreads / 32; ++k) {
+      const int4 r = s_red[k];
+      xlo = min(xlo, r.x); xhi = max(xhi, r.y); ylo = min(ylo, r.z); yhi = max(yhi, r.w);
+    }
+    const float* src = feats + (((size_t)b * Vt + v) * C + c0) * P;
+    if (xlo <= xhi) {                                       // uniform: someone samples inside the map
+      const int rw = xhi - xlo + 1, rh = yhi - ylo + 1;
+      if (rw * rh <= kVarCap) {                             // uniform
+        for (int c = warp; c < kCh; c += kVarThreads / 32) {
+          const bool c_ok = c0 + c < C;
+          const float* g = src + (size_t)c * P + (size_t)ylo * w + xlo;
+          float* s = s_tile + c * kVarCap;
+          for (int r = 0; r < rh; ++r)
+            for (int xx = lane; xx < rw; xx += 32) s[r * rw + xx] = c_ok ? __ldg(g + (size_t)r * w + xx) : 0.f;
+        }
+        __syncthreads();
+        if (needed) {
+          // corners without weight are clamped into the rectangle: they read staged (finite) data and multiply it by 0
+          const int cx0 = min(max(x0, xlo), xhi) - xlo, cx1 = min(max(x0 + 1, xlo), xhi) - xlo;
+          const int cy0 = (min(max(y0, ylo), yhi) - ylo) * rw, cy1 = (min(max(y0 + 1, ylo), yhi) - ylo) * rw;
+          const float* q_nw = s_tile + cy0 + cx0;
+          const float* q_ne = s_tile + cy0 + cx1;
+          const float* q_sw = s_tile + cy1 + cx0;
+          const float* q_se = s_tile + cy1 + cx1;
+#pragma unroll
+          for (int k = 0; k < kCh; ++k) {
+            float val = bl.nw * q_nw[k * kVarCap];
+            val = fmaf(bl.ne, q_ne[k * kVarCap], val);
+            val = fmaf(bl.sw, q_sw[k * kVarCap], val);
+            val = fmaf(bl.se, q_se[k * kVarCap], val);
+            sum[k] += val;
+            sq[k] = fmaf(val, val, sq[k]);
+          }
+        }
+      } else if (needed) {
+        const Gather g = make_gather(ix, iy, h, w);
+#pragma unroll
+        for (int k = 0; k < kCh; ++k) {
+          if (c0 + k < C) {
+            const float val = gather_val(src + (size_t)k * P, g);
+            sum[k] += val;
+            sq[k] = fmaf(val, val, sq[k]);
+          }
+        }
+      }
+    }
+    __syncthreads();                                        // s_red and the staged rectangle are reused by the next view
+  }
+  if (!active) return;
+  const float Vf = (float)Vt;
+  float* out = variance + (((size_t)b * C + c0) * out_D + out_d0 + dl) * P + p;
+#pragma unroll
+  for (int k = 0; k < kCh; ++k) {
+    if (c0 + k < C) {
+      const float mean = fdiv(sum[k], Vf);
+      out[(size_t)k * out_D * P] = fsub(fdiv(sq[k], Vf), fmul(mean, mean));  // :135
+    }
+  }
+}
+
 // homo_warp, materialising (blocks/utils.py:222-268): thread = voxel (d,y,x), loops channels.
 __global__ void __launch_bounds__(256) homo_warp_kernel(const float* __restrict__ src_feat, const float* __restrict__ src_proj,
                                                         const float* __restrict__ ref_proj_inv, const float* __restrict__ depths,
@@ -202,13 +332,25 @@ __global__ void __launch_bounds__(kRegWarps * 32) mvs_regress_kernel(const float
   SoftState st{-INFINITY, 0.f, 0.f, 0.f};
   if (act) {
     int d = g;
-    for (; d + 3 * kRegWarps < D; d += 4 * kRegWarps) {  // four independent loads in flight
-      const float x0 = __ldg(x + (size_t)d * P), x1 = __ldg(x + (size_t)(d + kRegWarps) * P);
-      const float x2 = __ldg(x + (size_t)(d + 2 * kRegWarps) * P), x3 = __ldg(x + (size_t)(d + 3 * kRegWarps) * P);
-      soft_push(st, x0, __ldg(dv + d), (float)(index0 + d));
-      soft_push(st, x1, __ldg(dv + d + kRegWarps), (float)(index0 + d + kRegWarps));
-      soft_push(st, x2, __ldg(dv + d + 2 * kRegWarps), (float)(index0 + d + 2 * kRegWarps));
-      soft_push(st, x3, __ldg(dv + d + 3 * kRegWarps), (float)(index0 + d + 3 * kRegWarps));
+    constexpr int kB = 8;                                  // loads in flight per thread; one rescale per batch
+    for (; d + (kB - 1) * kRegWarps < D; d += kB * kRegWarps) {
+      float xv[kB], dz[kB];
+#pragma unroll
+      for (int k = 0; k < kB; ++k) xv[k] = __ldg(x + (size_t)(d + k * kRegWarps) * P);
+#pragma unroll
+      for (int k = 0; k < kB; ++k) dz[k] = __ldg(dv + d + k * kRegWarps);
+      float mx = st.m;
+#pragma unroll
+      for (int k = 0; k < kB; ++k) mx = fmaxf(mx, xv[k]);
+      const float r = __expf(st.m - mx);                   // exp(-inf) = 0 on the first batch; nan-free because mx > -inf
+      st.Z *= r; st.A *= r; st.I *= r; st.m = mx;
+#pragma unroll
+      for (int k = 0; k < kB; ++k) {
+        const float e = __expf(xv[k] - mx);
+        st.Z += e;
+        st.A = fmaf(e, dz[k], st.A);
+        st.I = fmaf(e, (float)(index0 + d + k * kRegWarps), st.I);
+      }
     }
     for (; d < D; d += kRegWarps) soft_push(st, __ldg(x + (size_t)d * P), __ldg(dv + d), (float)(index0 + d));
   }
@@ -327,12 +469,29 @@ extern "C" int rmvd_mvs_variance_fwd(const float* feats, const float* proj, cons
   if (d_begin < 0 || d_end > D || d_begin > d_end || out_d0 < 0 || out_d0 + (d_end - d_begin) > out_D)
     return RMVD_E_RANGE;
   if (d_begin == d_end) return RMVD_OK;
-  const long long tot = (long long)(d_end - d_begin) * h * w;
-  constexpr int kCh = 8;
-  dim3 grid((unsigned)((tot + 255) / 256), (C + kCh - 1) / kCh, B);
-  mvs_variance_kernel<kCh><<<grid, 256, 0, (cudaStream_t)stream>>>(feats, proj, depths, B, Vt, C, h, w, D, d_begin,
-                                                                    d_end, variance, out_D, out_d0);
-  return (int)cudaGetLastError();
+  static const bool direct = getenv("RMVD_MVS_VARIANCE_DIRECT") != nullptr;   // A/B switch: the un-staged kernel
+  if (direct) {
+    const long long tot = (long long)(d_end - d_begin) * h * w;
+    constexpr int kCh = 8;
+    dim3 grid((unsigned)((tot + 255) / 256), (C + kCh - 1) / kCh, B);
+    mvs_variance_kernel<kCh><<<grid, 256, 0, (cudaStream_t)stream>>>(feats, proj, depths, B, Vt, C, h, w, D, d_begin,
+                                                                      d_end, variance, out_D, out_d0);
+    return (int)cudaGetLastError();
+  }
+  const int tiles_x = (w + kVarPx - 1) / kVarPx;
+  const int ndb = (d_end - d_begin + kVarDB - 1) / kVarDB;
+  auto launch = [&](auto kernel, int kCh) -> int {
+    const int ncg = (C + kCh - 1) / kCh;
+    if ((long long)ndb * ncg > 65535) return RMVD_E_SHAPE;
+    const size_t smem = sizeof(float) * kCh * kVarCap;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    dim3 grid((unsigned)(tiles_x * h), (unsigned)(ndb * ncg), B);
+    kernel<<<grid, kVarThreads, smem, (cudaStream_t)stream>>>(feats, proj, depths, B, Vt, C, h, w, D, d_begin, d_end, variance,
+                                                              out_D, out_d0, tiles_x, ncg);
+    return (int)cudaGetLastError();
+  };
+  return (C > 16) ? launch(mvs_variance_tile_kernel<32>, 32) : launch(mvs_variance_tile_kernel<16>, 16);
 }
 
 extern "C" int rmvd_homo_warp_fwd(const float* src_feat, const float* src_proj, const float* ref_proj_inv,
