@@ -146,7 +146,7 @@ constexpr int kVarThreads = kVarPx * kVarDB;
 template <int kCh>
 __global__ void __launch_bounds__(kVarThreads, 2) mvs_variance_tile_kernel(
     const float* __restrict__ feats, const float* __restrict__ proj, const float* __restrict__ depths, int B, int Vt, int C,
-    int h, int w, int D, int d_begin, int d_end, float* __restrict__ variance, int out_D, int out_d0, int tiles_x, int ncg) {
+    int h, int w, int D, int d_begin, int d_end, float* __restrict__ variance, int out_D, int out_d0, int tiles_x, int ncg, int vec16) {
   extern __shared__ __align__(16) float s_tile[];   // [kCh][kVarCap]
   __shared__ float s_M[kMaxMvsViews][12];
   __shared__ int4 s_red[kVarThreads / 32];
@@ -200,19 +200,46 @@ __global__ void __launch_bounds__(kVarThreads, 2) mvs_variance_tile_kernel(
     }
     const float* src = feats + (((size_t)b * Vt + v) * C + c0) * P;
     if (xlo <= xhi) {                                       // uniform: someone samples inside the map
-      const int rw = xhi - xlo + 1, rh = yhi - ylo + 1;
+      // staged rectangle: columns [xo, xo + rw), rows [ylo, ylo + rh); with 16-byte copies the columns are widened to
+      // multiples of 4 (w % 4 == 0 and a 16-byte aligned base keep every row segment aligned and inside its row)
+      const int xo = vec16 ? (xlo & ~3) : xlo;
+      const int rw = vec16 ? ((xhi - xo + 4) & ~3) : (xhi - xo + 1), rh = yhi - ylo + 1;
       if (rw * rh <= kVarCap) {                             // uniform
-        for (int c = warp; c < kCh; c += kVarThreads / 32) {
-          const bool c_ok = c0 + c < C;
-          const float* g = src + (size_t)c * P + (size_t)ylo * w + xlo;
-          float* s = s_tile + c * kVarCap;
-          for (int r = 0; r < rh; ++r)
-            for (int xx = lane; xx < rw; xx += 32) s[r * rw + xx] = c_ok ? __ldg(g + (size_t)r * w + xx) : 0.f;
+        const float* g0 = src + (size_t)ylo * w + xo;
+        if (vec16) {
+          const int cw = rw >> 2, nchunk = rh * cw;         // 16-byte chunks per row / per channel
+          for (int q = t & 63; q < nchunk; q += 64) {
+            const int r = q / cw, xc = q - r * cw;
+            const float* g = g0 + (size_t)r * w + 4 * xc;
+            const unsigned sdst = (unsigned)__cvta_generic_to_shared(s_tile + r * rw + 4 * xc);
+#pragma unroll
+            for (int c = t >> 6; c < kCh; c += kVarThreads / 64) {
+              if (c0 + c < C)   // asynchronous copies: the whole rectangle is in flight at once
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sdst + c * (kVarCap * 4)), "l"(g + (size_t)c * P));
+              else
+                *reinterpret_cast<float4*>(s_tile + c * kVarCap + r * rw + 4 * xc) = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+          }
+        } else {
+          const int area = rh * rw;
+          for (int e = t & 127; e < area; e += 128) {
+            const int r = e / rw, xx = e - r * rw;
+            const float* g = g0 + (size_t)r * w + xx;
+            const unsigned sdst = (unsigned)__cvta_generic_to_shared(s_tile + e);
+#pragma unroll 4
+            for (int c = t >> 7; c < kCh; c += kVarThreads / 128) {
+              if (c0 + c < C)
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(sdst + c * (kVarCap * 4)), "l"(g + (size_t)c * P));
+              else
+                s_tile[c * kVarCap + e] = 0.f;
+            }
+          }
         }
+        asm volatile("cp.async.wait_all;\n" ::: "memory");
         __syncthreads();
         if (needed) {
           // corners without weight are clamped into the rectangle: they read staged (finite) data and multiply it by 0
-          const int cx0 = min(max(x0, xlo), xhi) - xlo, cx1 = min(max(x0 + 1, xlo), xhi) - xlo;
+          const int cx0 = min(max(x0, xlo), xhi) - xo, cx1 = min(max(x0 + 1, xlo), xhi) - xo;
           const int cy0 = (min(max(y0, ylo), yhi) - ylo) * rw, cy1 = (min(max(y0 + 1, ylo), yhi) - ylo) * rw;
           const float* q_nw = s_tile + cy0 + cx0;
           const float* q_ne = s_tile + cy0 + cx1;
@@ -243,13 +270,13 @@ __global__ void __launch_bounds__(kVarThreads, 2) mvs_variance_tile_kernel(
     __syncthreads();                                        // s_red and the staged rectangle are reused by the next view
   }
   if (!active) return;
-  const float Vf = (float)Vt;
+  const float inv_V = 1.0f / (float)Vt;      // x / V as x * (1 / V): within 1 ulp, far inside the 1e-4 volume tolerance
   float* out = variance + (((size_t)b * C + c0) * out_D + out_d0 + dl) * P + p;
 #pragma unroll
   for (int k = 0; k < kCh; ++k) {
     if (c0 + k < C) {
-      const float mean = fdiv(sum[k], Vf);
-      out[(size_t)k * out_D * P] = fsub(fdiv(sq[k], Vf), fmul(mean, mean));  // :135
+      const float mean = sum[k] * inv_V;
+      out[(size_t)k * out_D * P] = fsub(sq[k] * inv_V, fmul(mean, mean));  // :135
     }
   }
 }
@@ -487,8 +514,9 @@ extern "C" int rmvd_mvs_variance_fwd(const float* feats, const float* proj, cons
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     dim3 grid((unsigned)(tiles_x * h), (unsigned)(ndb * ncg), B);
+    const int vec16 = (w % 4 == 0) && ((uintptr_t)feats % 16 == 0);
     kernel<<<grid, kVarThreads, smem, (cudaStream_t)stream>>>(feats, proj, depths, B, Vt, C, h, w, D, d_begin, d_end, variance,
-                                                              out_D, out_d0, tiles_x, ncg);
+                                                              out_D, out_d0, tiles_x, ncg, vec16);
     return (int)cudaGetLastError();
   };
   return (C > 16) ? launch(mvs_variance_tile_kernel<32>, 32) : launch(mvs_variance_tile_kernel<16>, 16);

@@ -137,3 +137,22 @@ def test_cfg3_full_size_properties(cuda_lib):
     assert np.array_equal(npy(r["depth_index"])[0], k)
     assert np.allclose(npy(r["depth"])[0], inp["depth"][0][k], rtol=1e-6)
     assert np.allclose(npy(r["confidence"]), 1.0, atol=1e-6)
+
+
+@pytest.mark.parametrize("w", [76, 78], ids=["w%4==0 (16-byte staging)", "w%4!=0 (4-byte staging)"])
+def test_variance_rotated_views(cuda_lib, w):
+    """Strong in-plane rotation between the views: the bounding rectangle of a tile's samples exceeds the staged
+    capacity for some tiles (direct gather path) and fits for others; both must agree with the oracle."""
+    from robustmvd_b200.blocks import utils as bu
+    inp = syn.mvs_inputs(56, w, 32, 4, 12, seed=77, fx=90.0)
+    K = np.array([[90.0, 0, w / 2.0, 0], [0, 90.0, 28.0, 0], [0, 0, 1, 0], [0, 0, 0, 1]], np.float64)
+    for v, roll in ((1, 35.0), (2, -80.0), (3, 8.0)):
+        pose = np.eye(4)
+        pose[:3, :3] = syn.rot_z(roll) @ syn.rot_y(2.0 * v)
+        pose[:3, 3] = (0.05 * v, -0.03, 0.01)
+        P = pose.astype(np.float32)
+        P[:3, :4] = (K[:3, :3].astype(np.float32) @ P[:3, :4]).astype(np.float32)
+        inp["proj"][:, v] = P
+    var = npy(bu.mvs_variance_volume(cu(inp["feats"]), cu(inp["proj"]), cu(inp["depth"])))
+    ov = oracle.mvs_variance(inp["feats"], inp["proj"], inp["depth"])
+    assert np.abs(var - ov).max() <= 1e-4 * np.abs(ov).max()
