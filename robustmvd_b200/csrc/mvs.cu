@@ -170,10 +170,11 @@ __global__ void __launch_bounds__(kVarThreads, 2) mvs_variance_tile_kernel(
 
   float sum[kCh], sq[kCh];
   {
-    const float* ref = feats + ((size_t)b * Vt) * C * P + p;
+    const float* ref = feats + (((size_t)b * Vt) * C + c0) * P + p;   // running pointer: one 64-bit add per channel
+    const int nch = active ? min(kCh, C - c0) : 0;
 #pragma unroll
-    for (int k = 0; k < kCh; ++k) {
-      const float r = (active && c0 + k < C) ? __ldg(ref + (size_t)(c0 + k) * P) : 0.f;
+    for (int k = 0; k < kCh; ++k, ref += P) {
+      const float r = (k < nch) ? __ldg(ref) : 0.f;
       sum[k] = r;               // volume_sum = ref_volume (:125)
       sq[k] = r * r;            // ref_volume ** 2 (:126)
     }
@@ -272,11 +273,13 @@ __global__ void __launch_bounds__(kVarThreads, 2) mvs_variance_tile_kernel(
   if (!active) return;
   const float inv_V = 1.0f / (float)Vt;      // x / V as x * (1 / V): within 1 ulp, far inside the 1e-4 volume tolerance
   float* out = variance + (((size_t)b * C + c0) * out_D + out_d0 + dl) * P + p;
+  const size_t cstride = (size_t)out_D * P;
+  const int nch = min(kCh, C - c0);
 #pragma unroll
-  for (int k = 0; k < kCh; ++k) {
-    if (c0 + k < C) {
+  for (int k = 0; k < kCh; ++k, out += cstride) {
+    if (k < nch) {
       const float mean = sum[k] * inv_V;
-      out[(size_t)k * out_D * P] = fsub(sq[k] * inv_V, fmul(mean, mean));  // :135
+      __stcs(out, fsub(sq[k] * inv_V, fmul(mean, mean)));  // :135; streaming store: the volume is written once, never re-read here
     }
   }
 }
