@@ -139,6 +139,7 @@ def run_ours(args):
     import torch.distributed as dist
     from robustmvd_b200 import _lib
     from robustmvd_b200.blocks.planesweep_corr import PlanesweepCorrelation
+    from robustmvd_b200.pipeline import HostPlanesweepPipeline
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -168,14 +169,10 @@ def run_ours(args):
     P = CFG["h"] * CFG["w"]
     out_host = torch.empty((2, CFG["V"], frames, CFG["S"], CFG["h"], CFG["w"]), dtype=torch.float32).pin_memory()
 
-    def step_e2e():
-        k = host["feat_key"].to(dev, non_blocking=True)
-        s = [f.to(dev, non_blocking=True) for f in host["feat_sources"]]
-        corrs, masks, _ = block(feat_key=k, intrinsics_key=Kk, feat_sources=s, source_to_key_transforms=Ts, **KW)
-        for v in range(CFG["V"]):
-            out_host[0, v].copy_(corrs[v], non_blocking=True)
-            out_host[1, v].copy_(masks[v], non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+    pipe = HostPlanesweepPipeline(dev, block, chunk_frames=args.e2e_chunk)
+
+    def step_e2e():   # pinned host features in, corr + mask back in pinned host memory; returns after the last byte landed
+        pipe.run(host["feat_key"], Kk, host["feat_sources"], Ts, out_host[0], out_host[1], **KW)
 
     def barrier():
         torch.cuda.synchronize()
@@ -220,7 +217,10 @@ def run_ours(args):
     if rank == 0:
         peaks, which = measured_peaks()
         ab = algorithmic_bytes(frames)
-        achieved = ab / (ms_call * 1e-3) / 1e9
+        # duration of the launch group: the back-to-back timed region (GPU-bound, no gaps between calls) when the step is the
+        # bare call; the per-call event pairs (which can include host gaps) only when an L2 flush sits between the steps
+        ms_launch = ms_call if flush is not None else ms_step
+        achieved = ab / (ms_launch * 1e-3) / 1e9
         h2d = 4 * frames * CFG["C"] * P * (1 + CFG["V"])
         d2h = 2 * 4 * frames * CFG["V"] * CFG["S"] * P
         line = base_line(args, frames, world)
@@ -229,12 +229,14 @@ def run_ours(args):
             "frames_per_s": frames * world / (ms_step * 1e-3),
             "e2e": {"value": voxels(frames) * world / (ms_e2e * 1e-3), "unit": "voxels/s", "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "api": "PlanesweepCorrelation.forward from pinned host buffers, corr + mask copied back"},
+                    "api": "HostPlanesweepPipeline.run: PlanesweepCorrelation.forward per chunk of %d frames from pinned host "
+                           "buffers, corr + mask copied back; H2D / kernels / D2H of consecutive chunks overlap on 3 streams"
+                           % args.e2e_chunk},
             "gpu_launches": args.steps * (CFG["V"] + 2),   # (1 + V) repack launches + 1 plane-sweep kernel per step
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                         "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": which,
-                         "kernel": "rmvd_psweep_corr_fwd = (1 + V) nchw_to_split_kernel + psweep_tc_kernel (tcgen05)",
-                         "algorithmic_bytes_per_launch": ab, "ms_per_launch": ms_call},
+                         "frac": achieved / peaks["hbm_gbs"], "traffic": ncu_traffic(frames), "peak_source": which,
+                         "kernel": "rmvd_psweep_corr_fwd = (1 + V) nchw_to_split_tile_kernel + psweep_tc_kernel (tcgen05 + TMA)",
+                         "algorithmic_bytes_per_launch": ab, "ms_per_launch": ms_launch, "ms_per_call_event_pairs": ms_call},
             "clocks": clocks,
         })
         if not args.no_cpu_baseline and world == 1:
@@ -242,6 +244,16 @@ def run_ours(args):
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def ncu_traffic(frames):
+    """DRAM bytes (read + write) of one call's kernels from the committed ncu --set full capture (profiles/roofline_traffic.json,
+    written from the capture by hand; bytes are per call of 8 frames), or None when the run does not match the capture."""
+    path = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if not os.path.exists(path):
+        return None
+    t = json.load(open(path))
+    return t["dram_bytes_per_call"] if t.get("frames") == frames else None
 
 
 def main():
@@ -252,6 +264,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--frames", type=int, default=8, help="frames per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-chunk", type=int, default=2, help="frames per chunk of the host pipeline (e2e leg)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
