@@ -169,7 +169,7 @@ def run_ours(args):
     P = CFG["h"] * CFG["w"]
     out_host = torch.empty((2, CFG["V"], frames, CFG["S"], CFG["h"], CFG["w"]), dtype=torch.float32).pin_memory()
 
-    pipe = HostPlanesweepPipeline(dev, block, chunk_frames=args.e2e_chunk)
+    pipe = HostPlanesweepPipeline(dev, block, chunk_frames=[int(c) for c in str(args.e2e_chunk).split(',')])
 
     def step_e2e():   # pinned host features in, corr + mask back in pinned host memory; returns after the last byte landed
         pipe.run(host["feat_key"], Kk, host["feat_sources"], Ts, out_host[0], out_host[1], **KW)
@@ -229,7 +229,7 @@ def run_ours(args):
             "frames_per_s": frames * world / (ms_step * 1e-3),
             "e2e": {"value": voxels(frames) * world / (ms_e2e * 1e-3), "unit": "voxels/s", "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "api": "HostPlanesweepPipeline.run: PlanesweepCorrelation.forward per chunk of %d frames from pinned host "
+                    "api": "HostPlanesweepPipeline.run: PlanesweepCorrelation.forward per chunk of %s frames from pinned host "
                            "buffers, corr + mask copied back; H2D / kernels / D2H of consecutive chunks overlap on 3 streams"
                            % args.e2e_chunk},
             "gpu_launches": args.steps * (CFG["V"] + 2),   # (1 + V) repack launches + 1 plane-sweep kernel per step
@@ -264,7 +264,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--frames", type=int, default=8, help="frames per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--e2e-chunk", type=int, default=2, help="frames per chunk of the host pipeline (e2e leg)")
+    ap.add_argument("--e2e-chunk", default="2", help="frames per chunk of the host pipeline (e2e leg); a,b,c = schedule, last repeats")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

@@ -15,7 +15,9 @@ class HostPlanesweepPipeline:
     def __init__(self, device, block=None, chunk_frames=2):
         self.device = torch.device(device)
         self.block = block if block is not None else PlanesweepCorrelation()
-        self.chunk = int(chunk_frames)
+        # int: equal chunks; sequence: chunk sizes in order, the last one repeating (a small first chunk starts the D2H
+        # stream earlier, which is the longer of the two copy directions)
+        self.chunk = [int(c) for c in chunk_frames] if isinstance(chunk_frames, (list, tuple)) else [int(chunk_frames)]
         self.s_in = torch.cuda.Stream(self.device)
         self.s_cmp = torch.cuda.Stream(self.device)
         self.s_out = torch.cuda.Stream(self.device)
@@ -42,8 +44,12 @@ class HostPlanesweepPipeline:
         for s in (self.s_in, self.s_cmp, self.s_out):
             s.wait_stream(cur)
         keep = []
-        for n0 in range(0, N, self.chunk):
-            n1 = min(N, n0 + self.chunk)
+        bounds, n0 = [], 0
+        while n0 < N:
+            c = self.chunk[min(len(bounds), len(self.chunk) - 1)]
+            bounds.append((n0, min(N, n0 + c)))
+            n0 += c
+        for n0, n1 in bounds:
             ev_in, ev_cmp = torch.cuda.Event(), torch.cuda.Event()
             with torch.cuda.stream(self.s_in):
                 d_key[n0:n1].copy_(host_key[n0:n1], non_blocking=True)
