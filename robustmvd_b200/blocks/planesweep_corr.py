@@ -172,12 +172,16 @@ class TorchCorr(nn.Module):
         return corr, cmask
 
 
+_INVDEPTH_CACHE = {}
+
+
 class PlanesweepCorrelation(nn.Module):
     """planesweep_corr.py:371-521.  ``forward`` returns ``(corrs, masks, sampling_invdepths)`` like the reference.
 
     ``plane_range=(s_begin, s_end)`` (extension, default all planes) restricts the call to a depth slab; outputs
     then hold only those planes.  ``debug=True`` additionally keeps ``self.debug`` with the integer
-    sampling indices and the geometric mask of every view.
+    sampling indices and the geometric mask of every view.  ``out=(corr, mask)`` (extension): caller-provided contiguous
+    float32 device tensors ``[V, N, planes, h, w]`` that receive the correlation outputs instead of fresh allocations.
     """
 
     @torch.no_grad()
@@ -203,11 +207,27 @@ class PlanesweepCorrelation(nn.Module):
             assert sampling_invdepths is None
             assert num_sampling_points is not None
             assert sampling_type is not None
-            sampling_invdepths = compute_sampling_invdepths(min_depth, max_depth, num_sampling_points, sampling_type)
+            # the schedule of a (range, count, type) is a constant: keep its device copy (a fresh pageable H2D copy per call
+            # would block the host on the launching stream and serialise a pipelined caller)
+            if not (isinstance(min_depth, (int, float)) and isinstance(max_depth, (int, float))):   # per-sample ranges
+                return self._as_4d(_to_torch(compute_sampling_invdepths(min_depth, max_depth, num_sampling_points,
+                                                                        sampling_type)).to(device))
+            key = (float(min_depth), float(max_depth), int(num_sampling_points), sampling_type, str(device))
+            cached = _INVDEPTH_CACHE.get(key)
+            if cached is None:
+                cached = self._as_4d(_to_torch(compute_sampling_invdepths(min_depth, max_depth, num_sampling_points,
+                                                                         sampling_type)).to(device))
+                if len(_INVDEPTH_CACHE) >= 16:
+                    _INVDEPTH_CACHE.clear()
+                _INVDEPTH_CACHE[key] = cached
+            return cached.clone()   # device-side copy: the caller owns the returned tensor, like in the reference
         else:
             assert num_sampling_points is None and min_depth is None and max_depth is None
             assert sampling_invdepths is not None
-        sampling_invdepths = _to_torch(sampling_invdepths).to(device)
+        return self._as_4d(_to_torch(sampling_invdepths).to(device))
+
+    @staticmethod
+    def _as_4d(sampling_invdepths):
         assert sampling_invdepths.ndim >= 2  # (N, S) or (N, S, H) or (N, S, H, W)
         while sampling_invdepths.ndim < 4:
             sampling_invdepths = sampling_invdepths.unsqueeze(-1)
@@ -216,7 +236,7 @@ class PlanesweepCorrelation(nn.Module):
     @torch.no_grad()
     def forward(self, feat_key, intrinsics_key, feat_sources, source_to_key_transforms, intrinsics_sources=None,
                 num_sampling_points=None, min_depth=None, max_depth=None, sampling_invdepths=None,
-                sampling_type="linear_invdepth", plane_range=None, debug=False):
+                sampling_type="linear_invdepth", plane_range=None, debug=False, out=None):
         self.reset()
         dev = feat_key.device
         if intrinsics_sources is None:  # :441-442
@@ -243,8 +263,13 @@ class PlanesweepCorrelation(nn.Module):
         if V == 0:
             return self.corrs, self.masks, inv
         if not self.warp_only:
-            corr = torch.empty((V, N, Sl, h, w), dtype=torch.float32, device=dev)
-            mask = torch.empty_like(corr)
+            if out is None:
+                corr = torch.empty((V, N, Sl, h, w), dtype=torch.float32, device=dev)
+                mask = torch.empty_like(corr)
+            else:
+                corr, mask = out
+                for o in (corr, mask):
+                    assert o.shape == (V, N, Sl, h, w) and o.dtype == torch.float32 and o.is_contiguous() and o.device == dev
             dbg = [None, None, None]
             if debug:
                 dbg = [torch.empty((V, N, Sl, h, w), dtype=torch.int32, device=dev) for _ in range(2)]

@@ -5,6 +5,10 @@ The batch is cut into chunks of frames; the H2D copy of chunk i+1, the kernels o
 on three CUDA streams, so the two PCIe directions (full duplex) and the GPU overlap.  Results are the block's own outputs,
 bit for bit: every chunk is one ordinary ``PlanesweepCorrelation.forward`` call (reference signature,
 rmvd/models/blocks/planesweep_corr.py:396-427) on a slice of the batch.
+
+A stream of batches (``run(..., wait=False)`` per batch, ``finish()`` at the end) also overlaps consecutive batches: the
+device-side input buffers are double-buffered, so the H2D copy of batch i+1 runs under the kernels and the D2H copy of batch
+i and the steady-state cost of a batch is the longer of its two PCIe directions.
 """
 import torch
 
@@ -21,29 +25,63 @@ class HostPlanesweepPipeline:
         self.s_in = torch.cuda.Stream(self.device)
         self.s_cmp = torch.cuda.Stream(self.device)
         self.s_out = torch.cuda.Stream(self.device)
-        self._dev_in = None   # persistent device copies of the inputs (allocated on first use, reused by later calls)
+        # persistent device copies of the inputs, two sets used alternately by consecutive calls (allocated on first use)
+        self._dev_in = [None, None]
+        self._cmp_done = [None, None]   # event after the last kernel that read each set
+        self._calls = 0
+        self._done = None               # event after the last D2H copy of the latest call
+        # persistent device outputs: a ring of chunk-sized (corr, mask) pairs, each reusable once its D2H copy has completed
+        self._out_ring = [None] * 4
+        self._chunks = 0
 
-    def _inputs(self, host_key, host_sources):
+    def _inputs(self, host_key, host_sources, slot):
         shapes = (tuple(host_key.shape), tuple(tuple(f.shape) for f in host_sources))
-        if self._dev_in is None or self._dev_in[0] != shapes:
+        if self._dev_in[slot] is None or self._dev_in[slot][0] != shapes:
+            if self._cmp_done[slot] is not None:
+                self._cmp_done[slot].synchronize()      # the old buffers of this set may still be in use
             key = torch.empty(host_key.shape, dtype=torch.float32, device=self.device)
             srcs = [torch.empty(f.shape, dtype=torch.float32, device=self.device) for f in host_sources]
-            self._dev_in = (shapes, key, srcs)
-        return self._dev_in[1], self._dev_in[2]
+            self._dev_in[slot] = (shapes, key, srcs)
+        return self._dev_in[slot][1], self._dev_in[slot][2]
+
+    def _outputs(self, shape):
+        slot = self._chunks % len(self._out_ring)
+        self._chunks += 1
+        e = self._out_ring[slot]
+        if e is None or e[0] != shape:
+            if e is not None:
+                e[3].synchronize()
+            e = [shape, torch.empty(shape, dtype=torch.float32, device=self.device),
+                 torch.empty(shape, dtype=torch.float32, device=self.device), None]
+            self._out_ring[slot] = e
+        elif e[3] is not None:
+            self.s_cmp.wait_event(e[3])                   # the previous contents have been copied out
+        return e
+
+    def finish(self):
+        """Block the host until every batch handed to ``run`` has landed in its host buffers; the current stream is ordered
+        after them as well."""
+        if self._done is not None:
+            torch.cuda.current_stream(self.device).wait_event(self._done)
+            self._done.synchronize()
 
     @torch.no_grad()
-    def run(self, host_key, intrinsics_key, host_sources, source_to_key_transforms, out_corr, out_mask, **kw):
+    def run(self, host_key, intrinsics_key, host_sources, source_to_key_transforms, out_corr, out_mask, wait=True, **kw):
         """``host_key [N,C,h,w]`` and ``host_sources`` (list of ``[N,C,hs,ws]``) are pinned host tensors,
         ``intrinsics_key [N,3,3]`` / ``source_to_key_transforms`` (list of ``[N,4,4]``) device tensors, ``out_corr`` /
         ``out_mask`` pinned host tensors ``[V,N,S,h,w]`` that receive the block's outputs.  ``kw``: the block's sampling
-        arguments (``num_sampling_points, min_depth, max_depth`` ...).  Returns after everything has landed on the host."""
+        arguments (``num_sampling_points, min_depth, max_depth`` ...).  Returns after everything has landed on the host;
+        with ``wait=False`` it returns once the work is queued (the host buffers must stay untouched until ``finish()``)."""
         N = host_key.shape[0]
         V = len(host_sources)
-        d_key, d_src = self._inputs(host_key, host_sources)
+        slot = self._calls & 1
+        self._calls += 1
+        d_key, d_src = self._inputs(host_key, host_sources, slot)
         cur = torch.cuda.current_stream(self.device)
         for s in (self.s_in, self.s_cmp, self.s_out):
             s.wait_stream(cur)
-        keep = []
+        if self._cmp_done[slot] is not None:              # kernels of the call before last read this set of input buffers
+            self.s_in.wait_event(self._cmp_done[slot])
         bounds, n0 = [], 0
         while n0 < N:
             c = self.chunk[min(len(bounds), len(self.chunk) - 1)]
@@ -56,20 +94,29 @@ class HostPlanesweepPipeline:
                 for v in range(V):
                     d_src[v][n0:n1].copy_(host_sources[v][n0:n1], non_blocking=True)
                 ev_in.record(self.s_in)
+            S = kw.get("num_sampling_points")
+            pr = kw.get("plane_range")
+            if S is None:
+                S = kw["sampling_invdepths"].shape[1]
+            planes = S if pr is None else pr[1] - pr[0]
+            ring = self._outputs((V, n1 - n0, planes, host_key.shape[2], host_key.shape[3]))
             with torch.cuda.stream(self.s_cmp):
                 self.s_cmp.wait_event(ev_in)
                 corrs, masks, _ = self.block(feat_key=d_key[n0:n1], intrinsics_key=intrinsics_key[n0:n1],
                                              feat_sources=[f[n0:n1] for f in d_src],
-                                             source_to_key_transforms=[t[n0:n1] for t in source_to_key_transforms], **kw)
+                                             source_to_key_transforms=[t[n0:n1] for t in source_to_key_transforms],
+                                             out=(ring[1], ring[2]), **kw)
                 ev_cmp.record(self.s_cmp)
             with torch.cuda.stream(self.s_out):
                 self.s_out.wait_event(ev_cmp)
-                for v in range(V):
-                    corrs[v].record_stream(self.s_out)
-                    masks[v].record_stream(self.s_out)
-                    out_corr[v, n0:n1].copy_(corrs[v], non_blocking=True)
-                    out_mask[v, n0:n1].copy_(masks[v], non_blocking=True)
-            keep.append((corrs, masks))
-        self.s_out.synchronize()
-        cur.wait_stream(self.s_cmp)
+                for v in range(V):                        # one contiguous block per view
+                    out_corr[v, n0:n1].copy_(ring[1][v], non_blocking=True)
+                    out_mask[v, n0:n1].copy_(ring[2][v], non_blocking=True)
+                ring[3] = torch.cuda.Event()
+                ring[3].record(self.s_out)
+            self._cmp_done[slot] = ev_cmp
+        self._done = torch.cuda.Event()
+        self._done.record(self.s_out)
+        if wait:
+            self.finish()
         return out_corr, out_mask

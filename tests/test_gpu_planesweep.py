@@ -190,3 +190,32 @@ def test_host_pipeline_equals_direct_call(cuda_lib):
                                               source_to_key_transforms=Ts, **kw)
     for v in range(V):
         assert torch.equal(out[0, v], corrs[v].cpu()) and torch.equal(out[1, v], masks[v].cpu())
+
+
+@pytest.mark.gpu
+def test_host_pipeline_stream_of_batches(cuda_lib):
+    """run(wait=False) per batch + finish(): consecutive batches overlap (double-buffered device inputs) and every batch
+    still equals the direct call on its own inputs."""
+    from robustmvd_b200 import synthetic as syn
+    from robustmvd_b200.blocks.planesweep_corr import PlanesweepCorrelation
+    from robustmvd_b200.pipeline import HostPlanesweepPipeline
+    N, V, S, B = 3, 2, 40, 5
+    kw = dict(num_sampling_points=S, min_depth=0.4, max_depth=1000.0)
+    dev = torch.device("cuda:0")
+    pipe = HostPlanesweepPipeline(dev, PlanesweepCorrelation(), chunk_frames=[1, 2])
+    batches = []
+    for b in range(B):
+        inp = syn.planesweep_inputs(24, 40, 64, V, n=N, seed=200 + b)
+        batches.append(dict(
+            Kk=torch.from_numpy(inp["intrinsics_key"]).to(dev), Ts=[torch.from_numpy(x).to(dev) for x in inp["transforms"]],
+            hk=torch.from_numpy(inp["feat_key"]).pin_memory(), hs=[torch.from_numpy(f).pin_memory() for f in inp["feat_sources"]],
+            out=torch.zeros((2, V, N, S, 24, 40), dtype=torch.float32).pin_memory()))
+    for x in batches:
+        pipe.run(x["hk"], x["Kk"], x["hs"], x["Ts"], x["out"][0], x["out"][1], wait=False, **kw)
+    pipe.finish()
+    blk = PlanesweepCorrelation()
+    for x in batches:
+        corrs, masks, _ = blk(feat_key=x["hk"].to(dev), intrinsics_key=x["Kk"], feat_sources=[f.to(dev) for f in x["hs"]],
+                              source_to_key_transforms=x["Ts"], **kw)
+        for v in range(V):
+            assert torch.equal(x["out"][0, v], corrs[v].cpu()) and torch.equal(x["out"][1, v], masks[v].cpu())
