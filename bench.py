@@ -274,7 +274,7 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--frames", type=int, default=8, help="frames per GPU per step")
+    ap.add_argument("--frames", type=int, default=16, help="frames per GPU per step (16 x 240 tiles = 12.97 waves of 296 CTA slots)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-chunk", default="2", help="frames per chunk of the host pipeline (e2e leg); a,b,c = schedule, last repeats")
     args = ap.parse_args()
