@@ -118,7 +118,8 @@ def base_line(args, frames, world):
                                    "C=256, S=256 planes (0.4 m..1000 m, linear inverse depth), 2 source views",
                        "frames_per_gpu_per_step": frames, "frames_per_step": frames * world,
                        "voxels_per_step": voxels(frames) * world, "parallelism": f"samples x{world}",
-                       "l2": "step working set 441 MB > 126 MB L2 (no flush needed)" if frames >= 4 else
+                       "l2": "step working set %d MB > 126 MB L2 (no flush needed)" % round(algorithmic_bytes(frames) / 1e6)
+                             if frames >= 4 else
                              "L2 flushed between steps (256 MB scratch write)"}}
 
 
