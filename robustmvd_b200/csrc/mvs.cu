@@ -42,6 +42,36 @@ __device__ __forceinline__ void homo_coord(const float* M, int xi, int yi, float
   iy = grid_unnormalize(yn, H);
 }
 
+// Same chain with the divisions through shared reciprocals (common.cuh: bit-identical to div.rn inside the guarded range;
+// operands outside it take homo_coord() itself).  y_w, y_h = rcp_refined((W - 1) / 2), rcp_refined((H - 1) / 2).
+__device__ __forceinline__ void homo_coord_shared(const float* M, int xi, int yi, float d, int H, int W, float y_w, float y_h,
+                                                  float& ix, float& iy) {
+  const float gx = fmul((float)xi, d), gy = fmul((float)yi, d), gz = d;  // :248
+  float p[3];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    float acc = fmul(M[r * 4 + 0], gx);
+    acc = __fmaf_rn(M[r * 4 + 1], gy, acc);
+    acc = __fmaf_rn(M[r * 4 + 2], gz, acc);
+    p[r] = fadd(acc, M[r * 4 + 3]);  // :251
+  }
+  // numerators and quotients: zero or inside [2^-60, 2^60], so that no quotient or residual is subnormal
+  auto in_range = [](float v) { const float a = fabsf(v); return (a == 0.0f) || ((a >= kDivLo) && (a <= kDivHi)); };
+  const float az = fabsf(p[2]);
+  bool fast = (az >= kDivLo) && (az <= kDivHi) && in_range(p[0]) && in_range(p[1]) && (W > 1) && (H > 1);
+  const float y = rcp_refined(p[2]);
+  const float sx = div_shared(p[0], p[2], y), sy = div_shared(p[1], p[2], y);
+  fast = fast && in_range(sx) && in_range(sy);
+  if (fast) {
+    const float xn = fsub(div_shared(sx, (float)(W - 1) * 0.5f, y_w), 1.0f);
+    const float yn = fsub(div_shared(sy, (float)(H - 1) * 0.5f, y_h), 1.0f);
+    ix = grid_unnormalize(xn, W);
+    iy = grid_unnormalize(yn, H);
+  } else {
+    homo_coord(M, xi, yi, d, H, W, ix, iy);
+  }
+}
+
 struct Gather {
   int o_nw, o_ne, o_sw, o_se;
   float nw, ne, sw, se;
@@ -143,13 +173,13 @@ constexpr int kVarDB = 4;        // depth planes per CTA
 constexpr int kVarCap = 768;     // staged floats per channel (rectangle area limit)
 constexpr int kVarThreads = kVarPx * kVarDB;
 
-template <int kCh>
+template <int kCh, bool kFull>   // kFull: C is a multiple of kCh (no per-channel guards)
 __global__ void __launch_bounds__(kVarThreads, 2) mvs_variance_tile_kernel(
     const float* __restrict__ feats, const float* __restrict__ proj, const float* __restrict__ depths, int B, int Vt, int C,
     int h, int w, int D, int d_begin, int d_end, float* __restrict__ variance, int out_D, int out_d0, int tiles_x, int ncg, int vec16) {
   extern __shared__ __align__(16) float s_tile[];   // [kCh][kVarCap]
   __shared__ float s_M[kMaxMvsViews][12];
-  __shared__ int4 s_red[kVarThreads / 32];
+  __shared__ int s_box[2][4];   // bounding rectangle {xlo, -xhi, ylo, -yhi} of the current view (min-reduced), two sets in turn
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int b = blockIdx.z;
   const int P = h * w;
@@ -160,7 +190,9 @@ __global__ void __launch_bounds__(kVarThreads, 2) mvs_variance_tile_kernel(
     const int v = 1 + e / 12, i = (e % 12) / 4, j = e % 4;
     s_M[v - 1][i * 4 + j] = matmul4_elem(proj + ((size_t)b * Vt + v) * 16, proj + ((size_t)b * Vt) * 16, i, j);
   }
+  if (t < 8) s_box[t >> 2][t & 3] = 0x7fffffff;
   __syncthreads();
+  const float y_w = rcp_refined((float)(w - 1) * 0.5f), y_h = rcp_refined((float)(h - 1) * 0.5f);
   const int xi = bx * kVarPx + (t & (kVarPx - 1));
   const int dl = dblk * kVarDB + (t / kVarPx);
   const int d = d_begin + dl;
@@ -171,17 +203,17 @@ __global__ void __launch_bounds__(kVarThreads, 2) mvs_variance_tile_kernel(
   float sum[kCh], sq[kCh];
   {
     const float* ref = feats + (((size_t)b * Vt) * C + c0) * P + p;   // running pointer: one 64-bit add per channel
-    const int nch = active ? min(kCh, C - c0) : 0;
+    const int nch = active ? (kFull ? kCh : min(kCh, C - c0)) : 0;
 #pragma unroll
     for (int k = 0; k < kCh; ++k, ref += P) {
-      const float r = (k < nch) ? __ldg(ref) : 0.f;
+      const float r = (kFull ? active : (k < nch)) ? __ldg(ref) : 0.f;
       sum[k] = r;               // volume_sum = ref_volume (:125)
       sq[k] = r * r;            // ref_volume ** 2 (:126)
     }
   }
   for (int v = 1; v < Vt; ++v) {
     float ix, iy;
-    homo_coord(s_M[v - 1], xi, yi, depth, h, w, ix, iy);
+    homo_coord_shared(s_M[v - 1], xi, yi, depth, h, w, y_w, y_h, ix, iy);
     const Bilinear bl = bilinear_setup(ix, iy, h, w);
     const int x0 = isnan(bl.x0f) ? -2 : sat_index(bl.x0f, w), y0 = isnan(bl.y0f) ? -2 : sat_index(bl.y0f, h);
     const bool left = (bl.nw != 0.f) || (bl.sw != 0.f), right = (bl.ne != 0.f) || (bl.se != 0.f);
@@ -190,15 +222,14 @@ __global__ void __launch_bounds__(kVarThreads, 2) mvs_variance_tile_kernel(
     // bounding rectangle of the corners that carry weight (a non-zero weight implies the corner is inside the map)
     int xlo = needed ? (left ? x0 : x0 + 1) : 0x7fffffff, xhi = needed ? (right ? x0 + 1 : x0) : -0x7fffffff;
     int ylo = needed ? (top ? y0 : y0 + 1) : 0x7fffffff, yhi = needed ? (bottom ? y0 + 1 : y0) : -0x7fffffff;
-    xlo = __reduce_min_sync(kFullMask, xlo); xhi = __reduce_max_sync(kFullMask, xhi);
-    ylo = __reduce_min_sync(kFullMask, ylo); yhi = __reduce_max_sync(kFullMask, yhi);
-    if (lane == 0) s_red[warp] = make_int4(xlo, xhi, ylo, yhi);
+    // warp reduction, then one shared atomic per warp and bound (lanes 0..3); maxima travel negated
+    xlo = __reduce_min_sync(kFullMask, xlo); xhi = -__reduce_max_sync(kFullMask, xhi);
+    ylo = __reduce_min_sync(kFullMask, ylo); yhi = -__reduce_max_sync(kFullMask, yhi);
+    int* box = s_box[v & 1];
+    if (lane < 4) atomicMin(box + lane, lane == 0 ? xlo : lane == 1 ? xhi : lane == 2 ? ylo : yhi);
     __syncthreads();
-#pragma unroll
-    for (int k = 0; k < kVarThreads / 32; ++k) {
-      const int4 r = s_red[k];
-      xlo = min(xlo, r.x); xhi = max(xhi, r.y); ylo = min(ylo, r.z); yhi = max(yhi, r.w);
-    }
+    xlo = box[0]; xhi = -box[1]; ylo = box[2]; yhi = -box[3];
+    if (t < 4) s_box[(v + 1) & 1][t] = 0x7fffffff;          // next view's set: last read before this view's first barrier
     const float* src = feats + (((size_t)b * Vt + v) * C + c0) * P;
     if (xlo <= xhi) {                                       // uniform: someone samples inside the map
       // staged rectangle: columns [xo, xo + rw), rows [ylo, ylo + rh); with 16-byte copies the columns are widened to
@@ -215,7 +246,7 @@ __global__ void __launch_bounds__(kVarThreads, 2) mvs_variance_tile_kernel(
             const unsigned sdst = (unsigned)__cvta_generic_to_shared(s_tile + r * rw + 4 * xc);
 #pragma unroll
             for (int c = t >> 6; c < kCh; c += kVarThreads / 64) {
-              if (c0 + c < C)   // asynchronous copies: the whole rectangle is in flight at once
+              if (kFull || c0 + c < C)   // asynchronous copies: the whole rectangle is in flight at once
                 asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sdst + c * (kVarCap * 4)), "l"(g + (size_t)c * P));
               else
                 *reinterpret_cast<float4*>(s_tile + c * kVarCap + r * rw + 4 * xc) = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -229,7 +260,7 @@ __global__ void __launch_bounds__(kVarThreads, 2) mvs_variance_tile_kernel(
             const unsigned sdst = (unsigned)__cvta_generic_to_shared(s_tile + e);
 #pragma unroll 4
             for (int c = t >> 7; c < kCh; c += kVarThreads / 128) {
-              if (c0 + c < C)
+              if (kFull || c0 + c < C)
                 asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(sdst + c * (kVarCap * 4)), "l"(g + (size_t)c * P));
               else
                 s_tile[c * kVarCap + e] = 0.f;
@@ -260,7 +291,7 @@ __global__ void __launch_bounds__(kVarThreads, 2) mvs_variance_tile_kernel(
         const Gather g = make_gather(ix, iy, h, w);
 #pragma unroll
         for (int k = 0; k < kCh; ++k) {
-          if (c0 + k < C) {
+          if (kFull || c0 + k < C) {
             const float val = gather_val(src + (size_t)k * P, g);
             sum[k] += val;
             sq[k] = fmaf(val, val, sq[k]);
@@ -268,16 +299,16 @@ __global__ void __launch_bounds__(kVarThreads, 2) mvs_variance_tile_kernel(
         }
       }
     }
-    __syncthreads();                                        // s_red and the staged rectangle are reused by the next view
+    __syncthreads();                                        // the staged rectangle is reused by the next view
   }
   if (!active) return;
   const float inv_V = 1.0f / (float)Vt;      // x / V as x * (1 / V): within 1 ulp, far inside the 1e-4 volume tolerance
   float* out = variance + (((size_t)b * C + c0) * out_D + out_d0 + dl) * P + p;
   const size_t cstride = (size_t)out_D * P;
-  const int nch = min(kCh, C - c0);
+  const int nch = kFull ? kCh : min(kCh, C - c0);
 #pragma unroll
   for (int k = 0; k < kCh; ++k, out += cstride) {
-    if (k < nch) {
+    if (kFull || k < nch) {
       const float mean = sum[k] * inv_V;
       __stcs(out, fsub(sq[k] * inv_V, fmul(mean, mean)));  // :135; streaming store: the volume is written once, never re-read here
     }
@@ -522,7 +553,8 @@ extern "C" int rmvd_mvs_variance_fwd(const float* feats, const float* proj, cons
                                                               out_D, out_d0, tiles_x, ncg, vec16);
     return (int)cudaGetLastError();
   };
-  return (C > 16) ? launch(mvs_variance_tile_kernel<32>, 32) : launch(mvs_variance_tile_kernel<16>, 16);
+  if (C > 16) return (C % 32 == 0) ? launch(mvs_variance_tile_kernel<32, true>, 32) : launch(mvs_variance_tile_kernel<32, false>, 32);
+  return (C % 16 == 0) ? launch(mvs_variance_tile_kernel<16, true>, 16) : launch(mvs_variance_tile_kernel<16, false>, 16);
 }
 
 extern "C" int rmvd_homo_warp_fwd(const float* src_feat, const float* src_proj, const float* ref_proj_inv,
