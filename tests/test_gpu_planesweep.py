@@ -56,6 +56,36 @@ def test_cuda_matches_oracle_and_golden(cuda_lib, case):
         check_planesweep_against_golden(g, corrs, masks, inv, tol=TOL)
 
 
+# key map (h, w), source map (hs, ws), channels: every kind of tile rectangle the launcher picks (row segments, 32 x 2, whole
+# rows of narrow maps, one-pixel-wide maps, ragged last tiles) and source maps of another size
+TILE_SHAPES = [(7, 33, 7, 33, 32), (10, 130, 10, 130, 64), (100, 8, 100, 8, 32), (50, 3, 50, 3, 32), (70, 1, 70, 1, 32),
+               (2, 200, 2, 200, 32), (1, 96, 1, 96, 64), (31, 31, 17, 45, 32), (9, 65, 20, 130, 32), (5, 64, 5, 64, 96)]
+
+
+@pytest.mark.parametrize("shape", TILE_SHAPES, ids=["%dx%d_src%dx%d_c%d" % s for s in TILE_SHAPES])
+def test_tile_shapes_against_oracle(cuda_lib, shape):
+    """Odd map sizes through the tensor-core kernel: masks and integer indices bit-exact, corr within tolerance."""
+    h, w, hs, ws, C = shape
+    inp = syn.planesweep_inputs(h, w, C, 2, n=2, seed=500 + h + w, hs=hs, ws=ws)
+    case = dict(name="shape", feat_key=inp["feat_key"], intrinsics_key=inp["intrinsics_key"],
+                feat_sources=inp["feat_sources"], transforms=inp["transforms"], intrinsics_sources=None,
+                kwargs=dict(num_sampling_points=40, min_depth=0.4, max_depth=1000.0))
+    corrs, masks, inv, dbg = _run_cuda(case)
+    ocorrs, omasks, oinv, odbg = oracle.planesweep_correlation(
+        case["feat_key"], case["intrinsics_key"], case["feat_sources"], case["transforms"], None, return_debug=True,
+        **case["kwargs"])
+    for v in range(2):
+        assert np.array_equal(masks[v], omasks[v]), f"mask view {v}: {(masks[v] != omasks[v]).sum()} mismatches"
+        assert np.array_equal(dbg["ix0"][v], odbg[v]["ix0"]) and np.array_equal(dbg["iy0"][v], odbg[v]["iy0"])
+        assert np.array_equal(dbg["geom"][v].astype(bool), odbg[v]["geom_mask"])
+        scale = max(float(np.abs(ocorrs[v]).max()), 1e-30)
+        assert float(np.abs(corrs[v] - ocorrs[v]).max()) / scale <= TOL
+    # same call without the debug outputs (dead-plane skipping enabled)
+    corrs2, masks2, _, _ = _run_cuda(case, debug=False)
+    for v in range(2):
+        assert np.array_equal(masks2[v], masks[v]) and np.array_equal(corrs2[v], corrs[v])
+
+
 def test_depth_slabs_concatenate_to_full_volume(cuda_lib):
     case = [c for c in PS if c["name"] == "kitti_like_c32"][0]
     full_c, full_m, _, _ = _run_cuda(case, debug=False)
