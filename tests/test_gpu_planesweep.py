@@ -86,6 +86,14 @@ def test_tile_shapes_against_oracle(cuda_lib, shape):
         assert np.array_equal(masks2[v], masks[v]) and np.array_equal(corrs2[v], corrs[v])
 
 
+def test_randomised_cases_against_oracle(cuda_lib, monkeypatch):
+    """tools/tc_fuzz.py: random shapes, poses, plane counts up to 300 and explicit schedules with zero / negative / inf / nan
+    entries; masks and indices bit-exact, with and without the debug outputs."""
+    from tools import tc_fuzz
+    monkeypatch.setattr("sys.argv", ["tc_fuzz", "40", "11"])
+    assert tc_fuzz.main() == 0
+
+
 def test_depth_slabs_concatenate_to_full_volume(cuda_lib):
     case = [c for c in PS if c["name"] == "kitti_like_c32"][0]
     full_c, full_m, _, _ = _run_cuda(case, debug=False)
