@@ -163,6 +163,17 @@ int rmvd_soft_argmin_fwd(const float* volume, int B, int D, int h, int w, float 
                          float* expected_index, float* prob_map, float* entropy, void* stream);
 
 /*
+ * Learned view fusion, elementwise part (rmvd/models/blocks/learned_fusion.py:33-47): replaces
+ * softmax(stack(view_weights), 0) + 1e-9, view_weight * mask, the two stacks / products / sums over the views, the division
+ * and the fused mask.  logits[v]: [N,1,h,w] (output of corr_to_view_weight, :28), corrs[v] / masks[v]: [N,S,h,w] (the
+ * outputs of rmvd_psweep_corr_fwd, separate or views of one allocation); host arrays of V <= 32 device pointers.
+ * weights (optional): [V,N,1,h,w] = self.view_weights; fused_corr, fused_mask: [N,S,h,w].  V == 1 is the caller's
+ * pass-through (:50-52), not a kernel call.
+ */
+int rmvd_view_fusion_fwd(const float* const* logits, const float* const* corrs, const float* const* masks, int V, int N,
+                         int S, int h, int w, float* weights, float* fused_corr, float* fused_mask, void* stream);
+
+/*
  * Test hook: the sampling chain of the tcgen05 kernel shares one refined reciprocal between its divisions
  * (csrc/psweep_tc.cu: rcp_refined / div_shared, the fast path of div.rn.f32 itself).  q_shared[i] = that sequence,
  * q_rn[i] = __fdiv_rn(a[i], b[i]); the two must agree bit for bit for 2^-60 <= |b| <= 2^60, |a| <= 2^60.

@@ -44,3 +44,4 @@ from .mvsnet import (  # noqa: F401
     soft_argmin,
     entropy,
 )
+from .fusion import view_fusion  # noqa: F401,E402

@@ -76,6 +76,8 @@ class LearnedFusion(nn.Module):
         if len(corrs) == 1:
             self.fused_corr, self.fused_mask = corrs[0], masks[0]
             return self.fused_corr, self.fused_mask
+        if corrs[0].is_cuda:
+            return self._forward_cuda(corrs, masks)
         logits = torch.stack([self.corr_to_view_weight(c) for c in corrs], 0)  # V,N,1,h,w
         weights = F.softmax(logits, dim=0) + 1e-9
         self.view_weights = list(weights.unbind(0))
@@ -84,6 +86,27 @@ class LearnedFusion(nn.Module):
         self.fused_mask = (wsum != 0).float()
         csum = (torch.stack(corrs, 0) * masked).sum(0)
         self.fused_corr = csum / (wsum + 1e-9) * self.fused_mask
+        return self.fused_corr, self.fused_mask
+
+
+    @torch.no_grad()
+    def _forward_cuda(self, corrs, masks):
+        """learned_fusion.py:33-48 in one pass over corrs / masks (csrc/fusion.cu); the convolutions stay in cuDNN."""
+        from .. import _lib
+        V = len(corrs)
+        N, S, h, w = corrs[0].shape
+        f32c = lambda t: t if (t.dtype == torch.float32 and t.is_contiguous()) else t.float().contiguous()  # noqa: E731
+        cs, ms = [f32c(c) for c in corrs], [f32c(m) for m in masks]
+        logits = [f32c(self.corr_to_view_weight(c)) for c in cs]                # V x [N,1,h,w]
+        dev = cs[0].device
+        weights = torch.empty((V, N, 1, h, w), dtype=torch.float32, device=dev)
+        fused_corr = torch.empty((N, S, h, w), dtype=torch.float32, device=dev)
+        fused_mask = torch.empty_like(fused_corr)
+        st = _lib.load().rmvd_view_fusion_fwd(_lib.ptr_array(logits), _lib.ptr_array(cs), _lib.ptr_array(ms), V, N, S, h, w,
+                                              _lib.ptr(weights), _lib.ptr(fused_corr), _lib.ptr(fused_mask), _lib.stream_ptr())
+        _lib.check(st, "rmvd_view_fusion_fwd")
+        self.view_weights = list(weights.unbind(0))
+        self.fused_corr, self.fused_mask = fused_corr, fused_mask
         return self.fused_corr, self.fused_mask
 
 

@@ -59,3 +59,21 @@ def test_torch_cpu_baseline_port_matches_oracle():
     m = MVS[0]
     var = torch_cpu.mvs_variance(m["feats"], m["proj"], m["depth"])
     check_mvs_variance_against_golden(load_golden("mvs", m["name"]), var, tol=1e-5)
+
+
+def test_fusion_oracle_against_golden():
+    """oracle.view_fusion against the outputs of the unmodified reference LearnedFusion (tools/make_fusion_golden.py)."""
+    import glob
+    import os
+    from golden_util import GOLDEN
+    files = sorted(glob.glob(os.path.join(GOLDEN, "fusion_*.npz")))
+    assert len(files) >= 4
+    for f in files:
+        g = np.load(f)
+        V = int(g["V"])
+        w, fc, fm = oracle.view_fusion([g[f"logit_{v}"] for v in range(V)], [g[f"corr_{v}"] for v in range(V)],
+                                       [g[f"mask_{v}"].astype(np.float32) for v in range(V)])
+        assert np.array_equal(fm, g["fused_mask"])
+        assert np.abs(fc - g["fused_corr"]).max() <= 1e-6 * max(float(np.abs(g["fused_corr"]).max()), 1e-30)
+        for v in range(V if V > 1 else 0):
+            assert np.abs(w[v] - g[f"weight_{v}"]).max() <= 1e-6

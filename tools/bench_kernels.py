@@ -88,6 +88,19 @@ def main():
     wblk = PlanesweepCorrelation(warp_only=True, normalize=False)
     kww, _, _ = psweep_case(syn.CFG2, 1, 1, S=64)
     add("psweep_warp_only_cfg2_S64", lambda: wblk(**kww), 4 * 256 * 7680 + 4 * 64 * 257 * 7680, 64 * 7680, "voxels")
+    # learned view fusion, elementwise part at cfg2 x 8 frames: reads corr + mask of V views, writes fused corr + mask
+    from robustmvd_b200 import _lib
+    Vf, Nf, Sf, Pf = 2, 8, 256, 48 * 160
+    fl = [torch.randn((Nf, 1, 48, 160), device="cuda") for _ in range(Vf)]
+    fc = [torch.randn((Nf, Sf, 48, 160), device="cuda") for _ in range(Vf)]
+    fm = [(torch.rand((Nf, Sf, 48, 160), device="cuda") < 0.6).float() for _ in range(Vf)]
+    fw = torch.empty((Vf, Nf, 1, 48, 160), device="cuda")
+    fo = [torch.empty((Nf, Sf, 48, 160), device="cuda") for _ in range(2)]
+
+    def run_fusion():
+        _lib.check(_lib.load().rmvd_view_fusion_fwd(_lib.ptr_array(fl), _lib.ptr_array(fc), _lib.ptr_array(fm), Vf, Nf, Sf, 48, 160,
+                                                    _lib.ptr(fw), _lib.ptr(fo[0]), _lib.ptr(fo[1]), _lib.stream_ptr()), "fusion")
+    add("view_fusion_cfg2_8frames", run_fusion, 4 * (2 * Vf + 2) * Nf * Sf * Pf + 8 * Vf * Nf * Pf, Nf * Sf * Pf, "voxels")
     for name, fn, nbytes, units, unit_name in jobs:
         cold, best, warm = time_fn(fn, args.reps, flush)
         print(json.dumps({"kernel": name, "ms_cold": cold, "ms_cold_min": best, "ms_warm": warm, "algorithmic_bytes": nbytes,
