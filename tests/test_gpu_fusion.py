@@ -25,7 +25,12 @@ def _fuse_cuda(logits, corrs, masks):
     tc = [torch.from_numpy(np.ascontiguousarray(x)).to(dev) for x in corrs]
     tm = [torch.from_numpy(np.ascontiguousarray(x)).to(dev) for x in masks]
     by_ptr = {c.data_ptr(): l for c, l in zip(tc, tl)}
-    blk.corr_to_view_weight = lambda c: by_ptr[c.data_ptr()]
+
+    class Lookup(torch.nn.Module):
+        def forward(self, c):
+            return by_ptr[c.data_ptr()]
+
+    blk.corr_to_view_weight = Lookup()
     fc, fm = blk(tc, tm)
     torch.cuda.synchronize()
     w = None if len(corrs) == 1 else np.stack([x.cpu().numpy() for x in blk.view_weights], 0)
