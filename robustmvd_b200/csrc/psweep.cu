@@ -410,8 +410,7 @@ extern "C" int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* f
   wsp += (((size_t)N * C * h * w * sizeof(float)) + 255) / 256 * 256;
   const int l2 = normalize_mode == RMVD_NORM_BEFORE;
   if (tc) {
-    int rc = repack_split(feat_key, key_nhwc, N, C, h * w, l2, st);
-    if (rc) return rc;
+    // repacked together with the first group of source maps below (one launch)
   } else if (band) {
     int rc = repack(feat_key, key_nhwc, N, C, h * w, l2, st);
     if (rc) return rc;
@@ -423,18 +422,30 @@ extern "C" int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* f
     A.Kk = intrinsics_key;
     A.invd = invdepths;
     for (int k = 0; k < 4; ++k) A.ist[k] = inv_stride[k];
+    const float* rp_src[1 + kMaxViews];
+    void* rp_dst[1 + kMaxViews];
+    int rp_P[1 + kMaxViews];
+    int rp_n = 0;
+    if (tc && v0 == 0) { rp_src[0] = feat_key; rp_dst[0] = key_nhwc; rp_P[0] = h * w; rp_n = 1; }
     for (int j = 0; j < nv; ++j) {
       const int v = v0 + j;
       float* dst = (float*)wsp;
       wsp += (((size_t)N * C * hs[v] * ws[v] * sizeof(float)) + 255) / 256 * 256;
-      int rc = tc ? repack_split(feat_src[v], dst, N, C, hs[v] * ws[v], l2, st)
-                  : repack(feat_src[v], dst, N, C, hs[v] * ws[v], l2, st);
-      if (rc) return rc;
+      if (tc) {
+        rp_src[rp_n] = feat_src[v]; rp_dst[rp_n] = dst; rp_P[rp_n] = hs[v] * ws[v]; ++rp_n;
+      } else {
+        int rc = repack(feat_src[v], dst, N, C, hs[v] * ws[v], l2, st);
+        if (rc) return rc;
+      }
       A.src[j] = dst;
       A.Ks[j] = intrinsics_src[v];
       A.T[j] = src_to_key[v];
       A.hs[j] = hs[v];
       A.ws[j] = ws[v];
+    }
+    if (tc) {
+      int rc = repack_split_batch(rp_src, rp_dst, rp_P, rp_n, N, C, l2, st);
+      if (rc) return rc;
     }
     A.N = N; A.C = C; A.h = h; A.w = w; A.S = S; A.s_begin = s_begin; A.s_end = s_end;
     A.norm = normalize_mode; A.out_S = out_S; A.out_s0 = out_s0; A.v0 = v0;

@@ -37,6 +37,9 @@ int launch_psweep_band(const PsweepArgs& A, const float* key_nhwc, int nviews, c
 // workspace slots (4 bytes per feature element) the fp32 channels-last copies of the band kernel use.
 bool psweep_tc_eligible(const PsweepArgs& A, int nviews);
 int repack_split(const float* src, void* dst, int N, int C, int P, int l2norm, cudaStream_t st);
+// the same for up to 1 + kMaxViews maps of one call (key + sources) in one launch
+int repack_split_batch(const float* const* srcs, void* const* dsts, const int* Ps, int count, int N, int C, int l2norm,
+                       cudaStream_t st);
 int launch_psweep_tc(const PsweepArgs& A, const void* key_split, int nviews, cudaStream_t st);
 
 }  // namespace rmvd

@@ -21,7 +21,7 @@ echo "ncu launches rc=$?"
 timeout 300 $BCMD > $OUT/plain2.log 2>&1 &&
 timeout 1200 ncu --set full --clock-control none --import-source on -k regex:psweep_tc_kernel -s 3 -c 1 -o $OUT/prof_tc $BCMD > $OUT/ncu_tc.log 2>&1
 echo "ncu tc rc=$?"
-timeout 600 ncu --set full --clock-control none -k regex:nchw_to_split -s 9 -c 1 -o $OUT/prof_repack $BCMD > $OUT/ncu_repack.log 2>&1
+timeout 600 ncu --set full --clock-control none -k regex:nchw_to_split -s 3 -c 1 -o $OUT/prof_repack $BCMD > $OUT/ncu_repack.log 2>&1
 VCMD="python tools/bench_kernels.py --reps 1 --only mvs_variance"
 timeout 300 $VCMD > $OUT/plain_var.log 2>&1 &&
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:mvs_variance_tile -s 2 -c 1 -o $OUT/prof_var $VCMD > $OUT/ncu_var.log 2>&1
