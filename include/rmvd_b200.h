@@ -166,7 +166,7 @@ int rmvd_soft_argmin_fwd(const float* volume, int B, int D, int h, int w, float 
  * Learned view fusion, elementwise part (rmvd/models/blocks/learned_fusion.py:33-47): replaces
  * softmax(stack(view_weights), 0) + 1e-9, view_weight * mask, the two stacks / products / sums over the views, the division
  * and the fused mask.  logits[v]: [N,1,h,w] (output of corr_to_view_weight, :28), corrs[v] / masks[v]: [N,S,h,w] (the
- * outputs of rmvd_psweep_corr_fwd, separate or views of one allocation); host arrays of V <= 32 device pointers.
+ * outputs of rmvd_psweep_corr_fwd, separate or views of one allocation); host arrays of V <= 64 device pointers.
  * weights (optional): [V,N,1,h,w] = self.view_weights; fused_corr, fused_mask: [N,S,h,w].  V == 1 is the caller's
  * pass-through (:50-52), not a kernel call.
  */

@@ -14,7 +14,7 @@
 
 namespace rmvd {
 
-constexpr int kFuseMaxViews = 32;
+constexpr int kFuseMaxViews = 64;
 constexpr int kFusePl = 8;        // planes per thread (2 * V * kFusePl independent loads in flight)
 constexpr int kFuseThreads = 128;
 

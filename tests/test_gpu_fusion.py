@@ -59,8 +59,8 @@ def test_fusion_matches_oracle_and_golden(cuda_lib, path):
     _check(w, fc, fm, gw, g["fused_corr"], g["fused_mask"])
 
 
-@pytest.mark.parametrize("shape", [(2, 2, 256, 48, 160), (10, 1, 256, 24, 36), (3, 1, 13, 7, 33), (32, 1, 5, 3, 9)],
-                         ids=["cfg2_2frames", "v10", "ragged_planes", "v32"])
+@pytest.mark.parametrize("shape", [(2, 2, 256, 48, 160), (10, 1, 256, 24, 36), (3, 1, 13, 7, 33), (64, 1, 5, 3, 9)],
+                         ids=["cfg2_2frames", "v10", "ragged_planes", "v64"])
 def test_fusion_sizes_against_oracle(cuda_lib, shape):
     """Bench shape, many views, a plane count that is not a multiple of the planes per thread, the view limit."""
     V, N, S, h, w = shape
@@ -80,6 +80,6 @@ def test_fusion_rejects_too_many_views(cuda_lib):
     x = torch.zeros((1, 1, 2, 2), device="cuda:0")
     c = torch.zeros((1, 3, 2, 2), device="cuda:0")
     out = torch.empty_like(c)
-    st = _lib.load().rmvd_view_fusion_fwd(_lib.ptr_array([x] * 33), _lib.ptr_array([c] * 33), _lib.ptr_array([c] * 33), 33, 1, 3,
+    st = _lib.load().rmvd_view_fusion_fwd(_lib.ptr_array([x] * 65), _lib.ptr_array([c] * 65), _lib.ptr_array([c] * 65), 65, 1, 3,
                                           2, 2, None, _lib.ptr(out), _lib.ptr(out), _lib.stream_ptr())
     assert st < 0
