@@ -6,6 +6,7 @@ linear in inverse depth over (0.4 m, 1000 m), :71-80) -> learned fusion -> cost-
 Only ``corr_block`` is the hot path; the convolutions are stock cuDNN modules (``nets.py``).
 """
 import math
+import os
 
 import numpy as np
 import torch
@@ -54,8 +55,18 @@ class RobustMVD(nn.Module):
         intrinsics_source = exclude_index(intrinsics, keyview_idx)
         source_to_key_transforms = exclude_index(poses, keyview_idx)
 
-        all_enc_key, enc_key = self.encoder(image_key)
-        enc_sources = [self.encoder(image_source)[1] for image_source in images_source]
+        if image_key.is_cuda and len(images_source) > 0 and os.environ.get("RMVD_BATCH_ENCODER", "1") != "0":
+            # key and source views through the encoder as ONE (1 + V) * N batch (robust_mvd.py:66-67 runs
+            # it once per view): the same convolutions with 1 / (1 + V) of the launches; the per-view features are
+            # contiguous slices of one tensor, which is also what the correlation call's single repack launch reads
+            nb = image_key.shape[0]
+            all_enc, enc = self.encoder(torch.cat([image_key] + list(images_source), 0))
+            all_enc_key = {k: v[:nb] for k, v in all_enc.items()}
+            enc_key = enc[:nb]
+            enc_sources = list(enc[nb:].split(nb, 0))
+        else:
+            all_enc_key, enc_key = self.encoder(image_key)
+            enc_sources = [self.encoder(image_source)[1] for image_source in images_source]
         ctx = self.context_encoder(enc_key)
 
         corrs, masks, _ = self.corr_block(
