@@ -78,6 +78,25 @@ int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* feat_src, co
                          size_t workspace_bytes, void* stream);
 
 /*
+ * Backward of rmvd_psweep_corr_fwd with respect to the feature maps.  The reference obtains it from
+ * autograd through TorchCorr.forward (planesweep_corr.py:152-195: matmul -> / sqrt(C) -> grid_sample -> * corr_mask ->
+ * * geometric mask); sampling points carry no gradient (:436, :464, :489 are no_grad).  Same geometry arguments as the
+ * forward call; normalize_mode RMVD_NORM_NONE or RMVD_NORM_DIM (L2-normalised inputs are differentiated by the caller
+ * around a RMVD_NORM_NONE call).
+ *   grad_corr  [V,N,out_S,h,w], plane s of [s_begin, s_end) read at index out_s0 + (s - s_begin)
+ *   grad_key   [N,C,h,w] (overwritten) or NULL
+ *   grad_src   host array of V device pointers, view v is [N,C,hs[v],ws[v]] (overwritten); entries may be NULL
+ *   workspace  rmvd_psweep_bwd_workspace_bytes(...) bytes of device scratch
+ */
+size_t rmvd_psweep_bwd_workspace_bytes(int N, int C, int h, int w, int V, const int* hs_host, const int* ws_host);
+int rmvd_psweep_corr_bwd(const float* feat_key, const float* const* feat_src, const float* intrinsics_key,
+                         const float* const* intrinsics_src, const float* const* src_to_key,
+                         const float* invdepths, const int64_t* inv_stride_host, int N, int C, int h, int w,
+                         int V, const int* hs_host, const int* ws_host, int S, int s_begin, int s_end,
+                         int normalize_mode, const float* grad_corr, int out_S, int out_s0, float* grad_key,
+                         float* const* grad_src, void* workspace, size_t workspace_bytes, void* stream);
+
+/*
  * PlanesweepCorrelation.forward with warp_only=True: WarpOnlyCorr.forward + warp_multi
  * (planesweep_corr.py:107-140, :13-46).  One source view per call.
  *   warped [N,out_S,C,h,w], mask [N,out_S,h,w] (sampling mask only: the geometric mask is ignored, :116-140)

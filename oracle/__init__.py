@@ -32,6 +32,7 @@ from .planesweep import (  # noqa: F401
     torch_corr,
     warp_only_corr,
     planesweep_correlation,
+    planesweep_correlation_backward,
 )
 from .mvsnet import (  # noqa: F401
     homo_warp_coords,

@@ -340,3 +340,83 @@ def planesweep_correlation(feat_key, intrinsics_key, feat_sources, source_to_key
     if return_debug:
         return corrs, masks, inv, dbg
     return corrs, masks, inv
+
+
+# --------------------------------------------------------------------------------------
+# f-4: backward of the correlation with respect to the feature maps
+# --------------------------------------------------------------------------------------
+def _l2_normalize_backward(x, g, axis):
+    """Gradient of ``x / (||x|| + 1e-9)`` (planesweep_corr.py:8-10) for upstream gradient ``g``."""
+    x = x.astype(np.float64)
+    g = g.astype(np.float64)
+    r = np.sqrt(np.sum(x * x, axis=axis, keepdims=True))
+    den = r + 1e-9
+    dot = np.sum(g * x, axis=axis, keepdims=True)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        corr = np.where(r > 0, x * dot / (den * den * r), 0.0)
+    return g / den - corr
+
+
+def planesweep_correlation_backward(feat_key, intrinsics_key, feat_sources, source_to_key_transforms, grad_corrs,
+                                    intrinsics_sources=None, num_sampling_points=None, min_depth=None, max_depth=None,
+                                    sampling_invdepths=None, sampling_type="linear_invdepth", normalize="dim"):
+    """What autograd returns for ``sum_v <grad_corrs[v], corrs[v]>`` through the reference block with
+    ``warp_only=False`` (``TorchCorr.forward``, planesweep_corr.py:152-195: matmul :174, ``/ sqrt(C)`` :178-179,
+    ``grid_sample`` :91, ``* corr_mask`` :189, ``* mask`` :191-192).  Sampling points carry no gradient (:436, :464,
+    :489 are ``no_grad``).  Returns ``(grad_key [N,C,h,w], [grad_src_v [N,C,hs,ws]])`` as float32 (float64 sums).
+    """
+    feat_key = _f32(feat_key)
+    N, C, h, w = feat_key.shape
+    if intrinsics_sources is None:
+        intrinsics_sources = [intrinsics_key] * len(feat_sources)
+    if min_depth is not None and max_depth is not None:
+        inv = compute_sampling_invdepths(min_depth, max_depth, num_sampling_points, sampling_type)
+    else:
+        inv = _f32(sampling_invdepths)
+    while inv.ndim < 4:
+        inv = inv[..., None]
+    l2 = bool(normalize) and normalize != "dim"
+    scale = np.float64(np.sqrt(F32(C))) if normalize == "dim" else np.float64(1.0)
+    P = h * w
+    key_in = feat_key.reshape(N, C, P)
+    key = _l2_normalize(key_in, 1) if l2 else key_in
+    gkey = np.zeros((N, C, P), np.float64)
+    gsrcs = []
+    for v, T in enumerate(source_to_key_transforms):
+        fs_in = _f32(feat_sources[v])
+        hs, ws = fs_in.shape[-2:]
+        fs_in = fs_in.reshape(N, C, hs * ws)
+        fs = _l2_normalize(fs_in, 1) if l2 else fs_in
+        co = epipolar_coeffs(intrinsics_key, intrinsics_sources[v], T, h, w, hs, ws)
+        us, vs, _, gmask = sampling_points(co, inv)
+        b = bilinear_setup(us, vs, hs, ws)
+        valid = b["samp_mask"].astype(np.float64) * gmask.astype(np.float64)      # [N,S,h,w]
+        g = _f32(grad_corrs[v]).astype(np.float64) * valid / scale
+        gs = np.zeros((N, hs * ws, C), np.float64)
+        S = g.shape[1]
+        for n in range(N):
+            x0 = np.clip(b["ix0"][n], 0, ws - 1).astype(np.int64)
+            x1 = np.clip(b["ix0"][n] + 1, 0, ws - 1).astype(np.int64)
+            y0 = np.clip(b["iy0"][n], 0, hs - 1).astype(np.int64)
+            y1 = np.clip(b["iy0"][n] + 1, 0, hs - 1).astype(np.int64)
+            key_pc = key[n].T.astype(np.float64)                                  # [P,C]
+            src_tc = fs[n].T.astype(np.float64)                                   # [hs*ws,C]
+            for idx, wname, iname in ((y0 * ws + x0, "nw", "in_nw"), (y0 * ws + x1, "ne", "in_ne"),
+                                      (y1 * ws + x0, "sw", "in_sw"), (y1 * ws + x1, "se", "in_se")):
+                with np.errstate(invalid="ignore"):
+                    a = np.where(b[iname][n] & (valid[n] > 0), b[wname][n].astype(np.float64) * g[n], 0.0)  # [S,h,w]
+                for s in range(S):
+                    a_s = a[s].reshape(P)
+                    nz = np.nonzero(a_s)[0]
+                    if nz.size == 0:
+                        continue
+                    t = idx[s].reshape(P)[nz]
+                    gkey[n][:, nz] += (src_tc[t] * a_s[nz, None]).T
+                    np.add.at(gs[n], t, key_pc[nz] * a_s[nz, None])
+        gs = np.ascontiguousarray(np.moveaxis(gs, 2, 1))                          # [N,C,hs*ws]
+        if l2:
+            gs = _l2_normalize_backward(fs_in, gs, 1)
+        gsrcs.append(gs.reshape(N, C, hs, ws).astype(np.float32))
+    if l2:
+        gkey = _l2_normalize_backward(key_in, gkey, 1)
+    return gkey.reshape(N, C, h, w).astype(np.float32), gsrcs

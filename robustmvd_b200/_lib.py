@@ -13,7 +13,8 @@ _lib = None
 
 EXPORTS = (
     "rmvd_abi_version", "rmvd_status_string", "rmvd_psweep_workspace_bytes", "rmvd_psweep_corr_fwd",
-    "rmvd_psweep_warp_fwd", "rmvd_corr_grid_fwd", "rmvd_warp_grid_fwd", "rmvd_mvs_variance_fwd",
+    "rmvd_psweep_warp_fwd", "rmvd_psweep_bwd_workspace_bytes", "rmvd_psweep_corr_bwd",
+    "rmvd_corr_grid_fwd", "rmvd_warp_grid_fwd", "rmvd_mvs_variance_fwd",
     "rmvd_homo_warp_fwd", "rmvd_mvs_regress_fwd", "rmvd_softargmax_partial", "rmvd_softargmax_combine",
     "rmvd_softargmax_confidence", "rmvd_soft_argmin_fwd", "rmvd_view_fusion_fwd", "rmvd_debug_div_check",
 )
@@ -35,6 +36,10 @@ def _declare(lib):
     lib.rmvd_psweep_workspace_bytes.argtypes = [c_int, c_int, c_int, c_int, c_int, PI, PI]
     lib.rmvd_psweep_corr_fwd.argtypes = [P, PP, P, PP, PP, P, PL] + [c_int] * 5 + [PI, PI] + [c_int] * 4 + \
         [P, P, c_int, c_int, P, P, P, P, c_size_t, P]
+    lib.rmvd_psweep_bwd_workspace_bytes.restype = c_size_t
+    lib.rmvd_psweep_bwd_workspace_bytes.argtypes = [c_int, c_int, c_int, c_int, c_int, PI, PI]
+    lib.rmvd_psweep_corr_bwd.argtypes = [P, PP, P, PP, PP, P, PL] + [c_int] * 5 + [PI, PI] + [c_int] * 4 + \
+        [P, c_int, c_int, P, PP, P, c_size_t, P]
     lib.rmvd_psweep_warp_fwd.argtypes = [P, P, P, P, P, PL] + [c_int] * 10 + [P, P, c_int, c_int, P]
     lib.rmvd_corr_grid_fwd.argtypes = [P, P, P, P] + [c_int] * 8 + [P, P, P, c_size_t, P]
     lib.rmvd_warp_grid_fwd.argtypes = [P, P] + [c_int] * 7 + [P, P, P]
@@ -48,7 +53,8 @@ def _declare(lib):
     lib.rmvd_view_fusion_fwd.argtypes = [PP, PP, PP] + [c_int] * 5 + [P, P, P, P]
     lib.rmvd_debug_div_check.argtypes = [P, P, c_int, P, P, P]
     for name in EXPORTS:
-        if name not in ("rmvd_abi_version", "rmvd_status_string", "rmvd_psweep_workspace_bytes"):
+        if name not in ("rmvd_abi_version", "rmvd_status_string", "rmvd_psweep_workspace_bytes",
+                        "rmvd_psweep_bwd_workspace_bytes"):
             getattr(lib, name).restype = c_int
 
 
@@ -85,6 +91,14 @@ def ptr_array(tensors):
     arr = (c_void_p * len(tensors))()
     for i, t in enumerate(tensors):
         arr[i] = ptr(t).value
+    return arr
+
+
+def ptr_array_opt(tensors):
+    """Like ptr_array, with None entries -> NULL."""
+    arr = (c_void_p * len(tensors))()
+    for i, t in enumerate(tensors):
+        arr[i] = None if t is None else ptr(t).value
     return arr
 
 

@@ -3,8 +3,9 @@
 Same names, constructor and ``forward`` signatures, return values and assertions as the reference
 (``PlanesweepCorrelation`` :371-521, ``TorchCorr`` :143-195, ``WarpOnlyCorr`` :107-140, ``warp`` :49-104,
 ``warp_multi`` :13-46, ``compute_sampling_invdepths`` :524-555).  All arithmetic runs in the CUDA library
-(``include/rmvd_b200.h``); there is no PyTorch or CPU fallback.  Forward only: outputs carry no autograd graph
-(the reference's backward is SURVEY.md row f-4).
+(``include/rmvd_b200.h``); there is no PyTorch or CPU fallback.  When gradients are enabled and a feature map requires
+them, the correlation outputs carry an autograd node whose backward is the CUDA kernel behind ``rmvd_psweep_corr_bwd``
+(SURVEY.md row f-4); sampling points carry no gradient, like in the reference (:436, :464, :489 are ``no_grad``).
 """
 import numpy as np
 import torch
@@ -175,6 +176,32 @@ class TorchCorr(nn.Module):
 _INVDEPTH_CACHE = {}
 
 
+class _CorrFunction(torch.autograd.Function):
+    """Autograd node of the correlation (``warp_only=False``): forward = ``rmvd_psweep_corr_fwd``, backward =
+    ``rmvd_psweep_corr_bwd``; the 0/1 mask output is not differentiable."""
+
+    @staticmethod
+    def forward(ctx, block, args, mode, feat_key, *feat_sources):
+        _, _, inv = block._forward_impl(feat_key=feat_key, feat_sources=list(feat_sources), norm_mode=mode, **args)
+        corr, mask = block._stacked
+        block._stacked = None
+        block._inv = inv
+        ctx.block, ctx.args, ctx.mode, ctx.inv = block, args, mode, inv
+        ctx.save_for_backward(feat_key, *feat_sources)
+        ctx.mark_non_differentiable(mask)
+        return corr, mask
+
+    @staticmethod
+    def backward(ctx, grad_corr, _grad_mask):
+        feat_key, *feat_sources = ctx.saved_tensors
+        a = ctx.args
+        need = ctx.needs_input_grad[3:]
+        gkey, gsrcs = ctx.block._backward_impl(
+            grad_corr, feat_key, feat_sources, a["intrinsics_key"], a["source_to_key_transforms"],
+            a["intrinsics_sources"], ctx.inv, a["plane_range"], ctx.mode, need[0], list(need[1:]))
+        return (None, None, None, gkey, *gsrcs)
+
+
 class PlanesweepCorrelation(nn.Module):
     """planesweep_corr.py:371-521.  ``forward`` returns ``(corrs, masks, sampling_invdepths)`` like the reference.
 
@@ -233,10 +260,70 @@ class PlanesweepCorrelation(nn.Module):
             sampling_invdepths = sampling_invdepths.unsqueeze(-1)
         return sampling_invdepths
 
-    @torch.no_grad()
     def forward(self, feat_key, intrinsics_key, feat_sources, source_to_key_transforms, intrinsics_sources=None,
                 num_sampling_points=None, min_depth=None, max_depth=None, sampling_invdepths=None,
                 sampling_type="linear_invdepth", plane_range=None, debug=False, out=None):
+        needs_grad = torch.is_grad_enabled() and not self.warp_only and len(feat_sources) > 0 and (
+            feat_key.requires_grad or any(f.requires_grad for f in feat_sources))
+        if not needs_grad:
+            return self._forward_impl(feat_key, intrinsics_key, feat_sources, source_to_key_transforms,
+                                      intrinsics_sources, num_sampling_points, min_depth, max_depth, sampling_invdepths,
+                                      sampling_type, plane_range, debug, out)
+        assert out is None, "out= is not available on the differentiable path"
+        mode = _corr_norm_mode(self.normalize)
+        feat_sources = list(feat_sources)
+        if mode == NORM_BEFORE:  # normalize(feat, dim=1) (:8-10, :170-172) through autograd, kernels see NORM_NONE
+            feat_key = feat_key / (torch.linalg.norm(feat_key, dim=1, keepdim=True) + 1e-9)
+            feat_sources = [f / (torch.linalg.norm(f, dim=1, keepdim=True) + 1e-9) for f in feat_sources]
+            mode = NORM_NONE
+        args = dict(intrinsics_key=intrinsics_key, source_to_key_transforms=source_to_key_transforms,
+                    intrinsics_sources=intrinsics_sources, num_sampling_points=num_sampling_points, min_depth=min_depth,
+                    max_depth=max_depth, sampling_invdepths=sampling_invdepths, sampling_type=sampling_type,
+                    plane_range=plane_range, debug=debug)
+        corr, mask = _CorrFunction.apply(self, args, mode, feat_key, *feat_sources)
+        self.corrs = list(corr.unbind(0))
+        self.masks = list(mask.unbind(0))
+        return self.corrs, self.masks, self._inv
+
+    @torch.no_grad()
+    def _backward_impl(self, grad_corr, feat_key, feat_sources, intrinsics_key, source_to_key_transforms,
+                       intrinsics_sources, inv, plane_range, mode, need_key, need_src):
+        """Gradients of ``sum <grad_corr, corr>`` with respect to ``feat_key`` and every ``feat_sources[v]``."""
+        dev = feat_key.device
+        if intrinsics_sources is None:
+            intrinsics_sources = [intrinsics_key] * len(feat_sources)
+        inv_c = _f32c(inv)
+        feat_key = _f32c(feat_key)
+        N, C, h, w = feat_key.shape
+        S = inv_c.shape[1]
+        V = len(feat_sources)
+        s0, s1 = (0, S) if plane_range is None else plane_range
+        Sl = s1 - s0
+        srcs = [_f32c(f) for f in feat_sources]
+        Kk = _f32c(_to_torch(intrinsics_key, dev))
+        Ks = [_f32c(_to_torch(k, dev)) for k in intrinsics_sources]
+        Ts = [_f32c(_to_torch(t, dev)) for t in source_to_key_transforms]
+        hs = [f.shape[2] for f in srcs]
+        ws = [f.shape[3] for f in srcs]
+        grad_corr = _f32c(grad_corr)
+        assert grad_corr.shape == (V, N, Sl, h, w)
+        gkey = torch.empty_like(feat_key) if need_key else None
+        gsrcs = [torch.empty_like(f) if need_src[v] else None for v, f in enumerate(srcs)]
+        lib = _lib.load()
+        nb = lib.rmvd_psweep_bwd_workspace_bytes(N, C, h, w, V, _lib.int_array(hs), _lib.int_array(ws))
+        wsp = _workspace(nb, dev)
+        st = lib.rmvd_psweep_corr_bwd(
+            _lib.ptr(feat_key), _lib.ptr_array(srcs), _lib.ptr(Kk), _lib.ptr_array(Ks), _lib.ptr_array(Ts),
+            _lib.ptr(inv_c), _lib.i64_array(_inv_strides(inv_c, N)), N, C, h, w, V, _lib.int_array(hs),
+            _lib.int_array(ws), S, s0, s1, mode, _lib.ptr(grad_corr), Sl, 0, _lib.ptr(gkey),
+            _lib.ptr_array_opt(gsrcs), _lib.ptr(wsp), wsp.numel(), _lib.stream_ptr())
+        _lib.check(st, "rmvd_psweep_corr_bwd")
+        return gkey, gsrcs
+
+    @torch.no_grad()
+    def _forward_impl(self, feat_key, intrinsics_key, feat_sources, source_to_key_transforms, intrinsics_sources=None,
+                      num_sampling_points=None, min_depth=None, max_depth=None, sampling_invdepths=None,
+                      sampling_type="linear_invdepth", plane_range=None, debug=False, out=None, norm_mode=None):
         self.reset()
         dev = feat_key.device
         if intrinsics_sources is None:  # :441-442
@@ -279,11 +366,13 @@ class PlanesweepCorrelation(nn.Module):
             st = lib.rmvd_psweep_corr_fwd(
                 _lib.ptr(feat_key), _lib.ptr_array(srcs), _lib.ptr(Kk), _lib.ptr_array(Ks), _lib.ptr_array(Ts),
                 _lib.ptr(inv_c), ist, N, C, h, w, V, _lib.int_array(hs), _lib.int_array(ws), S, s0, s1,
-                _corr_norm_mode(self.normalize), _lib.ptr(corr), _lib.ptr(mask), Sl, 0, _lib.ptr(dbg[0]),
+                _corr_norm_mode(self.normalize) if norm_mode is None else norm_mode, _lib.ptr(corr), _lib.ptr(mask), Sl, 0,
+                _lib.ptr(dbg[0]),
                 _lib.ptr(dbg[1]), _lib.ptr(dbg[2]), _lib.ptr(wsp), wsp.numel(), _lib.stream_ptr())
             _lib.check(st, "rmvd_psweep_corr_fwd")
             self.corrs = list(corr.unbind(0))
             self.masks = list(mask.unbind(0))
+            self._stacked = (corr, mask)
             if debug:
                 self.debug = dict(ix0=dbg[0], iy0=dbg[1], geom=dbg[2])
         else:

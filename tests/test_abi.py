@@ -53,6 +53,14 @@ def test_argument_validation_needs_no_device(lib):
     assert lib.rmvd_mvs_variance_fwd(one, one, one, 1, 3, 8, 4, 4, 8, 2, 9, one, 8, 0, null) == -5  # RMVD_E_RANGE
     assert lib.rmvd_warp_grid_fwd(one, one, 1, 1, 4, 4, 4, 4, 7, one, one, null) == -3  # RMVD_E_MODE
     assert lib.rmvd_status_string(-4).decode().startswith("workspace")
+    arr = (ctypes.c_void_p * 1)(1)
+    ints = (ctypes.c_int * 1)(4)
+    st = (ctypes.c_int64 * 4)(0, 1, 0, 0)
+    assert lib.rmvd_psweep_corr_bwd(one, arr, one, arr, arr, one, st, 1, 8, 4, 4, 1, ints, ints, 4, 0, 4, 2, one, 4, 0,
+                                    one, arr, one, 1 << 20, null) == -3             # NORM_BEFORE: caller differentiates
+    assert lib.rmvd_psweep_corr_bwd(one, arr, one, arr, arr, one, st, 1, 8, 4, 4, 1, ints, ints, 4, 0, 4, 1, one, 4, 0,
+                                    one, arr, one, 16, null) == -4                  # RMVD_E_WORKSPACE
+    assert lib.rmvd_psweep_bwd_workspace_bytes(1, 8, 4, 4, 1, ints, ints) == 3 * 512
 
 
 def test_missing_library_fails_loudly(monkeypatch, tmp_path):

@@ -77,3 +77,21 @@ def test_fusion_oracle_against_golden():
         assert np.abs(fc - g["fused_corr"]).max() <= 1e-6 * max(float(np.abs(g["fused_corr"]).max()), 1e-30)
         for v in range(V if V > 1 else 0):
             assert np.abs(w[v] - g[f"weight_{v}"]).max() <= 1e-6
+
+
+BW = cases.backward_cases()
+
+
+@pytest.mark.parametrize("case", BW, ids=[c["name"] for c in BW])
+def test_backward_oracle_matches_reference_autograd(case):
+    """oracle.planesweep_correlation_backward against the gradients of the unmodified reference block
+    (tools/make_bwd_golden.py: torch autograd through TorchCorr.forward on CPU)."""
+    g = load_golden("psbwd", case["name"])
+    S = int(np.asarray(oracle.planesweep_correlation(case["feat_key"], case["intrinsics_key"], case["feat_sources"][:1],
+                                                     case["transforms"][:1], **case["kwargs"])[2]).shape[1])
+    gk, gs = oracle.planesweep_correlation_backward(
+        case["feat_key"], case["intrinsics_key"], case["feat_sources"], case["transforms"], cases.grad_corrs(case, S),
+        case["intrinsics_sources"], normalize=case.get("normalize", "dim"), **case["kwargs"])
+    assert np.abs(gk - g["grad_key"]).max() <= 1e-5 * np.abs(g["grad_key"]).max()
+    for v, x in enumerate(gs):
+        assert np.abs(x - g[f"grad_src_{v}"]).max() <= 1e-5 * max(np.abs(g[f"grad_src_{v}"]).max(), 1e-30)

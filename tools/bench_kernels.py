@@ -75,6 +75,16 @@ def main():
                                   ("cfg4_eth3d_1frame_v2", syn.CFG4, 2, 1), ("cfg4_eth3d_1frame_v10", syn.CFG4, 10, 1)):
         kw, nb, vox = psweep_case(cfg, V, frames)
         add(f"psweep_corr_{label}", (lambda kw=kw: blk(**kw)), nb, vox, "voxels")
+    # backward of the correlation at cfg2, one frame: reads key + sources + grad_corr, writes their gradients
+    kwb, _, voxb = psweep_case(syn.CFG2, 2, 1)
+    kwb["feat_key"].requires_grad_(True)
+    for f in kwb["feat_sources"]:
+        f.requires_grad_(True)
+    bcorrs = blk(**kwb)[0]
+    bg = [torch.randn_like(x) for x in bcorrs]
+    bin_ = [kwb["feat_key"]] + kwb["feat_sources"]
+    add("psweep_corr_bwd_cfg2_kitti_1frame", lambda: torch.autograd.grad(bcorrs, bin_, bg, retain_graph=True),
+        2 * 4 * 256 * 7680 * 3 + 4 * voxb, voxb, "voxels")
     c3 = syn.CFG3
     m = syn.mvs_inputs(c3["h"], c3["w"], c3["C"], c3["V"], c3["D"])
     feats, proj, depth, cost = cu(m["feats"]), cu(m["proj"]), cu(m["depth"]), cu(m["cost"])

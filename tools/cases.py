@@ -94,6 +94,33 @@ def planesweep_cases(include_large=True):
     return cases
 
 
+BACKWARD_CASE_NAMES = ("identity_6x10", "stereo_x_12x20", "forward_12x20", "behind_12x20", "roll_pitch_12x20",
+                       "src_res_differs", "batch2_ranges", "linear_depth", "explicit_inv_rank4", "inv_zero_negative",
+                       "normalize_False", "normalize_True", "normalize_before", "odd_sizes", "band_stereo_c32",
+                       "band_roll_c64", "band_rot90_behind_c32", "band_srcres_batch2_c32")
+
+
+def backward_cases():
+    """Cases of the correlation backward: a subset of the forward zoo plus channel counts that take
+    the vectorised kernel (C = 128 k).  ``grad_corrs(case)`` gives the seeded upstream gradients."""
+    T = syn.make_transform
+    by_name = {c["name"]: c for c in planesweep_cases(include_large=False)}
+    out = [by_name[n] for n in BACKWARD_CASE_NAMES]
+    out.append(_ps("bwd_c128_stereo", 12, 20, 128, [T(t=(-0.54, 0, 0)), T(syn.rot_y(2), (0.54, 0, 0.03))], S=24, seed=70))
+    out.append(_ps("bwd_c256_kitti_small", 12, 40, 256, syn.kitti_like_views(2), S=48, seed=71))
+    out.append(_ps("bwd_c128_batch2_srcres", 10, 18, 128, [T(syn.rot_z(5), (0.3, 0.02, 0.01), n=2)], hs=8, ws=13, n=2, S=20,
+                   seed=72))
+    return out
+
+
+def grad_corrs(case, S):
+    """Seeded upstream gradients, one ``[N,S,h,w]`` array per source view."""
+    import zlib
+    n, _, h, w = case["feat_key"].shape
+    rng = np.random.default_rng(zlib.crc32(case["name"].encode()))
+    return [rng.standard_normal((n, S, h, w)).astype(np.float32) for _ in case["feat_sources"]]
+
+
 def mvs_cases(include_large=True):
     cases = []
     cases.append(dict(name="mvs_small", **syn.mvs_inputs(12, 16, 8, 3, 8, seed=40, fx=20.0, min_depth=0.5, max_depth=1.5)))
