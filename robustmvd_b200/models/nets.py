@@ -76,7 +76,9 @@ class LearnedFusion(nn.Module):
         if len(corrs) == 1:
             self.fused_corr, self.fused_mask = corrs[0], masks[0]
             return self.fused_corr, self.fused_mask
-        if corrs[0].is_cuda:
+        needs_grad = torch.is_grad_enabled() and (any(c.requires_grad for c in corrs) or
+                                                  any(p.requires_grad for p in self.parameters()))
+        if corrs[0].is_cuda and not needs_grad:   # training differentiates the torch expression below (forward-only kernel)
             return self._forward_cuda(corrs, masks)
         logits = torch.stack([self.corr_to_view_weight(c) for c in corrs], 0)  # V,N,1,h,w
         weights = F.softmax(logits, dim=0) + 1e-9

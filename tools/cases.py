@@ -146,6 +146,18 @@ MODEL_CASES = {
 }
 
 
+MODEL_GRAD_CASES = ("robust_mvd_batch2",)
+MODEL_GRAD_PARAMS = ("encoder.conv1.0.weight", "encoder.conv3.0.weight", "encoder.conv3.0.bias",
+                     "fusion_block.corr_to_view_weight.0.weight", "fusion_enc_block.conv3_1.0.weight",
+                     "context_encoder.conv_redir.0.weight", "decoder.pred_5.0.weight")
+MODEL_GRAD_STRIDE = 7
+
+
+def model_grad_loss(aux):
+    """Scalar the model-gradient goldens differentiate (same expression on both sides)."""
+    return aux["invdepth"].mean() + 0.1 * aux["invdepth_log_b"].mean()
+
+
 def prepare_model_for_case(model, model_name):
     """Test-only weight tweak applied identically to the reference model and to the candidate."""
     import torch
