@@ -17,6 +17,9 @@
 // CTA = 32 consecutive key pixels of one (view, sample); warp = 4 of those pixels, lanes split the channel axis.
 // Consecutive planes of a pixel that fall into the same source cell are merged before touching memory: the four
 // coefficients sum_s g' w_k are accumulated in registers and one gather + one scatter is issued per run of planes.
+#include <cstdlib>
+#include <cstring>
+
 #include "psweep.cuh"
 
 namespace rmvd {
@@ -34,6 +37,7 @@ struct PsweepBwdArgs {
   long long ist[4];
   int hs[kMaxViews], ws[kMaxViews];
   int N, C, h, w, S, s_begin, s_end, norm, out_S, out_s0, v0;
+  int planes0, rmax;            // tiled kernel: planes per chunk to start from, texels of a band box
 };
 
 __device__ __forceinline__ void red_add4(float* p, const float4 v) {
@@ -198,6 +202,188 @@ __global__ void __launch_bounds__(kWarps * 32) psweep_corr_bwd_kernel(const Pswe
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Tiled form (C <= 256), the one the launcher prefers.  Per (tile of 32 key pixels, chunk of planes) the gradient with
+// respect to the correlation matrix restricted to the chunk's band,
+//   dG[p][t] = sum_{s,k : t_k(p,s) = t} g'(p,s) w_k(p,s),
+// is built in shared memory over the bounding box of the band (<= kBwdRMax texels), and both gradients become small dense
+// contractions over it:  d key[p][c] += sum_t dG[p][t] src[t][c]   and   d src[t][c] += sum_p dG[p][t] key[p][c].
+// A source texel is read once and reduced into d src once per (tile, chunk) instead of once per (pixel, run, corner):
+// ~12x fewer bytes through the L2 reduction path at the KITTI shape.  Thread = channel: 32 key values and 32 key-gradient
+// accumulators in registers, dG column (32 floats) broadcast from shared memory, texel rows of the channels-last maps
+// coalesced.  A chunk whose box does not fit is retried with half the planes, a single plane with fewer pixels
+// (one pixel x one plane = 4 texels always fits).
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kBwdRMax = 320;   // texels of a band box (40 KB of dG + flags)
+constexpr int kBwdPlanes = 64;  // planes per chunk to start from
+
+struct BwdSample {
+  bool valid;
+  int x0c, y0c, dx, dy;
+  float nw, ne, sw, se;  // weights times g'
+};
+
+__device__ __forceinline__ BwdSample bwd_sample(const PsweepBwdArgs& A, const Epi& E, int n, int v, int p, int s, int hs, int ws,
+                                                float scale, size_t g_base, bool need_g) {
+  BwdSample r;
+  r.valid = false;
+  const int P = A.h * A.w;
+  if (p >= P) return r;
+  const int yi = p / A.w, xi = p - yi * A.w;
+  const EpiPix ep = epi_pixel(E, xi, yi);
+  const float d = A.invd[n * A.ist[0] + s * A.ist[1] + yi * A.ist[2] + xi * A.ist[3]];
+  float us, vs;
+  bool geom;
+  epi_sample(E, ep, d, us, vs, geom);
+  const Bilinear b = bilinear_setup(pix_to_unnorm(us, ws), pix_to_unnorm(vs, hs), hs, ws);
+  r.valid = sampling_mask(b.msum) && geom;
+  if (!r.valid) return r;
+  const int x0 = sat_index(b.x0f, ws), y0 = sat_index(b.y0f, hs);
+  r.x0c = clampi(x0, 0, ws - 1);
+  r.y0c = clampi(y0, 0, hs - 1);
+  r.dx = clampi(x0 + 1, 0, ws - 1) - r.x0c;
+  r.dy = clampi(y0 + 1, 0, hs - 1) - r.y0c;
+  if (need_g) {
+    const float g = fdiv(A.gcorr[(g_base + A.out_s0 + (s - A.s_begin)) * P + p], scale);
+    r.nw = b.nw * g; r.ne = b.ne * g; r.sw = b.sw * g; r.se = b.se * g;
+  }
+  return r;
+}
+
+__global__ void __launch_bounds__(256, 2) psweep_corr_bwd_tile_kernel(const PsweepBwdArgs A) {
+  extern __shared__ __align__(16) float smem[];
+  float* s_dg = smem;                                        // [rmax][32]  dG, texel-major
+  int* s_flag = reinterpret_cast<int*>(s_dg + A.rmax * 32);    // [rmax] texel touched
+  __shared__ int s_box[4];                                   // xmin, xmax, ymin, ymax
+
+  const int v = blockIdx.z, n = blockIdx.y;
+  const int C = A.C, P = A.h * A.w;
+  const int p0 = blockIdx.x * kTilePx;
+  const int t = threadIdx.x, lane = t & 31;
+  const int hs = A.hs[v], ws = A.ws[v];
+  const float* __restrict__ src = A.src[v] + (size_t)n * hs * ws * C;
+  float* __restrict__ gsrc = A.gsrc[v] ? A.gsrc[v] + (size_t)n * hs * ws * C : nullptr;
+  const bool ch = t < C;        // this thread owns channel t
+  const bool do_key = A.gkey != nullptr;
+
+  float key[32], gk[32];
+  {
+    const float* kp = A.key + ((size_t)n * C + (ch ? t : 0)) * P + p0;
+#pragma unroll
+    for (int p = 0; p < 32; ++p) {
+      key[p] = (ch && p0 + p < P) ? __ldg(kp + p) : 0.f;
+      gk[p] = 0.f;
+    }
+  }
+  const Epi E = epi_from_calib(A.Kk + n * 9, A.Ks[v] + n * 9, A.T[v] + n * 16, A.h, A.w, hs, ws);
+  const float scale = (A.norm == RMVD_NORM_DIM) ? sqrtf((float)C) : 1.0f;
+  const size_t g_base = ((size_t)(A.v0 + v) * A.N + n) * A.out_S;
+
+  // bounding box of the clamped corners of the valid samples of (planes [sc, sc+ns), pixels [pa, pa+npx)); false: no sample
+  auto find_box = [&](int sc, int ns, int pa, int npx) -> bool {
+    __syncthreads();
+    if (t == 0) { s_box[0] = 1 << 30; s_box[1] = -1; s_box[2] = 1 << 30; s_box[3] = -1; }
+    __syncthreads();
+    int xlo = 1 << 30, xhi = -1, ylo = 1 << 30, yhi = -1;
+    for (int idx = t; idx < npx * ns; idx += 256) {
+      const int q = idx % npx, sp = idx / npx;
+      const BwdSample r = bwd_sample(A, E, n, v, p0 + pa + q, sc + sp, hs, ws, scale, g_base, false);
+      if (r.valid) {
+        xlo = min(xlo, r.x0c); xhi = max(xhi, r.x0c + r.dx);
+        ylo = min(ylo, r.y0c); yhi = max(yhi, r.y0c + r.dy);
+      }
+    }
+    xlo = __reduce_min_sync(kFullMask, xlo); xhi = __reduce_max_sync(kFullMask, xhi);
+    ylo = __reduce_min_sync(kFullMask, ylo); yhi = __reduce_max_sync(kFullMask, yhi);
+    if (lane == 0 && xhi >= 0) {
+      atomicMin(&s_box[0], xlo); atomicMax(&s_box[1], xhi);
+      atomicMin(&s_box[2], ylo); atomicMax(&s_box[3], yhi);
+    }
+    __syncthreads();
+    return s_box[1] >= 0;
+  };
+
+  // dG over the box, then the two contractions
+  auto process = [&](int sc, int ns, int pa, int npx) {
+    const int bx = s_box[0], by = s_box[2];
+    const int bw = s_box[1] - bx + 1, bh = s_box[3] - by + 1;
+    const int R = bw * bh;
+    for (int i = t; i < R * 32; i += 256) s_dg[i] = 0.f;
+    for (int i = t; i < R; i += 256) s_flag[i] = 0;
+    __syncthreads();
+    for (int idx = t; idx < npx * ns; idx += 256) {
+      const int q = idx % npx, sp = idx / npx;
+      const BwdSample r = bwd_sample(A, E, n, v, p0 + pa + q, sc + sp, hs, ws, scale, g_base, true);
+      if (r.valid) {
+        const int col = pa + q;
+        const int t_nw = (r.y0c - by) * bw + (r.x0c - bx);
+        const int t_ne = t_nw + r.dx, t_sw = t_nw + r.dy * bw, t_se = t_sw + r.dx;
+        if (r.nw != 0.f) { atomicAdd(&s_dg[t_nw * 32 + col], r.nw); s_flag[t_nw] = 1; }
+        if (r.ne != 0.f) { atomicAdd(&s_dg[t_ne * 32 + col], r.ne); s_flag[t_ne] = 1; }
+        if (r.sw != 0.f) { atomicAdd(&s_dg[t_sw * 32 + col], r.sw); s_flag[t_sw] = 1; }
+        if (r.se != 0.f) { atomicAdd(&s_dg[t_se * 32 + col], r.se); s_flag[t_se] = 1; }
+      }
+    }
+    __syncthreads();
+    if (ch) {
+      for (int ty = 0; ty < bh; ++ty) {
+        const size_t row = ((size_t)(by + ty) * ws + bx) * C + t;
+        for (int tx = 0; tx < bw; ++tx) {
+          const int tl = ty * bw + tx;
+          if (!s_flag[tl]) continue;  // CTA-uniform
+          const size_t o = row + (size_t)tx * C;
+          const float sv = do_key ? __ldg(src + o) : 0.f;
+          const float4* dg = reinterpret_cast<const float4*>(s_dg + tl * 32);
+          float acc = 0.f;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const float4 d = dg[k];
+            gk[4 * k + 0] = fmaf(d.x, sv, gk[4 * k + 0]); acc = fmaf(d.x, key[4 * k + 0], acc);
+            gk[4 * k + 1] = fmaf(d.y, sv, gk[4 * k + 1]); acc = fmaf(d.y, key[4 * k + 1], acc);
+            gk[4 * k + 2] = fmaf(d.z, sv, gk[4 * k + 2]); acc = fmaf(d.z, key[4 * k + 2], acc);
+            gk[4 * k + 3] = fmaf(d.w, sv, gk[4 * k + 3]); acc = fmaf(d.w, key[4 * k + 3], acc);
+          }
+          if (gsrc) atomicAdd(gsrc + o, acc);  // RED, 128-byte rows per warp
+        }
+      }
+    }
+  };
+
+  int ns_try = A.planes0;
+  const long long rmax = A.rmax;
+  int sc = A.s_begin;
+  while (sc < A.s_end) {
+    const int ns = min(ns_try, A.s_end - sc);
+    if (!find_box(sc, ns, 0, kTilePx)) { sc += ns; continue; }                      // no valid sample in the chunk
+    const long long area = (long long)(s_box[1] - s_box[0] + 1) * (s_box[3] - s_box[2] + 1);
+    if (area <= rmax) {
+      process(sc, ns, 0, kTilePx);
+      sc += ns;
+      continue;
+    }
+    if (ns > 1) { ns_try = ns / 2; continue; }                                      // retry with half the planes
+    for (int pa = 0; pa < kTilePx;) {                                               // one plane: split the pixels
+      int npx = min(16, kTilePx - pa);
+      bool any;
+      for (;;) {
+        any = find_box(sc, 1, pa, npx);
+        if (!any || (long long)(s_box[1] - s_box[0] + 1) * (s_box[3] - s_box[2] + 1) <= rmax || npx == 1) break;
+        npx >>= 1;
+      }
+      if (any) process(sc, 1, pa, npx);
+      pa += npx;
+    }
+    sc += 1;
+  }
+
+  if (do_key && ch) {  // several views (CTAs of grid.z) add into the zeroed NCHW key gradient
+    float* gp = A.gkey + ((size_t)n * C + t) * P + p0;
+#pragma unroll
+    for (int p = 0; p < 32; ++p)
+      if (p0 + p < P && gk[p] != 0.f) atomicAdd(gp + p, gk[p]);
+  }
+}
+
 // channels-last [N,P,C] <-> NCHW [N,C,P] transposes (32 x 32 tiles through shared memory)
 __global__ void __launch_bounds__(256) bwd_nchw_to_nhwc_kernel(const float* __restrict__ src, float* __restrict__ dst,
                                                                int C, int P) {
@@ -287,19 +473,23 @@ extern "C" int rmvd_psweep_corr_bwd(const float* feat_key, const float* const* f
   const int P = h * w;
   const unsigned cb = (unsigned)((C + 31) / 32);
 
+  // kernel choice: tiled form for C <= 256; RMVD_PSWEEP_BWD_KERNEL=direct|tile restricts it (A/B runs only)
+  const char* force = getenv("RMVD_PSWEEP_BWD_KERNEL");
+  const bool tile = (C <= 256) && !(force && strcmp(force, "direct") == 0);
+
   char* wsp = (char*)workspace;
   float* gkey_cl = (float*)wsp;
   wsp += slot_bytes(N, C, P);
   cudaError_t e;
-  if (grad_key) {
-    e = cudaMemsetAsync(gkey_cl, 0, (size_t)N * C * P * sizeof(float), st);
+  if (grad_key) {  // the tiled kernel reduces straight into the NCHW output, the direct one into a channels-last copy
+    e = cudaMemsetAsync(tile ? grad_key : gkey_cl, 0, (size_t)N * C * P * sizeof(float), st);
     if (e != cudaSuccess) return (int)e;
   }
   for (int v0 = 0; v0 < V; v0 += kMaxViews) {
     const int nv = (V - v0 < kMaxViews) ? (V - v0) : kMaxViews;
     PsweepBwdArgs A{};
     A.key = feat_key; A.Kk = intrinsics_key; A.invd = invdepths; A.gcorr = grad_corr;
-    A.gkey = grad_key ? gkey_cl : nullptr;
+    A.gkey = grad_key ? (tile ? grad_key : gkey_cl) : nullptr;
     for (int k = 0; k < 4; ++k) A.ist[k] = inv_stride[k];
     float* g_cl[kMaxViews];
     for (int j = 0; j < nv; ++j) {
@@ -326,6 +516,20 @@ extern "C" int rmvd_psweep_corr_bwd(const float* feat_key, const float* const* f
     A.N = N; A.C = C; A.h = h; A.w = w; A.S = S; A.s_begin = s_begin; A.s_end = s_end;
     A.norm = normalize_mode; A.out_S = out_S; A.out_s0 = out_s0; A.v0 = v0;
     int rc;
+    if (tile) {
+      // RMVD_BWD_PLANES / RMVD_BWD_RMAX: tuning overrides (A/B runs only)
+      const char* ep = getenv("RMVD_BWD_PLANES");
+      const char* er = getenv("RMVD_BWD_RMAX");
+      A.planes0 = ep ? atoi(ep) : kBwdPlanes;
+      A.rmax = er ? atoi(er) : kBwdRMax;
+      if (A.planes0 < 1 || A.rmax < 4 || A.rmax > 1600) return RMVD_E_MODE;
+      const size_t smem = (size_t)A.rmax * 33 * sizeof(float);
+      e = cudaFuncSetAttribute(psweep_corr_bwd_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return (int)e;
+      dim3 grid((P + kTilePx - 1) / kTilePx, N, nv);
+      psweep_corr_bwd_tile_kernel<<<grid, 256, smem, st>>>(A);
+      rc = (int)cudaGetLastError();
+    } else
     switch (C) {
       case 128: rc = launch_bwd<1>(A, nv, st); break;
       case 256: rc = launch_bwd<2>(A, nv, st); break;
@@ -343,7 +547,7 @@ extern "C" int rmvd_psweep_corr_bwd(const float* feat_key, const float* const* f
       if ((e = cudaGetLastError()) != cudaSuccess) return (int)e;
     }
   }
-  if (grad_key) {
+  if (grad_key && !tile) {
     dim3 g((P + 31) / 32, cb, N);
     bwd_nhwc_to_nchw_kernel<<<g, 256, 0, st>>>(gkey_cl, grad_key, C, P);
     if ((e = cudaGetLastError()) != cudaSuccess) return (int)e;

@@ -76,6 +76,29 @@ def test_backward_matches_oracle_and_reference_autograd(cuda_lib, case):
         assert _rel(corrs[v], oc[v]) <= TOL
 
 
+@pytest.mark.parametrize("name", ["bwd_c128_stereo", "bwd_c256_kitti_small", "odd_sizes", "band_srcres_batch2_c32", "bwd_roll40_c32"])
+def test_direct_kernel_matches_reference_autograd(cuda_lib, monkeypatch, name):
+    """The general direct kernel (C > 256 in production) forced onto shapes the tiled kernel normally takes."""
+    monkeypatch.setenv("RMVD_PSWEEP_BWD_KERNEL", "direct")
+    case = [c for c in BW if c["name"] == name][0]
+    grads, _, _, _ = _run_backward(case)
+    g = load_golden("psbwd", name)
+    assert _rel(grads[0], g["grad_key"]) <= TOL
+    for v in range(len(grads) - 1):
+        assert _rel(grads[1 + v], g[f"grad_src_{v}"]) <= TOL
+
+
+def test_wide_channel_count_takes_the_direct_kernel(cuda_lib):
+    """C = 384 > 256: the direct vectorised kernel; checked against the oracle."""
+    T = syn.make_transform
+    case = cases._ps("bwd_c384", 6, 12, 384, [T(syn.rot_y(2), (0.3, 0, 0.02))], S=8, seed=91)
+    grads, _, _, S = _run_backward(case)
+    ogk, ogs = oracle.planesweep_correlation_backward(
+        case["feat_key"], case["intrinsics_key"], case["feat_sources"], case["transforms"], cases.grad_corrs(case, S),
+        **case["kwargs"])
+    assert _rel(grads[0], ogk) <= TOL and _rel(grads[1], ogs[0]) <= TOL
+
+
 def test_only_requested_gradients_are_computed(cuda_lib):
     case = [c for c in BW if c["name"] == "bwd_c128_stereo"][0]
     full, _, _, _ = _run_backward(case)

@@ -110,6 +110,10 @@ def backward_cases():
     out.append(_ps("bwd_c256_kitti_small", 12, 40, 256, syn.kitti_like_views(2), S=48, seed=71))
     out.append(_ps("bwd_c128_batch2_srcres", 10, 18, 128, [T(syn.rot_z(5), (0.3, 0.02, 0.01), n=2)], hs=8, ws=13, n=2, S=20,
                    seed=72))
+    # source map 12x finer than the key map: one plane of a 32-pixel tile spans > 320 texels (pixel-split path of the tiled
+    # kernel); and a strongly rolled view whose band boxes only fit for a few planes (plane-halving path)
+    out.append(_ps("bwd_zoom_split", 6, 32, 16, [T(syn.rot_y(1), (0.2, 0.01, 0.0))], hs=40, ws=400, S=10, seed=73))
+    out.append(_ps("bwd_roll40_c32", 16, 64, 32, [T(syn.rot_z(40) @ syn.rot_x(4), (0.4, -0.1, 0.05))], S=64, seed=74))
     return out
 
 
