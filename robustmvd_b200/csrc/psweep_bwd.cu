@@ -38,6 +38,7 @@ struct PsweepBwdArgs {
   int hs[kMaxViews], ws[kMaxViews];
   int N, C, h, w, S, s_begin, s_end, norm, out_S, out_s0, v0;
   int planes0, rmax;            // tiled kernel: planes per chunk to start from, texels of a band box
+  int zsplit;                   // tiled kernel: CTAs per tile, each sweeping 1/zsplit of the planes (fills the last wave)
 };
 
 __device__ __forceinline__ void red_add4(float* p, const float4 v) {
@@ -214,8 +215,8 @@ __global__ void __launch_bounds__(kWarps * 32) psweep_corr_bwd_kernel(const Pswe
 // coalesced.  A chunk whose box does not fit is retried with half the planes, a single plane with fewer pixels
 // (one pixel x one plane = 4 texels always fits).
 // ---------------------------------------------------------------------------------------------------------
-constexpr int kBwdRMax = 320;   // texels of a band box (40 KB of dG + flags)
-constexpr int kBwdPlanes = 64;  // planes per chunk to start from
+constexpr int kBwdRMax = 512;   // texels of a band box (72 KB of dG, texel list and flags)
+constexpr int kBwdPlanes = 128; // planes per chunk to start from (measured: 32 -> 0.89, 64 -> 0.69, 128 -> 0.63 ms at cfg2)
 
 struct BwdSample {
   bool valid;
@@ -254,11 +255,16 @@ __global__ void __launch_bounds__(256, 2) psweep_corr_bwd_tile_kernel(const Pswe
   extern __shared__ __align__(16) float smem[];
   float* s_dg = smem;                                        // [rmax][32]  dG, texel-major
   int* s_flag = reinterpret_cast<int*>(s_dg + A.rmax * 32);    // [rmax] texel touched
+  int2* s_list = reinterpret_cast<int2*>(s_flag + A.rmax);     // [rmax] touched texels: (box index, offset in the source map)
   __shared__ int s_box[4];                                   // xmin, xmax, ymin, ymax
+  __shared__ int s_count;
 
   const int v = blockIdx.z, n = blockIdx.y;
   const int C = A.C, P = A.h * A.w;
-  const int p0 = blockIdx.x * kTilePx;
+  const int p0 = (blockIdx.x / A.zsplit) * kTilePx;
+  const int zlen = (A.s_end - A.s_begin + A.zsplit - 1) / A.zsplit;
+  const int z_begin = A.s_begin + (blockIdx.x % A.zsplit) * zlen;
+  const int z_end = min(A.s_end, z_begin + zlen);
   const int t = threadIdx.x, lane = t & 31;
   const int hs = A.hs[v], ws = A.ws[v];
   const float* __restrict__ src = A.src[v] + (size_t)n * hs * ws * C;
@@ -310,6 +316,7 @@ __global__ void __launch_bounds__(256, 2) psweep_corr_bwd_tile_kernel(const Pswe
     const int R = bw * bh;
     for (int i = t; i < R * 32; i += 256) s_dg[i] = 0.f;
     for (int i = t; i < R; i += 256) s_flag[i] = 0;
+    if (t == 0) s_count = 0;
     __syncthreads();
     for (int idx = t; idx < npx * ns; idx += 256) {
       const int q = idx % npx, sp = idx / npx;
@@ -325,35 +332,48 @@ __global__ void __launch_bounds__(256, 2) psweep_corr_bwd_tile_kernel(const Pswe
       }
     }
     __syncthreads();
+    for (int i0 = 0; i0 < R; i0 += 256) {  // compact the touched texels of the box into a list (one shared atomic per warp)
+      const int i = i0 + t;
+      const bool on = i < R && s_flag[i] != 0;
+      const unsigned bal = __ballot_sync(kFullMask, on);
+      int base = 0;
+      if (lane == 0 && bal) base = atomicAdd(&s_count, __popc(bal));
+      base = __shfl_sync(kFullMask, base, 0);
+      if (on) {
+        const int ty = i / bw, tx = i - ty * bw;
+        s_list[base + __popc(bal & ((1u << lane) - 1u))] = make_int2(i, (by + ty) * ws + bx + tx);
+      }
+    }
+    __syncthreads();
     if (ch) {
-      for (int ty = 0; ty < bh; ++ty) {
-        const size_t row = ((size_t)(by + ty) * ws + bx) * C + t;
-        for (int tx = 0; tx < bw; ++tx) {
-          const int tl = ty * bw + tx;
-          if (!s_flag[tl]) continue;  // CTA-uniform
-          const size_t o = row + (size_t)tx * C;
-          const float sv = do_key ? __ldg(src + o) : 0.f;
-          const float4* dg = reinterpret_cast<const float4*>(s_dg + tl * 32);
-          float acc = 0.f;
+      const int cnt = s_count;  // touched texels of the box
+      int2 e = cnt > 0 ? s_list[0] : make_int2(0, 0);
+      float sv = (do_key && cnt > 0) ? __ldg(src + (size_t)e.y * C + t) : 0.f;
+      for (int i = 0; i < cnt; ++i) {
+        const int2 en = (i + 1 < cnt) ? s_list[i + 1] : e;
+        const float svn = do_key ? __ldg(src + (size_t)en.y * C + t) : 0.f;  // next texel's value under this one's FMAs
+        const float4* dg = reinterpret_cast<const float4*>(s_dg + e.x * 32);
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);   // four independent chains
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            const float4 d = dg[k];
-            gk[4 * k + 0] = fmaf(d.x, sv, gk[4 * k + 0]); acc = fmaf(d.x, key[4 * k + 0], acc);
-            gk[4 * k + 1] = fmaf(d.y, sv, gk[4 * k + 1]); acc = fmaf(d.y, key[4 * k + 1], acc);
-            gk[4 * k + 2] = fmaf(d.z, sv, gk[4 * k + 2]); acc = fmaf(d.z, key[4 * k + 2], acc);
-            gk[4 * k + 3] = fmaf(d.w, sv, gk[4 * k + 3]); acc = fmaf(d.w, key[4 * k + 3], acc);
-          }
-          if (gsrc) atomicAdd(gsrc + o, acc);  // RED, 128-byte rows per warp
+        for (int k = 0; k < 8; ++k) {
+          const float4 d = dg[k];
+          gk[4 * k + 0] = fmaf(d.x, sv, gk[4 * k + 0]); acc.x = fmaf(d.x, key[4 * k + 0], acc.x);
+          gk[4 * k + 1] = fmaf(d.y, sv, gk[4 * k + 1]); acc.y = fmaf(d.y, key[4 * k + 1], acc.y);
+          gk[4 * k + 2] = fmaf(d.z, sv, gk[4 * k + 2]); acc.z = fmaf(d.z, key[4 * k + 2], acc.z);
+          gk[4 * k + 3] = fmaf(d.w, sv, gk[4 * k + 3]); acc.w = fmaf(d.w, key[4 * k + 3], acc.w);
         }
+        if (gsrc) atomicAdd(gsrc + (size_t)e.y * C + t, (acc.x + acc.y) + (acc.z + acc.w));  // RED, 128-byte rows per warp
+        e = en;
+        sv = svn;
       }
     }
   };
 
   int ns_try = A.planes0;
   const long long rmax = A.rmax;
-  int sc = A.s_begin;
-  while (sc < A.s_end) {
-    const int ns = min(ns_try, A.s_end - sc);
+  int sc = z_begin;
+  while (sc < z_end) {
+    const int ns = min(ns_try, z_end - sc);
     if (!find_box(sc, ns, 0, kTilePx)) { sc += ns; continue; }                      // no valid sample in the chunk
     const long long area = (long long)(s_box[1] - s_box[0] + 1) * (s_box[3] - s_box[2] + 1);
     if (area <= rmax) {
@@ -521,12 +541,24 @@ extern "C" int rmvd_psweep_corr_bwd(const float* feat_key, const float* const* f
       const char* ep = getenv("RMVD_BWD_PLANES");
       const char* er = getenv("RMVD_BWD_RMAX");
       A.planes0 = ep ? atoi(ep) : kBwdPlanes;
-      A.rmax = er ? atoi(er) : kBwdRMax;
+      A.rmax = (er ? atoi(er) : kBwdRMax) & ~1;   // even: the texel list behind the flags is 8-byte aligned
       if (A.planes0 < 1 || A.rmax < 4 || A.rmax > 1600) return RMVD_E_MODE;
-      const size_t smem = (size_t)A.rmax * 33 * sizeof(float);
+      const size_t smem = (size_t)A.rmax * 35 * sizeof(float);
       e = cudaFuncSetAttribute(psweep_corr_bwd_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (e != cudaSuccess) return (int)e;
-      dim3 grid((P + kTilePx - 1) / kTilePx, N, nv);
+      // CTAs per tile
+      int dev = 0, sms = 148;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      const long long tiles = (long long)((P + kTilePx - 1) / kTilePx) * N * nv, slots = 2LL * sms;
+      const char* ez = getenv("RMVD_BWD_ZSPLIT");
+      // fewer than ~3 waves of tiles leave the last wave ragged: halve / third the plane range per CTA (measured at cfg2, one
+      // frame = 1.6 waves: 1 -> 0.68, 2 -> 0.62, 3 -> 0.66, 4 -> 0.68, 8 -> 0.87 ms; every split re-reads the tile-wide band)
+      int zs = 1;
+      while (zs < 3 && tiles * zs < 3 * slots && (s_end - s_begin) / (zs + 1) >= 64) ++zs;
+      A.zsplit = ez ? atoi(ez) : zs;
+      if (A.zsplit < 1 || A.zsplit > 64) return RMVD_E_MODE;
+      dim3 grid((unsigned)(((P + kTilePx - 1) / kTilePx) * A.zsplit), N, nv);
       psweep_corr_bwd_tile_kernel<<<grid, 256, smem, st>>>(A);
       rc = (int)cudaGetLastError();
     } else

@@ -85,6 +85,15 @@ def main():
     bin_ = [kwb["feat_key"]] + kwb["feat_sources"]
     add("psweep_corr_bwd_cfg2_kitti_1frame", lambda: torch.autograd.grad(bcorrs, bin_, bg, retain_graph=True),
         2 * 4 * 256 * 7680 * 3 + 4 * voxb, voxb, "voxels")
+    kwb8, _, voxb8 = psweep_case(syn.CFG2, 2, 8)
+    kwb8["feat_key"].requires_grad_(True)
+    for f in kwb8["feat_sources"]:
+        f.requires_grad_(True)
+    bcorrs8 = blk(**kwb8)[0]
+    bg8 = [torch.randn_like(x) for x in bcorrs8]
+    bin8 = [kwb8["feat_key"]] + kwb8["feat_sources"]
+    add("psweep_corr_bwd_cfg2_kitti_8frames", lambda: torch.autograd.grad(bcorrs8, bin8, bg8, retain_graph=True),
+        8 * (2 * 4 * 256 * 7680 * 3) + 4 * voxb8, voxb8, "voxels")
     c3 = syn.CFG3
     m = syn.mvs_inputs(c3["h"], c3["w"], c3["C"], c3["V"], c3["D"])
     feats, proj, depth, cost = cu(m["feats"]), cu(m["proj"]), cu(m["depth"]), cu(m["cost"])

@@ -26,4 +26,8 @@ VCMD="python tools/bench_kernels.py --reps 1 --only mvs_variance"
 timeout 300 $VCMD > $OUT/plain_var.log 2>&1 &&
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:mvs_variance_tile -s 2 -c 1 -o $OUT/prof_var $VCMD > $OUT/ncu_var.log 2>&1
 echo "ncu var rc=$?"
+WCMD="python tools/bench_kernels.py --reps 1 --only psweep_corr_bwd_cfg2_kitti_1frame"
+timeout 300 $WCMD > $OUT/plain_bwd.log 2>&1 &&
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:psweep_corr_bwd_tile -s 1 -c 1 -o $OUT/prof_bwd $WCMD > $OUT/ncu_bwd.log 2>&1
+echo "ncu bwd rc=$?"
 ls -la $OUT
