@@ -181,6 +181,23 @@ int rmvd_softargmax_confidence(const float* cost_slab, const float* merged, int 
 int rmvd_soft_argmin_fwd(const float* volume, int B, int D, int h, int w, float window, float* prob,
                          float* expected_index, float* prob_map, float* entropy, void* stream);
 
+/* ---------------------------------------------------------------------------------------------------
+ * Vis-MVSNet family
+ * ------------------------------------------------------------------------------------------------- */
+
+/*
+ * build_cost_volume + groupwise_correlation (vis_mvsnet_singlestage.py:86-122, :230-242; blocks/utils.py:71-89, :155-189)
+ * fused: cost[n,g,d,y,x] = sum over the channels of group g of ref[n,c,y,x] * homography_warping(src, H[n,d])[n,c,y,x];
+ * the warped volume is never written.  H holds one 3x3 homography (9 floats, row-major) per (n, d) or per (n, d, y, x):
+ * element (n,d,y,x) starts at H + n*h_stride[0] + d*h_stride[1] + y*h_stride[2] + x*h_stride[3] (0 for broadcast dims),
+ * i.e. the output of get_homographies (blocks/utils.py:96-150) as it lies.  ref, src [N,C,h,w]; cost [N,groups,D,h,w].
+ */
+int rmvd_homography_groupcorr_fwd(const float* ref, const float* src, const float* H, const int64_t* h_stride_host, int N,
+                                  int C, int h, int w, int D, int groups, float* cost, void* stream);
+/* homography_warping alone (blocks/utils.py:179-189): warped [N,C,D,h,w] (D = 1 for a single homography per sample). */
+int rmvd_homography_warp_fwd(const float* src, const float* H, const int64_t* h_stride_host, int N, int C, int h, int w,
+                             int D, float* warped, void* stream);
+
 /*
  * Learned view fusion, elementwise part (rmvd/models/blocks/learned_fusion.py:33-47): replaces
  * softmax(stack(view_weights), 0) + 1e-9, view_weight * mask, the two stacks / products / sums over the views, the division

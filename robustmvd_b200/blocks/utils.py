@@ -140,3 +140,94 @@ def softargmax_confidence(cost_slab, merged, D, d_begin):
                                                 int(d_begin), _lib.ptr(out), _lib.stream_ptr())
     _lib.check(st, "rmvd_softargmax_confidence")
     return out
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Vis-MVSNet cost volume: rmvd/models/blocks/utils.py:71-189, vis_mvsnet_singlestage.py:86-122, :230-242
+# ---------------------------------------------------------------------------------------------------------------------
+class NanError(Exception):
+    """utils.py:91-92."""
+
+
+def get_homographies(left_cam, right_cam, depth_num, depth_start, depth_interval, inv=False):
+    """utils.py:96-150: plane-induced homographies ``H = K_r R_r (I - (c_r - c_l) n^T / depth) R_l^T K_l^-1`` for
+    ``depth_num`` fronto-parallel planes of the left (reference) camera.  ``left_cam, right_cam [n,2,4,4]`` (``[:,0]``
+    extrinsics ``[R|t]``, ``[:,1]`` intrinsics), ``depth_start, depth_interval [n,1,1,1]`` or ``[n,1,h,w]``.  Returns
+    ``[n, depth_num, 1|h, 1|w, 3, 3]``.  Host-side set-up like the reference's (a handful of 3x3 products per plane, or per
+    pixel in the refinement stages); the per-voxel work is in the CUDA kernels that consume the result."""
+    with torch.no_grad():
+        n = depth_start.shape[0]
+        dt, dev = left_cam.dtype, left_cam.device
+        steps = torch.arange(0, depth_num, dtype=dt, device=dev).view(1, depth_num, 1, 1)
+        if not inv:
+            depth = depth_start + depth_interval * steps
+        else:
+            depth_end = depth_start + (depth_num - 1) * depth_interval
+            inv_interv = (1 / (depth_start + 1e-9) - 1 / (depth_end + 1e-9)) / (depth_num - 1 + 1e-9)
+            depth = 1 / (1 / (depth_end + 1e-9) + inv_interv * steps)
+        depth = depth.unsqueeze(-1).unsqueeze(-1)                                    # n d h w 1 1
+        R_l, R_r = left_cam[:, 0, :3, :3], right_cam[:, 0, :3, :3]
+        t_l, t_r = left_cam[:, 0, :3, 3:4], right_cam[:, 0, :3, 3:4]
+        K_l, K_r = left_cam[:, 1, :3, :3], right_cam[:, 1, :3, :3]
+        K_l_inv = K_l.float().inverse().to(dt)
+        R_l_t, R_r_t = R_l.transpose(-2, -1), R_r.transpose(-2, -1)
+        fronto = R_l[:, 2:3, :3]                                                     # n 1 3
+        c_rel = (-R_r_t @ t_r) - (-R_l_t @ t_l)                                      # n 3 1
+        outer = (c_rel @ fronto).view(n, 1, 1, 1, 3, 3)
+        middle0 = torch.eye(3, dtype=dt, device=dev).view(1, 1, 1, 1, 3, 3) - outer / (depth + 1e-9)
+        middle1 = (R_l_t @ K_l_inv).view(n, 1, 1, 1, 3, 3)
+        homographies = K_r.view(n, 1, 1, 1, 3, 3) @ R_r.view(n, 1, 1, 1, 3, 3) @ (middle0 @ middle1)
+    if (homographies != homographies).any():
+        raise NanError
+    return homographies
+
+
+def _h_strides(Hs):
+    """Element strides (n, d, y, x) of contiguous homographies ``[n,d,1|h,1|w,3,3]``, broadcast dims -> 0."""
+    st = list(Hs.stride()[:4])
+    for k in (2, 3):
+        if Hs.shape[k] == 1:
+            st[k] = 0
+    return st
+
+
+def homography_warping(input, H):
+    """utils.py:179-189: ``input [n,c,h,w]``, ``H [n,3,3]`` or ``[n,h,w,3,3]`` -> warped ``[n,c,h,w]``
+    (``rmvd_homography_warp_fwd`` with one plane)."""
+    input, H = _f32c(input), _f32c(H)
+    n, c, h, w = input.shape
+    Hs = H.view(n, 1, 1, 1, 3, 3) if H.ndim == 3 else H.view(n, 1, h, w, 3, 3)
+    out = torch.empty((n, c, 1, h, w), dtype=torch.float32, device=input.device)
+    st = _lib.load().rmvd_homography_warp_fwd(_lib.ptr(input), _lib.ptr(Hs), _lib.i64_array(_h_strides(Hs)), n, c, h, w, 1,
+                                              _lib.ptr(out), _lib.stream_ptr())
+    _lib.check(st, "rmvd_homography_warp_fwd")
+    return out[:, :, 0]
+
+
+def homography_warp_volume(src, Hs):
+    """``build_cost_volume`` (vis_mvsnet_singlestage.py:86-122) from ready homographies ``[n,d,1|h,1|w,3,3]``:
+    warped ``[n,c,d,h,w]`` without the d-fold repeat of the source (:109-113)."""
+    src, Hs = _f32c(src), _f32c(Hs)
+    n, c, h, w = src.shape
+    d = Hs.shape[1]
+    out = torch.empty((n, c, d, h, w), dtype=torch.float32, device=src.device)
+    st = _lib.load().rmvd_homography_warp_fwd(_lib.ptr(src), _lib.ptr(Hs), _lib.i64_array(_h_strides(Hs)), n, c, h, w, d,
+                                              _lib.ptr(out), _lib.stream_ptr())
+    _lib.check(st, "rmvd_homography_warp_fwd")
+    return out
+
+
+def groupwise_cost_volume(ref, src, Hs, groups=8):
+    """``groupwise_correlation(ref_ncdhw, build_cost_volume(...), groups, 1)`` (vis_mvsnet_singlestage.py:230-242,
+    utils.py:71-89) in one pass: ``ref, src [n,c,h,w]``, ``Hs [n,d,1|h,1|w,3,3]`` -> ``[n,groups,d,h,w]``; the warped
+    volume is never materialised."""
+    ref, src, Hs = _f32c(ref), _f32c(src), _f32c(Hs)
+    n, c, h, w = src.shape
+    assert ref.shape == src.shape and c % groups == 0
+    d = Hs.shape[1]
+    out = torch.empty((n, groups, d, h, w), dtype=torch.float32, device=src.device)
+    st = _lib.load().rmvd_homography_groupcorr_fwd(_lib.ptr(ref), _lib.ptr(src), _lib.ptr(Hs),
+                                                   _lib.i64_array(_h_strides(Hs)), n, c, h, w, d, groups, _lib.ptr(out),
+                                                   _lib.stream_ptr())
+    _lib.check(st, "rmvd_homography_groupcorr_fwd")
+    return out
