@@ -61,6 +61,7 @@ def test_argument_validation_needs_no_device(lib):
     assert lib.rmvd_psweep_corr_bwd(one, arr, one, arr, arr, one, st, 1, 8, 4, 4, 1, ints, ints, 4, 0, 4, 1, one, 4, 0,
                                     one, arr, one, 16, null) == -4                  # RMVD_E_WORKSPACE
     assert lib.rmvd_psweep_bwd_workspace_bytes(1, 8, 4, 4, 1, ints, ints) == 3 * 512
+    assert lib.rmvd_homography_groupcorr_fwd(one, one, one, st, 1, 10, 4, 4, 2, 4, one, null) == -2  # C % groups != 0
 
 
 def test_missing_library_fails_loudly(monkeypatch, tmp_path):

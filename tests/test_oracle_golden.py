@@ -95,3 +95,17 @@ def test_backward_oracle_matches_reference_autograd(case):
     assert np.abs(gk - g["grad_key"]).max() <= 1e-5 * np.abs(g["grad_key"]).max()
     for v, x in enumerate(gs):
         assert np.abs(x - g[f"grad_src_{v}"]).max() <= 1e-5 * max(np.abs(g[f"grad_src_{v}"]).max(), 1e-30)
+
+
+VIS = cases.vis_cases()
+
+
+@pytest.mark.parametrize("case", VIS, ids=[c["name"] for c in VIS])
+def test_vis_cost_volume_oracle_matches_reference(case):
+    """oracle.groupwise_cost_volume / homography_warp_volume against the unmodified reference functions
+    (tools/make_vis_golden.py: get_homographies + homography_warping + groupwise_correlation on CPU)."""
+    g = load_golden("vis", case["name"])
+    oc = oracle.groupwise_cost_volume(case["ref"], case["src"], g["Hs"], case["groups"])
+    ow = oracle.homography_warp_volume(case["src"], g["Hs"])
+    assert np.abs(oc.reshape(-1)[::int(g["cost_stride"])] - g["cost_sub"]).max() <= 1e-5 * float(g["cost_absmax"])
+    assert np.abs(ow.reshape(-1)[::int(g["warped_stride"])] - g["warped_sub"]).max() <= 1e-5 * float(g["warped_absmax"])

@@ -120,6 +120,13 @@ def main():
         _lib.check(_lib.load().rmvd_view_fusion_fwd(_lib.ptr_array(fl), _lib.ptr_array(fc), _lib.ptr_array(fm), Vf, Nf, Sf, 48, 160,
                                                     _lib.ptr(fw), _lib.ptr(fo[0]), _lib.ptr(fo[1]), _lib.stream_ptr()), "fusion")
     add("view_fusion_cfg2_8frames", run_fusion, 4 * (2 * Vf + 2) * Nf * Sf * Pf + 8 * Vf * Nf * Pf, Nf * Sf * Pf, "voxels")
+    # Vis-MVSNet fused homography warp + group-wise correlation: 128x160 features, C=32, 8 groups, 64 planes
+    vn, vc, vh, vw, vd, vg = 1, 32, 128, 160, 64, 8
+    vref, vsrc = torch.randn((vn, vc, vh, vw), device="cuda"), torch.randn((vn, vc, vh, vw), device="cuda")
+    vH = torch.eye(3, device="cuda").view(1, 1, 1, 1, 3, 3).repeat(vn, vd, 1, 1, 1, 1).contiguous()
+    vH[:, :, 0, 0, 0, 2] = torch.linspace(2.0, 40.0, vd, device="cuda")       # plane-dependent disparity
+    add("vis_groupcorr_128x160_c32_d64", lambda: bu.groupwise_cost_volume(vref, vsrc, vH, vg),
+        4 * vn * vc * vh * vw * 2 + 4 * vn * vg * vd * vh * vw, vn * vd * vh * vw, "voxels")
     for name, fn, nbytes, units, unit_name in jobs:
         cold, best, warm = time_fn(fn, args.reps, flush)
         print(json.dumps({"kernel": name, "ms_cold": cold, "ms_cold_min": best, "ms_warm": warm, "algorithmic_bytes": nbytes,

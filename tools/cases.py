@@ -169,3 +169,43 @@ def prepare_model_for_case(model, model_name):
         with torch.no_grad():
             model.cost_regularization.prob.weight *= MVSNET_PROB_GAIN
     return model
+
+
+def _vis_cam(R, t, fx, fy, cx, cy, n):
+    cam = np.zeros((n, 2, 4, 4), np.float32)
+    cam[:, 0] = np.eye(4, dtype=np.float32)
+    cam[:, 0, :3, :3] = R
+    cam[:, 0, :3, 3] = t
+    cam[:, 1, :3, :3] = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1]], np.float32)
+    cam[:, 1, 3, 3] = 1.0
+    return cam
+
+
+def vis_cases():
+    """Vis-MVSNet cost-volume cases: reference / source features ``[n,c,h,w]``, cameras ``[n,2,4,4]``
+    (``[:,0]`` world-to-camera extrinsics, ``[:,1]`` intrinsics), plane schedule ``depth_start + k * depth_interval``."""
+    out = []
+
+    def case(name, n, c, h, w, d, seed, R=None, t=(0.15, 0.02, 0.01), start=0.6, interval=0.05, per_pixel=False, groups=8,
+             inv=False):
+        rng = np.random.default_rng(seed)
+        R = np.eye(3, dtype=np.float32) if R is None else R.astype(np.float32)
+        fx = 0.9 * w
+        left = _vis_cam(np.eye(3, dtype=np.float32), (0, 0, 0), fx, fx, 0.5 * w, 0.5 * h, n)
+        right = _vis_cam(R, t, fx * 1.02, fx * 0.98, 0.49 * w, 0.51 * h, n)
+        if per_pixel:
+            ds = (start + 0.2 * rng.random((n, 1, h, w))).astype(np.float32)
+            di = (interval * (0.5 + rng.random((n, 1, h, w)))).astype(np.float32)
+        else:
+            ds = np.full((n, 1, 1, 1), start, np.float32) + np.arange(n, dtype=np.float32).reshape(n, 1, 1, 1) * 0.1
+            di = np.full((n, 1, 1, 1), interval, np.float32)
+        return dict(name=name, ref=syn.features((n, c, h, w), seed), src=syn.features((n, c, h, w), seed + 1), left_cam=left,
+                    right_cam=right, depth_num=d, depth_start=ds, depth_interval=di, groups=groups, inv=inv)
+
+    out.append(case("vis_small", 2, 16, 12, 16, 6, 80))
+    out.append(case("vis_rot", 1, 32, 20, 28, 8, 81, R=syn.rot_y(4) @ syn.rot_z(7), t=(0.2, -0.05, 0.03)))
+    out.append(case("vis_per_pixel", 2, 16, 10, 14, 5, 82, per_pixel=True, R=syn.rot_x(3)))
+    out.append(case("vis_inv_depth", 1, 8, 9, 13, 7, 83, inv=True, groups=4))
+    out.append(case("vis_behind", 1, 8, 10, 12, 6, 84, R=syn.rot_y(170), t=(0.1, 0, 0.8), groups=2))
+    out.append(case("vis_dtu_like", 1, 32, 64, 80, 32, 85, t=(0.12, 0.01, 0.0), start=0.45, interval=0.016))
+    return out
