@@ -6,7 +6,7 @@
 //   cost[n,g,d,y,x] = sum_{c in group g} ref[n,c,y,x] * bilinear(src[n,c], u, v),
 //   (hx,hy,hz) = H[n,d,(y,x)] . (x + 0.5, y + 0.5, 1),  (u,v) = (hx,hy) / (hz + 1e-9),
 //   grid = clamp(2 * (u / W, v / H) - 1, -1.1, 1.1), grid_sample(bilinear, zeros, align_corners=False).
-// Thread = voxel (d, y, x), x fastest: reference features and outputs are 128-byte rows per warp, source texels of adjacent
+// Thread = four consecutive planes of one pixel, x fastest across lanes: reference features and outputs are 128-byte rows per warp, source texels of adjacent
 // lanes are adjacent.  The homographies come from the host-side mirror of `get_homographies` (per plane, or per pixel for
 // the refinement stages); element strides select the broadcast form.
 #include "common.cuh"
@@ -22,14 +22,15 @@ struct VisArgs {
   float* out;         // fused: cost [N,G,D,h,w]; warp only: warped [N,C,D,h,w]
 };
 
-template <bool kFused>
-__global__ void __launch_bounds__(256) vis_homography_kernel(const VisArgs A) {
-  const int n = blockIdx.y;
-  const int P = A.h * A.w;
-  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (long long)A.D * P) return;
-  const int d = (int)(idx / P), p = (int)(idx - (long long)d * P);
-  const int yi = p / A.w, xi = p - yi * A.w;
+constexpr int kVisPlanes = 4;  // consecutive planes per thread: reference features and homography rows are loaded once per
+                               // thread for four voxels, and four independent gathers per channel are in flight
+
+struct VisTap {
+  int o_nw, o_ne, o_sw, o_se;
+  float nw, ne, sw, se;
+};
+
+__device__ __forceinline__ VisTap vis_tap(const VisArgs& A, int n, int d, int yi, int xi) {
   const float* Hm = A.H + n * A.hst[0] + d * A.hst[1] + yi * A.hst[2] + xi * A.hst[3];
   const float x = (float)xi + 0.5f, y = (float)yi + 0.5f;  // get_pixel_grids, utils.py:155-160
   float q[3];
@@ -50,28 +51,55 @@ __global__ void __launch_bounds__(256) vis_homography_kernel(const VisArgs A) {
   const int x0 = isnan(b.x0f) ? -2 : sat_index(b.x0f, A.w), y0 = isnan(b.y0f) ? -2 : sat_index(b.y0f, A.h);
   const int x0c = clampi(x0, 0, A.w - 1), x1c = clampi(x0 + 1, 0, A.w - 1);
   const int y0c = clampi(y0, 0, A.h - 1), y1c = clampi(y0 + 1, 0, A.h - 1);
-  const int o_nw = y0c * A.w + x0c, o_ne = y0c * A.w + x1c, o_sw = y1c * A.w + x0c, o_se = y1c * A.w + x1c;
+  VisTap t;
+  t.o_nw = y0c * A.w + x0c; t.o_ne = y0c * A.w + x1c; t.o_sw = y1c * A.w + x0c; t.o_se = y1c * A.w + x1c;
+  t.nw = b.nw; t.ne = b.ne; t.sw = b.sw; t.se = b.se;
+  return t;
+}
+__device__ __forceinline__ float vis_gather(const float* __restrict__ sc, const VisTap& t) {
+  return __ldg(sc + t.o_nw) * t.nw + __ldg(sc + t.o_ne) * t.ne + __ldg(sc + t.o_sw) * t.sw + __ldg(sc + t.o_se) * t.se;
+}
+
+template <bool kFused>
+__global__ void __launch_bounds__(256) vis_homography_kernel(const VisArgs A) {
+  const int n = blockIdx.y;
+  const int P = A.h * A.w;
+  const int Dq = (A.D + kVisPlanes - 1) / kVisPlanes;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)Dq * P) return;
+  const int d0 = (int)(idx / P) * kVisPlanes, p = (int)(idx % P);
+  const int yi = p / A.w, xi = p - yi * A.w;
+  VisTap tap[kVisPlanes];
+#pragma unroll
+  for (int k = 0; k < kVisPlanes; ++k) tap[k] = vis_tap(A, n, min(d0 + k, A.D - 1), yi, xi);
   const float* src = A.src + (size_t)n * A.C * P;
+  const size_t DP = (size_t)A.D * P;
   if (kFused) {
     const float* ref = A.ref + (size_t)n * A.C * P + p;
     const int cpg = A.C / A.groups;
-    float* out = A.out + (((size_t)n * A.groups) * A.D + d) * P + p;
+    float* out = A.out + (((size_t)n * A.groups) * A.D + d0) * P + p;
     for (int g = 0; g < A.groups; ++g) {
-      float acc = 0.f;
+      float acc[kVisPlanes];
+#pragma unroll
+      for (int k = 0; k < kVisPlanes; ++k) acc[k] = 0.f;
       for (int cc = 0; cc < cpg; ++cc) {
         const int c = g * cpg + cc;
         const float* sc = src + (size_t)c * P;
-        const float wv = __ldg(sc + o_nw) * b.nw + __ldg(sc + o_ne) * b.ne + __ldg(sc + o_sw) * b.sw + __ldg(sc + o_se) * b.se;
-        acc = fmaf(__ldg(ref + (size_t)c * P), wv, acc);
+        const float rv = __ldg(ref + (size_t)c * P);
+#pragma unroll
+        for (int k = 0; k < kVisPlanes; ++k) acc[k] = fmaf(rv, vis_gather(sc, tap[k]), acc[k]);
       }
-      __stcs(out + (size_t)g * A.D * P, acc);
+#pragma unroll
+      for (int k = 0; k < kVisPlanes; ++k)
+        if (d0 + k < A.D) __stcs(out + (size_t)g * DP + (size_t)k * P, acc[k]);
     }
   } else {
-    float* out = A.out + (((size_t)n * A.C) * A.D + d) * P + p;
+    float* out = A.out + (((size_t)n * A.C) * A.D + d0) * P + p;
     for (int c = 0; c < A.C; ++c) {
       const float* sc = src + (size_t)c * P;
-      __stcs(out + (size_t)c * A.D * P,
-             __ldg(sc + o_nw) * b.nw + __ldg(sc + o_ne) * b.ne + __ldg(sc + o_sw) * b.sw + __ldg(sc + o_se) * b.se);
+#pragma unroll
+      for (int k = 0; k < kVisPlanes; ++k)
+        if (d0 + k < A.D) __stcs(out + (size_t)c * DP + (size_t)k * P, vis_gather(sc, tap[k]));
     }
   }
 }
@@ -85,7 +113,7 @@ static int vis_launch(bool fused, const float* ref, const float* src, const floa
   A.ref = ref; A.src = src; A.H = H;
   for (int k = 0; k < 4; ++k) A.hst[k] = hst[k];
   A.N = N; A.C = C; A.h = h; A.w = w; A.D = D; A.groups = groups; A.out = out;
-  const long long tot = (long long)D * h * w;
+  const long long tot = (long long)((D + kVisPlanes - 1) / kVisPlanes) * h * w;
   dim3 grid((unsigned)((tot + 255) / 256), N);
   if (fused) vis_homography_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(A);
   else vis_homography_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(A);
