@@ -181,6 +181,15 @@ int rmvd_softargmax_confidence(const float* cost_slab, const float* merged, int 
 int rmvd_soft_argmin_fwd(const float* volume, int B, int D, int h, int w, float window, float* prob,
                          float* expected_index, float* prob_map, float* entropy, void* stream);
 
+/*
+ * CVP-MVSNet proj_cost (cvp_mvsnet_components.py:375-457): variance cost volume over PER-PIXEL depth
+ * hypotheses, the warped source volumes never written.  feats [B,Vt,C,h,w] (view 0 = reference level features),
+ * proj [B,Vt,4,4]: view 0 = inverse(ref_proj), views v >= 1 = src_proj (:398-405), depth_hypos [B,D,h,w],
+ * cost [B,C,D,h,w].  Reproduces the reference's in-place quirk (:392): both running sums start from ref^2.
+ */
+int rmvd_cvp_proj_cost_fwd(const float* feats, const float* proj, const float* depth_hypos, int B, int Vt, int C, int h,
+                           int w, int D, float* cost, void* stream);
+
 /* ---------------------------------------------------------------------------------------------------
  * Vis-MVSNet family
  * ------------------------------------------------------------------------------------------------- */

@@ -47,3 +47,4 @@ from .mvsnet import (  # noqa: F401
 )
 from .fusion import view_fusion  # noqa: F401,E402
 from .vismvsnet import homography_coords, homography_warp_volume, groupwise_cost_volume  # noqa: F401,E402
+from . import cvpmvsnet  # noqa: F401,E402

@@ -42,6 +42,24 @@ __device__ __forceinline__ void homo_coord(const float* M, int xi, int yi, float
   iy = grid_unnormalize(yn, H);
 }
 
+// CVP-MVSNet's chain (cvp_mvsnet_components.py:414-430, :217-233): rotate the integer pixel (x, y, 1) first, then scale by
+// the (per-pixel) depth hypothesis and translate; same normalisation and grid_sample convention as above.
+__device__ __forceinline__ void cvp_coord(const float* M, int xi, int yi, float d, int H, int W, float& ix, float& iy) {
+  float p[3];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    float acc = fmul(M[r * 4 + 0], (float)xi);
+    acc = __fmaf_rn(M[r * 4 + 1], (float)yi, acc);
+    acc = __fmaf_rn(M[r * 4 + 2], 1.0f, acc);     // rot @ xyz, :414
+    p[r] = fadd(fmul(acc, d), M[r * 4 + 3]);      // * depth_hypos + trans, :416-421
+  }
+  const float sx = fdiv(p[0], p[2]), sy = fdiv(p[1], p[2]);       // :422
+  const float xn = fsub(fdiv(sx, (float)(W - 1) * 0.5f), 1.0f);   // :423
+  const float yn = fsub(fdiv(sy, (float)(H - 1) * 0.5f), 1.0f);   // :424
+  ix = grid_unnormalize(xn, W);
+  iy = grid_unnormalize(yn, H);
+}
+
 // Same chain with the divisions through shared reciprocals (common.cuh: bit-identical to div.rn inside the guarded range;
 // operands outside it take homo_coord() itself).  y_w, y_h = rcp_refined((W - 1) / 2), rcp_refined((H - 1) / 2).
 __device__ __forceinline__ void homo_coord_shared(const float* M, int xi, int yi, float d, int H, int W, float y_w, float y_h,
@@ -100,7 +118,10 @@ __device__ __forceinline__ float gather_val(const float* __restrict__ img, const
 // Per source view the thread derives its sampling footprint once and gathers kCh channels, keeping the running
 // sum and sum of squares in registers (mvsnet.py:124-133); variance = sq/V - (sum/V)^2 (:135).
 // ---------------------------------------------------------------------------------------------------------
-template <int kCh>
+//   kCvp: CVP-MVSNet's proj_cost (cvp_mvsnet_components.py:375-457): per-pixel depth hypotheses [B,D,h,w], the chain of
+//   cvp_coord(), and the reference's in-place quirk -- `volume_sq_sum = volume_sum.pow_(2)` (:392) squares volume_sum
+//   itself, so BOTH running sums start from ref^2: cost = (ref^2 + sum w^2)/V - ((ref^2 + sum w)/V)^2.
+template <int kCh, bool kCvp = false>
 __global__ void __launch_bounds__(256) mvs_variance_kernel(const float* __restrict__ feats, const float* __restrict__ proj,
                                                            const float* __restrict__ depths, int B, int Vt, int C,
                                                            int h, int w, int D, int d_begin, int d_end,
@@ -121,19 +142,20 @@ __global__ void __launch_bounds__(256) mvs_variance_kernel(const float* __restri
   const int dl = (int)(idx / P), p = (int)(idx - (long long)dl * P);
   const int d = d_begin + dl;
   const int yi = p / w, xi = p - yi * w;
-  const float depth = depths[(size_t)b * D + d];
+  const float depth = kCvp ? depths[((size_t)b * D + d) * P + p] : depths[(size_t)b * D + d];
 
   float sum[kCh], sq[kCh];
   const float* ref = feats + ((size_t)b * Vt) * C * P + p;
 #pragma unroll
   for (int k = 0; k < kCh; ++k) {
     const float r = (c0 + k < C) ? __ldg(ref + (size_t)(c0 + k) * P) : 0.f;
-    sum[k] = r;               // volume_sum = ref_volume (:125)
-    sq[k] = fmul(r, r);       // ref_volume ** 2 (:126)
+    sum[k] = kCvp ? fmul(r, r) : r;   // volume_sum = ref_volume (:125); CVP: squared in place with volume_sq_sum
+    sq[k] = fmul(r, r);               // ref_volume ** 2 (:126)
   }
   for (int v = 1; v < Vt; ++v) {
     float ix, iy;
-    homo_coord(s_M[v - 1], xi, yi, depth, h, w, ix, iy);
+    if (kCvp) cvp_coord(s_M[v - 1], xi, yi, depth, h, w, ix, iy);
+    else homo_coord(s_M[v - 1], xi, yi, depth, h, w, ix, iy);
     const Gather g = make_gather(ix, iy, h, w);
     const float* src = feats + ((size_t)b * Vt + v) * C * P;
 #pragma unroll
@@ -635,4 +657,17 @@ extern "C" const char* rmvd_status_string(int status) {
     case RMVD_E_RANGE: return "plane range outside the schedule";
     default: return status > 0 ? cudaGetErrorString((cudaError_t)status) : "unknown status";
   }
+}
+
+extern "C" int rmvd_cvp_proj_cost_fwd(const float* feats, const float* proj, const float* depth_hypos, int B, int Vt, int C,
+                                      int h, int w, int D, float* cost, void* stream) {
+  if (!feats || !proj || !depth_hypos || !cost) return RMVD_E_NULL;
+  if (B <= 0 || Vt <= 0 || C <= 0 || h <= 0 || w <= 0 || D <= 0 || B > 65535) return RMVD_E_SHAPE;
+  if (Vt - 1 > kMaxMvsViews) return RMVD_E_SHAPE;
+  const long long tot = (long long)D * h * w;
+  constexpr int kCh = 8;
+  dim3 grid((unsigned)((tot + 255) / 256), (C + kCh - 1) / kCh, B);
+  mvs_variance_kernel<kCh, true><<<grid, 256, 0, (cudaStream_t)stream>>>(feats, proj, depth_hypos, B, Vt, C, h, w, D, 0, D,
+                                                                            cost, D, 0);
+  return (int)cudaGetLastError();
 }

@@ -109,3 +109,17 @@ def test_vis_cost_volume_oracle_matches_reference(case):
     ow = oracle.homography_warp_volume(case["src"], g["Hs"])
     assert np.abs(oc.reshape(-1)[::int(g["cost_stride"])] - g["cost_sub"]).max() <= 1e-5 * float(g["cost_absmax"])
     assert np.abs(ow.reshape(-1)[::int(g["warped_stride"])] - g["warped_sub"]).max() <= 1e-5 * float(g["warped_absmax"])
+
+
+CVP = cases.cvp_cases()
+
+
+@pytest.mark.parametrize("c", CVP, ids=[c["name"] for c in CVP])
+def test_cvp_oracle_matches_reference(c):
+    """oracle.cvpmvsnet against the unmodified reference proj_cost / homo_warping (tools/make_cvp_golden.py)."""
+    g = load_golden("cvp", c["name"])
+    oc = oracle.cvpmvsnet.proj_cost(c["ref"], c["srcs"], c["ref_in"], c["src_in"], c["ref_ex"], c["src_ex"], c["depth_hypos"])
+    ow = oracle.cvpmvsnet.homo_warping(c["srcs"][0], c["ref_in"], c["src_in"][:, 0], c["ref_ex"], c["src_ex"][:, 0],
+                                       c["depth_planes"])
+    assert np.abs(oc - g["cost"]).max() <= 2e-5 * np.abs(g["cost"]).max()
+    assert np.abs(ow - g["warped"]).max() <= 2e-5 * np.abs(g["warped"]).max()

@@ -127,6 +127,20 @@ def main():
     vH[:, :, 0, 0, 0, 2] = torch.linspace(2.0, 40.0, vd, device="cuda")       # plane-dependent disparity
     add("vis_groupcorr_128x160_c32_d64", lambda: bu.groupwise_cost_volume(vref, vsrc, vH, vg),
         4 * vn * vc * vh * vw * 2 + 4 * vn * vg * vd * vh * vw, vn * vd * vh * vw, "voxels")
+    # CVP-MVSNet proj_cost: refinement level 128x160, C=16, 2 source views, 8 per-pixel hypotheses
+    import types
+    from robustmvd_b200.blocks import cvp_mvsnet_components as cvpc
+    cB, cC, cH, cW, cD, cV = 1, 16, 128, 160, 8, 2
+    cref = torch.randn((cB, cC, cH, cW), device="cuda")
+    csrc = [[torch.randn((cB, cC, cH, cW), device="cuda")] for _ in range(cV)]
+    cK = torch.tensor([[140.0, 0, 80.0], [0, 140.0, 64.0], [0, 0, 1.0]], device="cuda").repeat(cB, 1, 1)
+    cE = torch.eye(4, device="cuda").repeat(cB, 1, 1)
+    cEs = cE[:, None].repeat(1, cV, 1, 1).contiguous()
+    cEs[:, :, 0, 3] = torch.tensor([0.1, -0.1], device="cuda")
+    chyp = (0.6 + 0.02 * torch.arange(cD, device="cuda").view(1, cD, 1, 1) + 0.1 * torch.rand((cB, 1, cH, cW), device="cuda")).contiguous()
+    cset = types.SimpleNamespace(nsrc=cV, mode="test")
+    add("cvp_proj_cost_128x160_c16_d8", lambda: cvpc.proj_cost(cset, cref, csrc, 0, cK, cK[:, None].repeat(1, cV, 1, 1), cE, cEs, chyp),
+        4 * cC * cH * cW * (1 + cV) + 4 * cD * cH * cW + 4 * cC * cD * cH * cW, cD * cH * cW, "voxels")
     for name, fn, nbytes, units, unit_name in jobs:
         cold, best, warm = time_fn(fn, args.reps, flush)
         print(json.dumps({"kernel": name, "ms_cold": cold, "ms_cold_min": best, "ms_warm": warm, "algorithmic_bytes": nbytes,

@@ -209,3 +209,33 @@ def vis_cases():
     out.append(case("vis_behind", 1, 8, 10, 12, 6, 84, R=syn.rot_y(170), t=(0.1, 0, 0.8), groups=2))
     out.append(case("vis_dtu_like", 1, 32, 64, 80, 32, 85, t=(0.12, 0.01, 0.0), start=0.45, interval=0.016))
     return out
+
+
+def cvp_cases():
+    """CVP-MVSNet cost-volume cases: reference + nsrc source maps ``[B,C,H,W]``, pixel intrinsics
+    ``[B,3,3]`` / ``[B,nsrc,3,3]``, world-to-camera extrinsics ``[B,4,4]`` / ``[B,nsrc,4,4]``, per-pixel hypotheses
+    ``[B,D,H,W]`` (and per-plane ``[B,D]`` for ``homo_warping``)."""
+    out = []
+
+    def case(name, B, C, H, W, D, nsrc, seed, rot=None):
+        rng = np.random.default_rng(seed)
+        K = np.array([[0.9 * W, 0, 0.5 * W], [0, 0.9 * W, 0.5 * H], [0, 0, 1]], np.float32)
+        ref_in = np.repeat(K[None], B, 0)
+        src_in = np.repeat(np.repeat((K * np.array([[1.02], [0.98], [1.0]], np.float32))[None, None], B, 0), nsrc, 1)
+        ref_ex = np.repeat(np.eye(4, dtype=np.float32)[None], B, 0)
+        src_ex = np.zeros((B, nsrc, 4, 4), np.float32)
+        for v in range(nsrc):
+            E = np.eye(4, dtype=np.float32)
+            E[:3, :3] = (syn.rot_y(1.5 * (v + 1)) if rot is None else rot(v)).astype(np.float32)
+            E[:3, 3] = (0.08 * (v + 1) * (-1) ** v, 0.01 * v, 0.005)
+            src_ex[:, v] = E
+        base = (0.5 + 0.3 * rng.random((B, 1, H, W))).astype(np.float32)
+        hyp = (base + 0.02 * np.arange(D, dtype=np.float32).reshape(1, D, 1, 1)).astype(np.float32)
+        planes = np.repeat((0.45 + 0.03 * np.arange(D, dtype=np.float32))[None], B, 0)
+        return dict(name=name, ref=syn.features((B, C, H, W), seed), srcs=[syn.features((B, C, H, W), seed + 1 + v) for v in range(nsrc)],
+                    ref_in=ref_in, src_in=src_in, ref_ex=ref_ex, src_ex=src_ex, depth_hypos=hyp, depth_planes=planes, nsrc=nsrc)
+
+    out.append(case("cvp_small", 2, 8, 10, 14, 5, 2, 90))
+    out.append(case("cvp_odd_c", 1, 5, 9, 11, 4, 3, 91, rot=lambda v: syn.rot_z(6 * (v + 1)) @ syn.rot_x(2)))
+    out.append(case("cvp_c16", 1, 16, 24, 32, 8, 4, 92))
+    return out

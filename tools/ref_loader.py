@@ -73,3 +73,10 @@ def block_utils():
     if "bu" not in _cache:
         _cache["bu"] = _load("_ref_block_utils", "rmvd/models/blocks/utils.py")
     return _cache["bu"]
+
+
+def cvp_components():
+    _install_stubs()
+    if "cvp" not in _cache:
+        _cache["cvp"] = _load("_ref_cvp_components", "rmvd/models/blocks/cvp_mvsnet_components.py")
+    return _cache["cvp"]
