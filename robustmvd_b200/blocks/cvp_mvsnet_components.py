@@ -11,13 +11,21 @@ def _f32c(t):
     return t.detach().to(torch.float32).contiguous()
 
 
-def _projections(ref_in, src_in, ref_ex, src_ex):
-    """:204-211 / :398-405: ``src_proj`` and ``inverse(ref_proj)`` as 4x4 matrices."""
+def _proj4(K, E):
+    """:204-209 / :398-403: ``K @ E[:3]`` with the row (0, 0, 0, 1) appended (built on the device, no host copy)."""
+    out = torch.zeros((K.shape[0], 4, 4), device=K.device, dtype=K.dtype)
+    out[:, :3] = torch.matmul(K, E[:, 0:3, :])
+    out[:, 3, 3] = 1.0
+    return out
+
+
+def _projections(ref_in, src_in, ref_ex, src_ex, ref_proj_inv=None):
+    """:204-211 / :398-405: ``src_proj`` and ``inverse(ref_proj)`` as 4x4 matrices (``inv_ex`` without the error check: no
+    device-to-host synchronisation; the reference inverts the same reference projection once per source view)."""
     with torch.no_grad():
-        last = torch.tensor([[[0, 0, 0, 1.0]]], device=ref_in.device, dtype=ref_in.dtype).repeat(len(src_in), 1, 1)
-        src_proj = torch.cat((torch.matmul(src_in, src_ex[:, 0:3, :]), last), 1)
-        ref_proj = torch.cat((torch.matmul(ref_in, ref_ex[:, 0:3, :]), last), 1)
-        return src_proj, torch.inverse(ref_proj)
+        if ref_proj_inv is None:
+            ref_proj_inv = torch.linalg.inv_ex(_proj4(ref_in, ref_ex), check_errors=False)[0]
+        return _proj4(src_in, src_ex), ref_proj_inv
 
 
 def homo_warping(src_feature, ref_in, src_in, ref_ex, src_ex, depth_hypos):
@@ -41,9 +49,9 @@ def proj_cost(settings, ref_feature, src_feature, level, ref_in, src_in, ref_ex,
     B, C, H, W = ref_feature.shape
     D = depth_hypos.shape[1]
     nsrc = settings.nsrc
-    projs = []
+    projs, ref_proj_inv = [], None
     for v in range(nsrc):
-        src_proj, ref_proj_inv = _projections(ref_in, src_in[:, v], ref_ex, src_ex[:, v])
+        src_proj, ref_proj_inv = _projections(ref_in, src_in[:, v], ref_ex, src_ex[:, v], ref_proj_inv)
         if v == 0:
             projs.append(ref_proj_inv)
         projs.append(src_proj)

@@ -41,21 +41,3 @@ def test_proj_cost_and_homo_warping_match_oracle_and_reference(cuda_lib, c):
     warped = cvp.homo_warping(_t(c["srcs"][0]), _t(c["ref_in"]), _t(c["src_in"][:, 0]), _t(c["ref_ex"]), _t(c["src_ex"][:, 0]),
                               _t(c["depth_planes"])).cpu().numpy()
     assert warped.shape == g["warped"].shape and _rel(warped, g["warped"]) <= TOL
-
-
-def test_proj_cost_quirk_is_the_references(cuda_lib):
-    """With identity geometry (source = reference camera) every warped map equals its source map at interior pixels, so
-    cost = (r^2 + sum s_v^2)/V - ((r^2 + sum s_v)/V)^2 -- the reference's in-place ``pow_`` (:392), not the variance."""
-    from robustmvd_b200.blocks import cvp_mvsnet_components as cvp
-    B, C, H, W, D, nsrc = 1, 8, 16, 20, 3, 2
-    gen = torch.Generator(device=DEV).manual_seed(5)
-    ref = torch.randn((B, C, H, W), device=DEV, generator=gen)
-    srcs = [torch.randn((B, C, H, W), device=DEV, generator=gen) for _ in range(nsrc)]
-    K = torch.tensor([[18.0, 0, 10.0], [0, 18.0, 8.0], [0, 0, 1.0]], device=DEV).repeat(B, 1, 1)
-    E = torch.eye(4, device=DEV).repeat(B, 1, 1)
-    hyp = torch.full((B, D, H, W), 0.7, device=DEV)
-    cost = cvp.proj_cost(types.SimpleNamespace(nsrc=nsrc, mode="test"), ref, [[s] for s in srcs], 0, K,
-                         K[:, None].repeat(1, nsrc, 1, 1), E, E[:, None].repeat(1, nsrc, 1, 1), hyp)
-    V = nsrc + 1
-    want = (ref ** 2 + sum(s ** 2 for s in srcs)) / V - ((ref ** 2 + sum(srcs)) / V) ** 2
-    assert float((cost[:, :, 1] - want).abs().max()) <= 1e-4 * float(want.abs().max())
