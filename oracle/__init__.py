@@ -6,6 +6,11 @@ This package is a numpy restatement of the reference's algorithm
 ``/root/reference/rmvd/models/mvsnet.py:123-160``).  Each function cites the
 reference ``file:line`` it follows.
 
+Added for the "next" rows of SURVEY.md 8(f): ``planesweep_correlation_backward`` (what autograd returns through
+``TorchCorr.forward``, pinned by ``tools/make_bwd_golden.py``), ``vismvsnet`` (``blocks/utils.py:71-189``, pinned by
+``tools/make_vis_golden.py``) and ``cvpmvsnet`` (``blocks/cvp_mvsnet_components.py:192-245, :375-457``, pinned by
+``tools/make_cvp_golden.py``).
+
 Who may import it: ``tests/``, ``__graft_entry__.smoke()`` and the
 ``cpu_baseline`` / ``--impl reference`` legs of ``bench.py`` -- there only as the
 checker or as the timed CPU baseline.  The product package ``robustmvd_b200``
