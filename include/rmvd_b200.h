@@ -186,7 +186,11 @@ int rmvd_soft_argmin_fwd(const float* volume, int B, int D, int h, int w, float 
  * hypotheses, the warped source volumes never written.  feats [B,Vt,C,h,w] (view 0 = reference level features),
  * proj [B,Vt,4,4]: view 0 = inverse(ref_proj), views v >= 1 = src_proj (:398-405), depth_hypos [B,D,h,w],
  * cost [B,C,D,h,w].  Reproduces the reference's in-place quirk (:392): both running sums start from ref^2.
+ * rmvd_cvp_projections builds that proj tensor on the device from ref_in [B,3,3], src_in [B,nsrc,3,3], ref_ex [B,4,4],
+ * src_ex [B,nsrc,4,4] (:398-405; the reference inverts ref_proj with torch.inverse once per source view).
  */
+int rmvd_cvp_projections(const float* ref_in, const float* src_in, const float* ref_ex, const float* src_ex, int B, int nsrc,
+                         float* proj, void* stream);
 int rmvd_cvp_proj_cost_fwd(const float* feats, const float* proj, const float* depth_hypos, int B, int Vt, int C, int h,
                            int w, int D, float* cost, void* stream);
 

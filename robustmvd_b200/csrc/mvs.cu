@@ -659,6 +659,58 @@ extern "C" const char* rmvd_status_string(int status) {
   }
 }
 
+// CVP-MVSNet projection set-up (cvp_mvsnet_components.py:398-405 / :204-211) on the device: thread = (sample, view).
+// View 0 gets inverse(ref_proj), views v >= 1 get src_proj, each a 4x4 with the row (0, 0, 0, 1): what
+// rmvd_cvp_proj_cost_fwd / rmvd_homo_warp_fwd take.  The affine inverse is evaluated in double and rounded once.
+__global__ void cvp_projection_kernel(const float* __restrict__ ref_in, const float* __restrict__ src_in,
+                                      const float* __restrict__ ref_ex, const float* __restrict__ src_ex, int B, int nsrc,
+                                      float* __restrict__ proj) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * (nsrc + 1)) return;
+  const int b = i / (nsrc + 1), v = i % (nsrc + 1);
+  const float* K = (v == 0) ? ref_in + (size_t)b * 9 : src_in + ((size_t)b * nsrc + v - 1) * 9;
+  const float* E = (v == 0) ? ref_ex + (size_t)b * 16 : src_ex + ((size_t)b * nsrc + v - 1) * 16;
+  float M[12];  // K @ E[:3, :]
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      float acc = fmul(K[r * 3 + 0], E[0 * 4 + c]);
+      acc = __fmaf_rn(K[r * 3 + 1], E[1 * 4 + c], acc);
+      M[r * 4 + c] = __fmaf_rn(K[r * 3 + 2], E[2 * 4 + c], acc);
+    }
+  float* out = proj + (size_t)i * 16;
+  if (v > 0) {
+#pragma unroll
+    for (int k = 0; k < 12; ++k) out[k] = M[k];
+  } else {  // inverse of [[A, t], [0, 1]] = [[A^-1, -A^-1 t], [0, 1]]
+    const double a = M[0], bb = M[1], c = M[2], d = M[4], e = M[5], f = M[6], g = M[8], h = M[9], k = M[10];
+    const double c00 = e * k - f * h, c01 = -(d * k - f * g), c02 = d * h - e * g;
+    const double det = a * c00 + bb * c01 + c * c02;
+    const double inv[9] = {c00 / det, -(bb * k - c * h) / det, (bb * f - c * e) / det,
+                           c01 / det, (a * k - c * g) / det, -(a * f - c * d) / det,
+                           c02 / det, -(a * h - bb * g) / det, (a * e - bb * d) / det};
+    const double t[3] = {M[3], M[7], M[11]};
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      out[r * 4 + 0] = (float)inv[r * 3 + 0];
+      out[r * 4 + 1] = (float)inv[r * 3 + 1];
+      out[r * 4 + 2] = (float)inv[r * 3 + 2];
+      out[r * 4 + 3] = (float)(-(inv[r * 3 + 0] * t[0] + inv[r * 3 + 1] * t[1] + inv[r * 3 + 2] * t[2]));
+    }
+  }
+  out[12] = 0.f; out[13] = 0.f; out[14] = 0.f; out[15] = 1.f;
+}
+
+extern "C" int rmvd_cvp_projections(const float* ref_in, const float* src_in, const float* ref_ex, const float* src_ex, int B,
+                                    int nsrc, float* proj, void* stream) {
+  if (!ref_in || !src_in || !ref_ex || !src_ex || !proj) return RMVD_E_NULL;
+  if (B <= 0 || nsrc <= 0) return RMVD_E_SHAPE;
+  const int tot = B * (nsrc + 1);
+  cvp_projection_kernel<<<(tot + 127) / 128, 128, 0, (cudaStream_t)stream>>>(ref_in, src_in, ref_ex, src_ex, B, nsrc, proj);
+  return (int)cudaGetLastError();
+}
+
 extern "C" int rmvd_cvp_proj_cost_fwd(const float* feats, const float* proj, const float* depth_hypos, int B, int Vt, int C,
                                       int h, int w, int D, float* cost, void* stream) {
   if (!feats || !proj || !depth_hypos || !cost) return RMVD_E_NULL;
