@@ -149,6 +149,8 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":   # NCCL writes its version banner to STDOUT: keep the
+            os.environ["NCCL_DEBUG"] = "WARN"                        # one-JSON-line contract of this script
         dist.init_process_group("nccl", device_id=dev)
     _lib.load()
     frames = args.frames
