@@ -207,6 +207,17 @@ int rmvd_cvp_proj_cost_fwd(const float* feats, const float* proj, const float* d
  */
 int rmvd_homography_groupcorr_fwd(const float* ref, const float* src, const float* H, const int64_t* h_stride_host, int N,
                                   int C, int h, int w, int D, int groups, float* cost, void* stream);
+/*
+ * The same cost volume straight from the cameras: get_homographies (blocks/utils.py:96-150) folded into the kernel, no
+ * [n,d,h,w,3,3] tensor.  left_cam, right_cam [N,2,4,4] ([:,0] extrinsics [R|t], [:,1] intrinsics); depth_start and
+ * depth_interval are [N,1,1,1] or [N,1,h,w]: element (n,y,x) at n*stride[0] + y*stride[1] + x*stride[2] (0 = broadcast);
+ * plane k is depth_start + k*depth_interval, or the inverse-depth schedule of :117-123 when inv != 0.
+ * workspace: N*18 floats of device scratch (per-sample A and B with H = A - B / (depth + 1e-9)).
+ */
+int rmvd_vis_cost_volume_fwd(const float* ref, const float* src, const float* left_cam, const float* right_cam,
+                             const float* depth_start, const int64_t* start_stride_host, const float* depth_interval,
+                             const int64_t* interval_stride_host, int N, int C, int h, int w, int D, int inv, int groups,
+                             float* cost, void* workspace, size_t workspace_bytes, void* stream);
 /* homography_warping alone (blocks/utils.py:179-189): warped [N,C,D,h,w] (D = 1 for a single homography per sample). */
 int rmvd_homography_warp_fwd(const float* src, const float* H, const int64_t* h_stride_host, int N, int C, int h, int w,
                              int D, float* warped, void* stream);

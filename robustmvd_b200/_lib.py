@@ -16,7 +16,7 @@ EXPORTS = (
     "rmvd_psweep_warp_fwd", "rmvd_psweep_bwd_workspace_bytes", "rmvd_psweep_corr_bwd",
     "rmvd_corr_grid_fwd", "rmvd_warp_grid_fwd", "rmvd_mvs_variance_fwd",
     "rmvd_homo_warp_fwd", "rmvd_mvs_regress_fwd", "rmvd_softargmax_partial", "rmvd_softargmax_combine",
-    "rmvd_softargmax_confidence", "rmvd_soft_argmin_fwd", "rmvd_view_fusion_fwd", "rmvd_homography_groupcorr_fwd", "rmvd_homography_warp_fwd", "rmvd_cvp_proj_cost_fwd", "rmvd_cvp_projections", "rmvd_debug_div_check",
+    "rmvd_softargmax_confidence", "rmvd_soft_argmin_fwd", "rmvd_view_fusion_fwd", "rmvd_homography_groupcorr_fwd", "rmvd_homography_warp_fwd", "rmvd_vis_cost_volume_fwd", "rmvd_cvp_proj_cost_fwd", "rmvd_cvp_projections", "rmvd_debug_div_check",
 )
 
 
@@ -53,6 +53,7 @@ def _declare(lib):
     lib.rmvd_view_fusion_fwd.argtypes = [PP, PP, PP] + [c_int] * 5 + [P, P, P, P]
     lib.rmvd_homography_groupcorr_fwd.argtypes = [P, P, P, PL] + [c_int] * 6 + [P, P]
     lib.rmvd_homography_warp_fwd.argtypes = [P, P, PL] + [c_int] * 5 + [P, P]
+    lib.rmvd_vis_cost_volume_fwd.argtypes = [P, P, P, P, P, PL, P, PL] + [c_int] * 7 + [P, P, c_size_t, P]
     lib.rmvd_cvp_proj_cost_fwd.argtypes = [P, P, P] + [c_int] * 6 + [P, P]
     lib.rmvd_cvp_projections.argtypes = [P, P, P, P, c_int, c_int, P, P]
     lib.rmvd_debug_div_check.argtypes = [P, P, c_int, P, P, P]

@@ -231,3 +231,27 @@ def groupwise_cost_volume(ref, src, Hs, groups=8):
                                                    _lib.stream_ptr())
     _lib.check(st, "rmvd_homography_groupcorr_fwd")
     return out
+
+
+def vis_cost_volume(ref, src, left_cam, right_cam, depth_num, depth_start, depth_interval, groups=8, inv=False):
+    """``get_homographies`` + ``build_cost_volume`` + ``groupwise_correlation`` (utils.py:96-150, vis_mvsnet_singlestage.py:
+    86-122, :230-242) in one call: the homography of every (plane, pixel) is formed inside the kernel from two 3x3 matrices per
+    sample, so neither ``Hs [n,d,h,w,3,3]`` nor the warped volume exists.  ``left_cam / right_cam [n,2,4,4]`` (already scaled,
+    :99-100), ``depth_start / depth_interval [n,1,1,1]`` or ``[n,1,h,w]`` -> ``[n,groups,depth_num,h,w]``."""
+    ref, src, left_cam, right_cam = map(_f32c, (ref, src, left_cam, right_cam))
+    ds, di = _f32c(depth_start), _f32c(depth_interval)
+    n, c, h, w = src.shape
+
+    def strides(t):
+        assert t.shape[0] == n and t.shape[1] == 1 and t.shape[2] in (1, h) and t.shape[3] in (1, w)
+        st = t.stride()
+        return [st[0], 0 if t.shape[2] == 1 else st[2], 0 if t.shape[3] == 1 else st[3]]
+
+    out = torch.empty((n, groups, depth_num, h, w), dtype=torch.float32, device=src.device)
+    wsp = torch.empty(n * 18, dtype=torch.float32, device=src.device)
+    st = _lib.load().rmvd_vis_cost_volume_fwd(
+        _lib.ptr(ref), _lib.ptr(src), _lib.ptr(left_cam), _lib.ptr(right_cam), _lib.ptr(ds), _lib.i64_array(strides(ds)),
+        _lib.ptr(di), _lib.i64_array(strides(di)), n, c, h, w, depth_num, 1 if inv else 0, groups, _lib.ptr(out),
+        _lib.ptr(wsp), wsp.numel() * 4, _lib.stream_ptr())
+    _lib.check(st, "rmvd_vis_cost_volume_fwd")
+    return out

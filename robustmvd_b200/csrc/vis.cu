@@ -16,8 +16,14 @@ namespace rmvd {
 struct VisArgs {
   const float* ref;   // [N,C,h,w] (fused mode)
   const float* src;   // [N,C,h,w]
-  const float* H;     // homographies, 9 floats each
+  const float* H;     // homographies, 9 floats each (nullptr: analytic mode below)
   long long hst[4];   // element strides of H for (n, d, y, x); 0 = broadcast
+  // analytic mode: H(n, d, y, x) = AB[n][0] - AB[n][1] / (depth + 1e-9) with the plane schedule of get_homographies
+  const float* AB;    // [N,2,3,3] from vis_setup_kernel
+  const float* dstart;  // depth_start, element (n,y,x) at n*sst[0] + y*sst[1] + x*sst[2]
+  const float* dinter;  // depth_interval, same addressing with ist
+  long long sst[3], ist[3];
+  int inv;
   int N, C, h, w, D, groups;
   float* out;         // fused: cost [N,G,D,h,w]; warp only: warped [N,C,D,h,w]
 };
@@ -31,14 +37,35 @@ struct VisTap {
 };
 
 __device__ __forceinline__ VisTap vis_tap(const VisArgs& A, int n, int d, int yi, int xi) {
-  const float* Hm = A.H + n * A.hst[0] + d * A.hst[1] + yi * A.hst[2] + xi * A.hst[3];
+  float Hm[9];
+  if (A.H) {
+    const float* Hp = A.H + n * A.hst[0] + d * A.hst[1] + yi * A.hst[2] + xi * A.hst[3];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) Hm[k] = __ldg(Hp + k);
+  } else {  // get_homographies, utils.py:113-126 (schedule) and :139-146 (H = A - B / (depth + 1e-9))
+    const float ds = __ldg(A.dstart + n * A.sst[0] + yi * A.sst[1] + xi * A.sst[2]);
+    const float di = __ldg(A.dinter + n * A.ist[0] + yi * A.ist[1] + xi * A.ist[2]);
+    float depth;
+    if (!A.inv) {
+      depth = fadd(ds, fmul(di, (float)d));                                               // :114-116
+    } else {
+      const float dend = fadd(ds, fmul((float)(A.D - 1), di));                            // :118
+      const float i0 = fdiv(1.0f, fadd(dend, 1e-9f));
+      const float step = fdiv(fsub(fdiv(1.0f, fadd(ds, 1e-9f)), i0), fadd((float)(A.D - 1), 1e-9f));  // :119
+      depth = fdiv(1.0f, fadd(i0, fmul(step, (float)d)));                                 // :120-123
+    }
+    const float r = fdiv(1.0f, fadd(depth, 1e-9f));
+    const float* ab = A.AB + (size_t)n * 18;
+#pragma unroll
+    for (int k = 0; k < 9; ++k) Hm[k] = __fmaf_rn(-__ldg(ab + 9 + k), r, __ldg(ab + k));
+  }
   const float x = (float)xi + 0.5f, y = (float)yi + 0.5f;  // get_pixel_grids, utils.py:155-160
   float q[3];
 #pragma unroll
   for (int r = 0; r < 3; ++r) {  // H @ (x, y, 1), utils.py:184
-    float acc = fmul(__ldg(Hm + r * 3 + 0), x);
-    acc = __fmaf_rn(__ldg(Hm + r * 3 + 1), y, acc);
-    q[r] = __fmaf_rn(__ldg(Hm + r * 3 + 2), 1.0f, acc);
+    float acc = fmul(Hm[r * 3 + 0], x);
+    acc = __fmaf_rn(Hm[r * 3 + 1], y, acc);
+    q[r] = __fmaf_rn(Hm[r * 3 + 2], 1.0f, acc);
   }
   const float den = fadd(q[2], 1e-9f);                       // :185
   float gx = fdiv(fdiv(q[0], den), (float)A.w);              // :185, :168
@@ -120,6 +147,57 @@ static int vis_launch(bool fused, const float* ref, const float* src, const floa
   return (int)cudaGetLastError();
 }
 
+
+// Per sample: A = K_r R_r R_l^T K_l^-1 and B = K_r R_r (c_r - c_l) n^T R_l^T K_l^-1 with c = -R^T t and n^T = third row of
+// R_l (get_homographies, utils.py:101-146), so that H(depth) = A - B / (depth + 1e-9).  Evaluated in double, rounded once.
+// cams [N,2,4,4]: [:,0] = extrinsics [R|t], [:,1] = intrinsics.
+__global__ void vis_setup_kernel(const float* __restrict__ left_cam, const float* __restrict__ right_cam, int N,
+                                 float* __restrict__ AB) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  const float* L = left_cam + (size_t)n * 32;
+  const float* Rc = right_cam + (size_t)n * 32;
+  double Rl[9], Rr[9], tl[3], tr[3], Kl[9], Kr[9];
+  for (int i = 0; i < 3; ++i) {
+    for (int j = 0; j < 3; ++j) {
+      Rl[i * 3 + j] = L[i * 4 + j]; Rr[i * 3 + j] = Rc[i * 4 + j];
+      Kl[i * 3 + j] = L[16 + i * 4 + j]; Kr[i * 3 + j] = Rc[16 + i * 4 + j];
+    }
+    tl[i] = L[i * 4 + 3]; tr[i] = Rc[i * 4 + 3];
+  }
+  // K_l^-1 by the adjugate
+  double Ki[9];
+  {
+    const double a = Kl[0], b = Kl[1], c = Kl[2], d = Kl[3], e = Kl[4], f = Kl[5], g = Kl[6], h = Kl[7], k = Kl[8];
+    const double c00 = e * k - f * h, c01 = -(d * k - f * g), c02 = d * h - e * g;
+    const double det = a * c00 + b * c01 + c * c02;
+    Ki[0] = c00 / det; Ki[1] = -(b * k - c * h) / det; Ki[2] = (b * f - c * e) / det;
+    Ki[3] = c01 / det; Ki[4] = (a * k - c * g) / det;  Ki[5] = -(a * f - c * d) / det;
+    Ki[6] = c02 / det; Ki[7] = -(a * h - b * g) / det; Ki[8] = (a * e - b * d) / det;
+  }
+  auto mm = [](const double* X, const double* Y, double* Z) {
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) Z[i * 3 + j] = X[i * 3 + 0] * Y[0 * 3 + j] + X[i * 3 + 1] * Y[1 * 3 + j] + X[i * 3 + 2] * Y[2 * 3 + j];
+  };
+  double RlT[9], M1[9], KR[9], Am[9], outer[9], T1[9], Bm[9], crel[3];
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) RlT[i * 3 + j] = Rl[j * 3 + i];
+  mm(RlT, Ki, M1);   // R_l^T K_l^-1, :132
+  mm(Kr, Rr, KR);
+  mm(KR, M1, Am);
+  for (int i = 0; i < 3; ++i) {  // c_right - c_left, c = -R^T t (:126-128)
+    const double cl = -(Rl[0 * 3 + i] * tl[0] + Rl[1 * 3 + i] * tl[1] + Rl[2 * 3 + i] * tl[2]);
+    const double cr = -(Rr[0 * 3 + i] * tr[0] + Rr[1 * 3 + i] * tr[1] + Rr[2 * 3 + i] * tr[2]);
+    crel[i] = cr - cl;
+  }
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) outer[i * 3 + j] = crel[i] * Rl[2 * 3 + j];  // c_rel @ fronto_direction, :131
+  mm(outer, M1, T1);
+  mm(KR, T1, Bm);
+  float* o = AB + (size_t)n * 18;
+  for (int k = 0; k < 9; ++k) { o[k] = (float)Am[k]; o[9 + k] = (float)Bm[k]; }
+}
+
 }  // namespace rmvd
 
 extern "C" int rmvd_homography_groupcorr_fwd(const float* ref, const float* src, const float* H, const int64_t* h_stride,
@@ -130,4 +208,29 @@ extern "C" int rmvd_homography_groupcorr_fwd(const float* ref, const float* src,
 extern "C" int rmvd_homography_warp_fwd(const float* src, const float* H, const int64_t* h_stride, int N, int C, int h, int w,
                                         int D, float* warped, void* stream) {
   return rmvd::vis_launch(false, nullptr, src, H, h_stride, N, C, h, w, D, 1, warped, stream);
+}
+
+extern "C" int rmvd_vis_cost_volume_fwd(const float* ref, const float* src, const float* left_cam, const float* right_cam,
+                                        const float* depth_start, const int64_t* start_stride, const float* depth_interval,
+                                        const int64_t* interval_stride, int N, int C, int h, int w, int D, int inv, int groups,
+                                        float* cost, void* workspace, size_t workspace_bytes, void* stream) {
+  using namespace rmvd;
+  if (!ref || !src || !left_cam || !right_cam || !depth_start || !start_stride || !depth_interval || !interval_stride || !cost)
+    return RMVD_E_NULL;
+  if (N <= 0 || C <= 0 || h <= 0 || w <= 0 || D <= 0 || N > 65535 || h >= 32768 || w >= 32768) return RMVD_E_SHAPE;
+  if (groups <= 0 || C % groups != 0) return RMVD_E_SHAPE;
+  if (!workspace || workspace_bytes < (size_t)N * 18 * sizeof(float)) return RMVD_E_WORKSPACE;
+  cudaStream_t st = (cudaStream_t)stream;
+  float* AB = (float*)workspace;
+  vis_setup_kernel<<<(N + 63) / 64, 64, 0, st>>>(left_cam, right_cam, N, AB);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return (int)e;
+  VisArgs A{};
+  A.ref = ref; A.src = src; A.H = nullptr; A.AB = AB; A.dstart = depth_start; A.dinter = depth_interval; A.inv = inv;
+  for (int k = 0; k < 3; ++k) { A.sst[k] = start_stride[k]; A.ist[k] = interval_stride[k]; }
+  A.N = N; A.C = C; A.h = h; A.w = w; A.D = D; A.groups = groups; A.out = cost;
+  const long long tot = (long long)((D + kVisPlanes - 1) / kVisPlanes) * h * w;
+  dim3 grid((unsigned)((tot + 255) / 256), N);
+  vis_homography_kernel<true><<<grid, 256, 0, st>>>(A);
+  return (int)cudaGetLastError();
 }

@@ -89,3 +89,15 @@ def test_shape_validation(cuda_lib):
     st = (ctypes.c_int64 * 4)(9, 9, 0, 0)
     assert cuda_lib.rmvd_homography_groupcorr_fwd(one, one, one, st, 1, 10, 4, 4, 2, 4, one, None) == -2   # C % groups != 0
     assert cuda_lib.rmvd_homography_warp_fwd(None, one, st, 1, 8, 4, 4, 2, one, None) == -1
+
+
+@pytest.mark.parametrize("case", VIS, ids=[c["name"] for c in VIS])
+def test_cost_volume_straight_from_the_cameras(cuda_lib, case):
+    """``rmvd_vis_cost_volume_fwd``: get_homographies folded into the kernel (H = A - B / (depth + 1e-9), A and B per sample in
+    double).  Against the reference's cost volume, whose own homographies carry float32 rounding of a longer chain: 5e-4 of
+    max|ref| (the ABI path that takes the reference's Hs tensor holds 1e-4, above)."""
+    from robustmvd_b200.blocks import utils as bu
+    g = load_golden("vis", case["name"])
+    cost = bu.vis_cost_volume(_t(case["ref"]), _t(case["src"]), _t(case["left_cam"]), _t(case["right_cam"]), case["depth_num"],
+                              _t(case["depth_start"]), _t(case["depth_interval"]), case["groups"], case["inv"]).cpu().numpy()
+    assert _rel(cost.reshape(-1)[::int(g["cost_stride"])], g["cost_sub"], float(g["cost_absmax"])) <= 5e-4

@@ -127,6 +127,16 @@ def main():
     vH[:, :, 0, 0, 0, 2] = torch.linspace(2.0, 40.0, vd, device="cuda")       # plane-dependent disparity
     add("vis_groupcorr_128x160_c32_d64", lambda: bu.groupwise_cost_volume(vref, vsrc, vH, vg),
         4 * vn * vc * vh * vw * 2 + 4 * vn * vg * vd * vh * vw, vn * vd * vh * vw, "voxels")
+    vcamL = torch.zeros((vn, 2, 4, 4), device="cuda")
+    vcamL[:, 0] = torch.eye(4, device="cuda")
+    vcamL[:, 1, :3, :3] = torch.tensor([[140.0, 0, 80.0], [0, 140.0, 64.0], [0, 0, 1.0]], device="cuda")
+    vcamR = vcamL.clone()
+    vcamR[:, 0, 0, 3] = 0.12
+    vds = (0.45 + 0.05 * torch.rand((vn, 1, vh, vw), device="cuda")).contiguous()      # per-pixel schedule (refinement stage)
+    vdi = torch.full((vn, 1, vh, vw), 0.008, device="cuda")
+    add("vis_cost_volume_from_cameras_perpixel_128x160_c32_d64",
+        lambda: bu.vis_cost_volume(vref, vsrc, vcamL, vcamR, vd, vds, vdi, vg),
+        4 * vn * vc * vh * vw * 2 + 8 * vn * vh * vw + 4 * vn * vg * vd * vh * vw, vn * vd * vh * vw, "voxels")
     # CVP-MVSNet proj_cost: refinement level 128x160, C=16, 2 source views, 8 per-pixel hypotheses
     import types
     from robustmvd_b200.blocks import cvp_mvsnet_components as cvpc
