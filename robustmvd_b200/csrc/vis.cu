@@ -36,9 +36,10 @@ struct VisTap {
   float nw, ne, sw, se;
 };
 
+template <bool kAnalytic>
 __device__ __forceinline__ VisTap vis_tap(const VisArgs& A, int n, int d, int yi, int xi) {
   float Hm[9];
-  if (A.H) {
+  if (!kAnalytic) {
     const float* Hp = A.H + n * A.hst[0] + d * A.hst[1] + yi * A.hst[2] + xi * A.hst[3];
 #pragma unroll
     for (int k = 0; k < 9; ++k) Hm[k] = __ldg(Hp + k);
@@ -87,7 +88,7 @@ __device__ __forceinline__ float vis_gather(const float* __restrict__ sc, const 
   return __ldg(sc + t.o_nw) * t.nw + __ldg(sc + t.o_ne) * t.ne + __ldg(sc + t.o_sw) * t.sw + __ldg(sc + t.o_se) * t.se;
 }
 
-template <bool kFused>
+template <bool kFused, bool kAnalytic>
 __global__ void __launch_bounds__(256) vis_homography_kernel(const VisArgs A) {
   const int n = blockIdx.y;
   const int P = A.h * A.w;
@@ -98,7 +99,7 @@ __global__ void __launch_bounds__(256) vis_homography_kernel(const VisArgs A) {
   const int yi = p / A.w, xi = p - yi * A.w;
   VisTap tap[kVisPlanes];
 #pragma unroll
-  for (int k = 0; k < kVisPlanes; ++k) tap[k] = vis_tap(A, n, min(d0 + k, A.D - 1), yi, xi);
+  for (int k = 0; k < kVisPlanes; ++k) tap[k] = vis_tap<kAnalytic>(A, n, min(d0 + k, A.D - 1), yi, xi);
   const float* src = A.src + (size_t)n * A.C * P;
   const size_t DP = (size_t)A.D * P;
   if (kFused) {
@@ -142,8 +143,8 @@ static int vis_launch(bool fused, const float* ref, const float* src, const floa
   A.N = N; A.C = C; A.h = h; A.w = w; A.D = D; A.groups = groups; A.out = out;
   const long long tot = (long long)((D + kVisPlanes - 1) / kVisPlanes) * h * w;
   dim3 grid((unsigned)((tot + 255) / 256), N);
-  if (fused) vis_homography_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(A);
-  else vis_homography_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(A);
+  if (fused) vis_homography_kernel<true, false><<<grid, 256, 0, (cudaStream_t)stream>>>(A);
+  else vis_homography_kernel<false, false><<<grid, 256, 0, (cudaStream_t)stream>>>(A);
   return (int)cudaGetLastError();
 }
 
@@ -231,6 +232,6 @@ extern "C" int rmvd_vis_cost_volume_fwd(const float* ref, const float* src, cons
   A.N = N; A.C = C; A.h = h; A.w = w; A.D = D; A.groups = groups; A.out = cost;
   const long long tot = (long long)((D + kVisPlanes - 1) / kVisPlanes) * h * w;
   dim3 grid((unsigned)((tot + 255) / 256), N);
-  vis_homography_kernel<true><<<grid, 256, 0, st>>>(A);
+  vis_homography_kernel<true, true><<<grid, 256, 0, st>>>(A);
   return (int)cudaGetLastError();
 }
