@@ -149,8 +149,11 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":   # NCCL writes its version banner to STDOUT: keep the
-            os.environ["NCCL_DEBUG"] = "WARN"                        # one-JSON-line contract of this script
+        # torch / NCCL write a "NCCL version ..." banner to file descriptor 1 when the communicator comes up: point fd 1 at
+        # stderr until the JSON line is printed (one-JSON-line contract of this script)
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
     _lib.load()
     frames = args.frames
@@ -256,6 +259,9 @@ def run_ours(args):
         })
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = time_cpu_baseline(3, 1)
+        if world > 1:
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
