@@ -5,7 +5,7 @@ import subprocess
 
 CSRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc")
 LIB = os.path.join(CSRC, "librmvd_b200.so")
-SOURCES = ("psweep.cu", "psweep_band.cu", "psweep_tc.cu", "psweep_bwd.cu", "mvs.cu", "fusion.cu", "vis.cu")
+SOURCES = ("psweep.cu", "psweep_band.cu", "psweep_tc.cu", "psweep_ws.cu", "psweep_bwd.cu", "mvs.cu", "fusion.cu", "vis.cu")
 HEADERS = ("common.cuh", "psweep.cuh", os.path.join("..", "..", "include", "rmvd_b200.h"))
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "-shared"]
@@ -30,7 +30,8 @@ def build(force=False, verbose=False):
     """Compile the library if missing or older than its sources.  Returns the path of the .so."""
     if not force and not is_stale():
         return LIB
-    cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + list(SOURCES)
+    defs = ["-D" + d for d in os.environ.get("RMVD_BUILD_DEFS", "").split() if d]   # e.g. RMVD_WS_WATCHDOG (development builds)
+    cmd = [_nvcc()] + NVCC_FLAGS + defs + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + list(SOURCES)
     res = subprocess.run(cmd, cwd=CSRC, capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)

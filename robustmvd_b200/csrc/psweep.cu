@@ -362,7 +362,7 @@ using namespace rmvd;
 
 extern "C" size_t rmvd_psweep_workspace_bytes(int N, int C, int h, int w, int V, const int* hs, const int* ws) {
   size_t tot = (((size_t)N * C * h * w * sizeof(float)) + 255) / 256 * 256;  // channels-last key copy
-  for (int v = 0; v < V; ++v) tot += (((size_t)N * C * hs[v] * ws[v] * sizeof(float)) + 255) / 256 * 256;
+  for (int v = 0; v < V; ++v) tot += (psweep_ws_src_bytes(N, C, hs[v], ws[v]) + 255) / 256 * 256;   // rows padded to 8 texels
   return tot;
 }
 
@@ -392,24 +392,29 @@ extern "C" int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* f
 
   // kernel choice: tcgen05 kernel (C % 32 == 0, per-plane hypotheses) > banded fp32 kernel (C % 32 == 0, source map
   // <= 65536 texels) > general direct kernel.  RMVD_PSWEEP_KERNEL=tc|band|direct restricts the choice (A/B runs only).
-  const char* force = getenv("RMVD_PSWEEP_KERNEL");
-  const bool allow_tc = !force || strcmp(force, "tc") == 0;
+  static const char* const force = getenv("RMVD_PSWEEP_KERNEL");   // read once per process
+  const bool allow_ws = !force || strcmp(force, "ws") == 0;
+  const bool allow_tc = (force && strcmp(force, "tc") == 0);
   const bool allow_band = !force || strcmp(force, "band") == 0;
   bool band = (C % 32 == 0) && allow_band;
   for (int v = 0; v < V; ++v) band = band && ((long long)hs[v] * ws[v] <= 65536);
-  bool tc = allow_tc;
+  bool tc = allow_tc, wsk = allow_ws;
   {
     PsweepArgs T{};
     T.C = C;
     for (int k = 0; k < 4; ++k) T.ist[k] = inv_stride[k];
     tc = tc && psweep_tc_eligible(T, 0);
+    wsk = wsk && psweep_ws_eligible(T, 0) && (long long)N * (V < kMaxViews ? V : kMaxViews) <= 65535;
   }
 
   char* wsp = (char*)workspace;
   float* key_nhwc = (float*)wsp;
   wsp += (((size_t)N * C * h * w * sizeof(float)) + 255) / 256 * 256;
   const int l2 = normalize_mode == RMVD_NORM_BEFORE;
-  if (tc) {
+  if (wsk) {
+    int rc = repack_split(feat_key, key_nhwc, N, C, h * w, l2, st);
+    if (rc) return rc;
+  } else if (tc) {
     // repacked together with the first group of source maps below (one launch)
   } else if (band) {
     int rc = repack(feat_key, key_nhwc, N, C, h * w, l2, st);
@@ -430,8 +435,10 @@ extern "C" int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* f
     for (int j = 0; j < nv; ++j) {
       const int v = v0 + j;
       float* dst = (float*)wsp;
-      wsp += (((size_t)N * C * hs[v] * ws[v] * sizeof(float)) + 255) / 256 * 256;
-      if (tc) {
+      wsp += (psweep_ws_src_bytes(N, C, hs[v], ws[v]) + 255) / 256 * 256;
+      if (wsk) {
+        rp_src[rp_n] = feat_src[v]; rp_dst[rp_n] = dst; rp_P[rp_n] = hs[v] * ws[v]; ++rp_n;
+      } else if (tc) {
         rp_src[rp_n] = feat_src[v]; rp_dst[rp_n] = dst; rp_P[rp_n] = hs[v] * ws[v]; ++rp_n;
       } else {
         int rc = repack(feat_src[v], dst, N, C, hs[v] * ws[v], l2, st);
@@ -443,14 +450,18 @@ extern "C" int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* f
       A.hs[j] = hs[v];
       A.ws[j] = ws[v];
     }
-    if (tc) {
+    if (wsk) {
+      int rc = repack_grouped_batch(rp_src, rp_dst, hs + v0, ws + v0, rp_n, N, C, l2, st);
+      if (rc) return rc;
+    } else if (tc) {
       int rc = repack_split_batch(rp_src, rp_dst, rp_P, rp_n, N, C, l2, st);
       if (rc) return rc;
     }
     A.N = N; A.C = C; A.h = h; A.w = w; A.S = S; A.s_begin = s_begin; A.s_end = s_end;
     A.norm = normalize_mode; A.out_S = out_S; A.out_s0 = out_s0; A.v0 = v0;
     A.corr = corr; A.mask = mask; A.dbg_ix0 = dbg_ix0; A.dbg_iy0 = dbg_iy0; A.dbg_geom = dbg_geom;
-    int rc = tc ? launch_psweep_tc(A, key_nhwc, nv, st)
+    int rc = wsk ? launch_psweep_ws(A, key_nhwc, nv, st)
+                : tc ? launch_psweep_tc(A, key_nhwc, nv, st)
                 : band ? launch_psweep_band(A, key_nhwc, nv, st) : dispatch_corr<false>(A, nv, st);
     if (rc) return rc;
   }

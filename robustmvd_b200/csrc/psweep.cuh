@@ -42,4 +42,12 @@ int repack_split_batch(const float* const* srcs, void* const* dsts, const int* P
                        cudaStream_t st);
 int launch_psweep_tc(const PsweepArgs& A, const void* key_split, int nviews, cudaStream_t st);
 
+// psweep_ws.cu: persistent warp-specialised tcgen05 kernel (one CTA per SM).  The key map uses repack_split()'s layout, the
+// source maps the grouped split layout of repack_grouped_batch() (rows padded to multiples of 8 texels: psweep_ws_src_bytes).
+bool psweep_ws_eligible(const PsweepArgs& A, int nviews);
+size_t psweep_ws_src_bytes(int N, int C, int hs, int ws);
+int repack_grouped_batch(const float* const* srcs, void* const* dsts, const int* hs, const int* ws, int count, int N, int C, int l2norm,
+                         cudaStream_t st);
+int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, cudaStream_t st);
+
 }  // namespace rmvd

@@ -1,0 +1,1230 @@
+// Plane-sweep correlation, persistent warp-specialised form (sm_100a): one CTA per SM owns all 512 TMEM columns and
+// loops over work items (tile of 64 key pixels, sample, source view).  Same contraction as psweep_tc.cu --
+// corr = bilinear(G), G = key . band^T over the source texels under the tile's epipolar band
+// (planesweep_corr.py:174-186 restricted to where it is sampled), bf16 hi/lo split operands on tcgen05 -- but the serial
+// phases of a tile no longer wait for one another:
+//
+//   warp 0      planner    per item: calibration (planesweep_corr.py:228-300), tile slots; per chunk of planes: the band
+//                          (one 8-aligned [xa, xa + len) span per source row), the per-plane terms and dead-plane bits,
+//                          published as a self-contained chunk descriptor in a ring of three
+//   warp 1      producer   per (pass of 128 band texels, 32 channels): one bulk copy (cp.async.bulk, no tensor map) per
+//                          band row straight into the UMMA no-swizzle K-major stage; ring of six 16 KB stages
+//   warp 2      MMA        one elected lane: 4 x tcgen05.mma (M = 128 = [key_hi ; key_lo] rows, N <= 128, K = 16) per stage
+//                          into one of three 128-column accumulators; tcgen05.commit frees stages / publishes passes
+//   warps 4-15  consumers  drain the accumulators (tcgen05.ld, key_hi + key_lo rows added by one shuffle) into the shared
+//                          G tile, then sample it: filtered locate (integer corner and 0/1 mask bit-exact, see below),
+//                          four G reads, 128-byte streaming stores of corr and mask.  While they sample chunk i the
+//                          planner / producer / MMA warps already work on chunk i + 1 (or the next tile); the key tile
+//                          of the next item goes to TMEM during the last chunk of the current one.
+//
+// Source operand layout ("grouped split", written by nchw_to_grouped_kernel): per (sample, 32-channel block kc, group of 8
+// consecutive texels of one source row) one 1024-byte block [chunk j = 0..7][texel r = 0..7][8 bf16]; chunks 0..3 hold
+// the hi halves of channels 8j..8j+7, chunks 4..7 the lo halves (x = hi + lo to 2^-17).  Rows are padded to a multiple of
+// 8 texels (zeros).  A band row span that starts at a multiple of 8 is therefore ONE contiguous run, and the copy lands as
+// UMMA's canonical K-major SWIZZLE_NONE layout (core matrix = 8 texels x 16 bytes; LBO = 128 B between K chunks,
+// SBO = 1024 B between 8-texel groups).
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include <cstdio>
+#include <cstdlib>
+
+#include "psweep.cuh"
+
+namespace rmvd {
+namespace ws {
+
+constexpr int kThreads = 512;
+constexpr int kPx = 64;                      // key pixels per tile (A' has 2 * kPx = 128 rows: key_hi, key_lo)
+constexpr int kNT = 128;                     // band texels per pass = N of one MMA = columns of one accumulator
+constexpr int kNBuf = 3;                     // accumulators: a whole chunk (<= 3 passes) can sit in TMEM
+constexpr int kKC = 32;                      // channels per stage
+constexpr int kStages = 6;                   // ring of B' stages
+constexpr int kStageBytes = kNT * 128;       // 16 KB: 128 texels x [hi 32 ch | lo 32 ch] bf16
+constexpr int kMaxC = 256;                   // A' in TMEM: C / 2 columns
+constexpr int kTmemA = kNBuf * kNT;          // TMEM columns: D = [0, 384), A' = [384, 384 + C / 2)
+constexpr int kTmemCols = 512;
+constexpr int kRMax = kNBuf * kNT;           // band capacity of one chunk (G columns)
+constexpr int kGPitch = kRMax + 2;           // 2 (mod 32): conflict-free sampling reads and drain stores (see psweep_tc.cu)
+static_assert(kGPitch % 32 == 2, "G pitch must be 2 mod 32");
+constexpr int kMaxRows = 64;                 // source rows a band may span
+constexpr int kMaxPlanes = 256;              // planes per chunk
+constexpr int kDescs = 3;                    // chunk descriptors in flight
+constexpr int kConsWarps = 12;
+constexpr int kConsThreads = kConsWarps * 32;
+constexpr int kStep = kConsWarps / 2;        // planes between two sampling steps of a warp
+
+struct __align__(16) PlaneTerm { float ed, id, md, zs; };   // e*d, i*d, m*d, 1/d of one plane (planesweep_corr.py:334,343,492)
+// Texels [xa, xa + len) of one source row of the band; xa and len are multiples of 8.  G column of texel x = offp + x.
+struct __align__(16) RowSpan { int xa, lenm1, offp, len; };
+
+enum { kStop = 0, kGemm = 1, kDirect = 2 };
+
+struct __align__(16) ChunkDesc {
+  RowSpan rows[kMaxRows];
+  PlaneTerm planes[kMaxPlanes];
+  int pix[kPx];                    // key pixel (y * w + x) of every tile slot, -1 for empty slots
+  unsigned dead[kMaxPlanes / 32];  // planes without any valid sample in this tile
+  Epi E;
+  const __nv_bfloat16* key;        // split key map of the sample: [pixel][C/32][hi 32 | lo 32]
+  const __nv_bfloat16* src;        // grouped split source map of the (view, sample)
+  unsigned long long out_base;     // element offset of plane index 0 of this (view, sample) in the outputs
+  int hs, ws, wg, G;               // wg: 8-texel groups per source row, G: groups per map
+  int n, v, kind, first, last;     // first / last chunk of its tile
+  int s0, len, R, ymin, H, out_plane0;
+  int pad_[1];
+};
+static_assert(sizeof(ChunkDesc) % 16 == 0, "descriptor ring alignment");
+
+struct WsConst {                   // per-launch constants of the out-of-line paths
+  float* corr; float* mask; int32_t* dbg_ix0; int32_t* dbg_iy0; uint8_t* dbg_geom;
+  const float* G;
+  int P, C, w;
+  float inv_scale;
+};
+__shared__ WsConst s_k;
+
+// barrier slots
+constexpr int kBarFull = 0, kBarFree = kBarFull + kStages, kBarAcc = kBarFree + kStages, kBarDrained = kBarAcc + kNBuf,
+              kBarCReady = kBarDrained + kNBuf, kBarCFree = kBarCReady + kDescs, kBarAReady = kBarCFree + kDescs,
+              kNumBars = kBarAReady + 1;
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+#ifdef RMVD_WS_WATCHDOG
+// Development aid: a wait that does not complete within ~2^22 polls reports itself and releases every waiter of the grid, so a
+// protocol error ends as a wrong result with a message instead of a hung GPU.
+__device__ int g_ws_abort;
+#endif
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+  unsigned done = 0;
+#ifdef RMVD_WS_WATCHDOG
+  unsigned polls = 0;
+#endif
+  while (!done) {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.b32 %0, 1, 0, p;\n\t}\n"
+                 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+#ifdef RMVD_WS_WATCHDOG
+    if (!done && (++polls & 1023u) == 0) {
+      if (*reinterpret_cast<volatile int*>(&g_ws_abort)) return;
+      if (polls > (1u << 22)) {
+        if ((threadIdx.x & 31) == 0 || threadIdx.x == 64)
+          printf("[psweep_ws watchdog] block %d warp %d: barrier at smem %u parity %u never completed\n", blockIdx.x, threadIdx.x >> 5, bar, parity);
+        atomicExch(&g_ws_abort, 1);
+        return;
+      }
+    }
+#endif
+  }
+}
+#ifdef RMVD_WS_STATS
+// Development build: per-role cycle counters (one recording lane per role), printed by launch_psweep_ws after a synchronise.
+__device__ unsigned long long g_ws_stats[32];
+#define WS_T0() const long long ws_t0_ = clock64()
+#define WS_ADD(i) atomicAdd(&g_ws_stats[i], (unsigned long long)(clock64() - ws_t0_))
+#define WS_CNT(i, n) atomicAdd(&g_ws_stats[i], (unsigned long long)(n))
+#else
+#define WS_T0()
+#define WS_ADD(i)
+#define WS_CNT(i, n)
+#endif
+__device__ __forceinline__ void mbar_arrive(unsigned bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool elect_one() {
+  unsigned pred;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}\n" : "=r"(pred));
+  return pred != 0;
+}
+__device__ __forceinline__ void cons_bar() { asm volatile("bar.sync 1, %0;\n" ::"n"(kConsThreads) : "memory"); }
+// K-major SWIZZLE_NONE operand: lbo = bytes between 16-byte K chunks, sbo = bytes between 8-row groups; version 1.
+__device__ __forceinline__ unsigned long long umma_desc(unsigned addr, unsigned lbo, unsigned sbo) {
+  return (unsigned long long)((addr >> 4) & 0x3fffu) | ((unsigned long long)((lbo >> 4) & 0x3fffu) << 16) |
+         ((unsigned long long)((sbo >> 4) & 0x3fffu) << 32) | (1ull << 46);
+}
+__device__ __forceinline__ unsigned umma_idesc_bf16(int M, int N) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((unsigned)(N >> 3) << 17) | ((unsigned)(M >> 4) << 24);
+}
+__device__ __forceinline__ void tc_mma(unsigned d_tmem, unsigned a_tmem, unsigned long long b_desc, unsigned idesc, unsigned acc) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+               "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}\n" ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(acc)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(unsigned addr, float* v) {
+  unsigned r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,"
+      "%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+        "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+        "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+        "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(addr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+// One contiguous run global -> shared, completing its bytes on the mbarrier (SASS: UBLKCP).
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(dst), "l"(src),
+               "r"(bytes), "r"(bar)
+               : "memory");
+}
+
+// key map, split channels-last lines (nchw_to_split_tile_kernel of psweep_tc.cu): element (p, c)
+__device__ __forceinline__ size_t key_index(size_t p, int c, int C) { return (p * (size_t)(C >> 5) + (size_t)(c >> 5)) * 64 + (c & 31); }
+__device__ __forceinline__ float key_at(const __nv_bfloat16* key, int p, int c, int C) {
+  const size_t o = key_index((size_t)p, c, C);
+  return __bfloat162float(key[o]) + __bfloat162float(key[o + 32]);
+}
+// source map, grouped split layout: element (y, x, c) in bf16 units; the lo half sits 256 elements (4 chunks) further
+__device__ __forceinline__ size_t src_index(int G, int wg, int y, int x, int c) {
+  return ((size_t)(c >> 5) * G + (size_t)y * wg + (x >> 3)) * 512 + ((c >> 3) & 3) * 64 + (x & 7) * 8 + (c & 7);
+}
+__device__ __forceinline__ float src_at(const ChunkDesc* D, int y, int x, int c) {
+  const size_t o = src_index(D->G, D->wg, y, x, c);
+  return __bfloat162float(D->src[o]) + __bfloat162float(D->src[o + 256]);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// NCHW fp32 -> grouped split copy of up to kMaxViews source maps in one launch.  CTA = 32 texels of one source row x 128
+// channels (grid: row tiles x channel blocks x (map, sample)); kNorm: L2-normalised along C first (normalize(x, dim=1),
+// planesweep_corr.py:8-10, :170-172), the CTA then walks all channel blocks itself.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kRpCh = 128;
+struct GroupBatch {
+  const float* src[kMaxViews];
+  __nv_bfloat16* dst[kMaxViews];
+  int hs[kMaxViews], ws[kMaxViews];
+};
+
+template <bool kNorm>
+__global__ void __launch_bounds__(256) nchw_to_grouped_kernel(const GroupBatch B, int C, int N) {
+  __shared__ float tile[kRpCh][33];
+  __shared__ float s_norm[32];
+  const int which = blockIdx.z / N, n = blockIdx.z - which * N;
+  const int hs = B.hs[which], ws = B.ws[which];
+  const int wg = (ws + 7) >> 3, tpr = (wg + 3) >> 2;        // groups per row, 32-texel tiles per row
+  if ((int)blockIdx.x >= tpr * hs) return;                   // maps of different sizes share the grid of the largest
+  const int y = blockIdx.x / tpr, x0 = (blockIdx.x - y * tpr) * 32;
+  const int G = hs * wg;
+  const size_t Ps = (size_t)hs * ws;
+  const float* __restrict__ src = B.src[which] + (size_t)n * C * Ps + (size_t)y * ws;
+  __nv_bfloat16* __restrict__ dst = B.dst[which] + (size_t)n * (C >> 5) * G * 512;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const bool in = x0 + tx < ws;
+  float inv_norm = 1.0f;
+  if (kNorm) {
+    float acc = 0.f;
+    for (int c = ty; c < C; c += 8) {
+      const float v = in ? __ldg(src + (size_t)c * Ps + x0 + tx) : 0.f;
+      acc = fmaf(v, v, acc);
+    }
+    tile[ty][tx] = acc;
+    __syncthreads();
+    if (ty == 0) {
+      float t = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) t += tile[k][tx];
+      s_norm[tx] = sqrtf(t) + 1e-9f;
+    }
+    __syncthreads();
+    inv_norm = s_norm[tx];                                    // divisor of this thread's loads (pixel tx)
+  }
+  const int cb0 = kNorm ? 0 : blockIdx.y * kRpCh, cb1 = kNorm ? C : min(C, cb0 + kRpCh);
+  for (int c0 = cb0; c0 < cb1; c0 += kRpCh) {
+    const int nc = min(kRpCh, C - c0);                        // multiple of 32
+    float v[kRpCh / 8];
+#pragma unroll
+    for (int k = 0; k < kRpCh / 8; ++k) v[k] = (ty + 8 * k < nc && in) ? __ldg(src + (size_t)(c0 + ty + 8 * k) * Ps + x0 + tx) : 0.f;
+#pragma unroll
+    for (int k = 0; k < kRpCh / 8; ++k) tile[ty + 8 * k][tx] = kNorm ? fdiv(v[k], inv_norm) : v[k];
+    __syncthreads();
+    // one 16-byte chunk pair (hi, lo) per item: (channel block kcl, group g, chunk jj, texel r); a warp = the four hi chunks
+    // (512 contiguous bytes) and the four lo chunks of one group
+    for (int idx = threadIdx.x; idx < (nc >> 5) * 128; idx += 256) {
+      const int r = idx & 7, jj = (idx >> 3) & 3, g = (idx >> 5) & 3, kcl = idx >> 7;
+      const int gx = (x0 >> 3) + g;
+      if (gx < wg) {
+        float f[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] = tile[kcl * 32 + jj * 8 + e][g * 8 + r];
+        uint4 hi4, lo4;
+        unsigned* hp = reinterpret_cast<unsigned*>(&hi4);
+        unsigned* lp = reinterpret_cast<unsigned*>(&lo4);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const __nv_bfloat162 hi = __floats2bfloat162_rn(f[2 * e], f[2 * e + 1]);
+          const __nv_bfloat162 lo = __floats2bfloat162_rn(f[2 * e] - __low2float(hi), f[2 * e + 1] - __high2float(hi));
+          hp[e] = *reinterpret_cast<const unsigned*>(&hi);
+          lp[e] = *reinterpret_cast<const unsigned*>(&lo);
+        }
+        __nv_bfloat16* o = dst + ((size_t)((c0 >> 5) + kcl) * G + (size_t)y * wg + gx) * 512 + jj * 64 + r * 8;
+        *reinterpret_cast<uint4*>(o) = hi4;
+        *reinterpret_cast<uint4*>(o + 256) = lo4;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Exact sample location (bit-identical to epi_sample() + pix_to_unnorm() + bilinear_setup() of common.cuh).
+// ---------------------------------------------------------------------------------------------------------
+struct Sample {
+  int x0, y0;             // floor of the un-normalised coordinate, saturated like sat_index()
+  float nw, ne, sw, se;   // bilinear weights, 0 for corners outside the source map
+  bool valid, geom;
+};
+struct Pixel {            // per-thread constants of its key pixel
+  float u_h, v_h, k_h, z_pole;
+  int mode;               // 1: k_h > 0, 2: k_h < 0, 3: k_h == 0 && m > 0, 0: never visible (planesweep_corr.py:500-504)
+};
+
+__device__ __forceinline__ void finish(float ix, float iy, int hs, int ws, bool geom, Sample& L) {
+  const float x0f = floorf(ix), y0f = floorf(iy);
+  const float wx1 = fsub(ix, x0f), wx0 = fsub(1.0f, wx1);
+  const float wy1 = fsub(iy, y0f), wy0 = fsub(1.0f, wy1);
+  L.x0 = (int)fminf(fmaxf(x0f, -2.0f), (float)ws);          // saturating keeps every range test exact; NaN -> -2
+  L.y0 = (int)fminf(fmaxf(y0f, -2.0f), (float)hs);
+  const bool x0_in = (unsigned)L.x0 < (unsigned)ws, x1_in = (unsigned)(L.x0 + 1) < (unsigned)ws;
+  const bool y0_in = (unsigned)L.y0 < (unsigned)hs, y1_in = (unsigned)(L.y0 + 1) < (unsigned)hs;
+  L.nw = (y0_in && x0_in) ? fmul(wy0, wx0) : 0.0f;
+  L.ne = (y0_in && x1_in) ? fmul(wy0, wx1) : 0.0f;
+  L.sw = (y1_in && x0_in) ? fmul(wy1, wx0) : 0.0f;
+  L.se = (y1_in && x1_in) ? fmul(wy1, wx1) : 0.0f;
+  const float msum = fadd(fadd(fadd(L.nw, L.ne), L.sw), L.se);
+  L.geom = geom;
+  L.valid = sampling_mask(msum) && geom;
+}
+
+__device__ __forceinline__ void locate(const Pixel& px, const PlaneTerm& pt, int hs, int ws, Sample& L) {
+  const float den = fadd(px.k_h, pt.md), nu = fadd(px.u_h, pt.ed), nv = fadd(px.v_h, pt.id);  // :334, :343
+  const float zs = pt.zs;
+  const bool vis_src = (px.mode == 1) ? (zs > px.z_pole) : (px.mode == 2) ? (zs < px.z_pole) : (px.mode == 3);
+  const bool geom = (zs > 0.0f) && vis_src;                                                     // :499-506
+  const float us = replace_nonfinite(fdiv(nu, den)), vs = replace_nonfinite(fdiv(nv, den));
+  finish(pix_to_unnorm(us, ws), pix_to_unnorm(vs, hs), hs, ws, geom, L);
+}
+
+__device__ __forceinline__ Pixel pixel_consts(const Epi& E, int p, int w) {
+  const int yi = p / w, xi = p - yi * w;
+  const EpiPix ep = epi_pixel(E, xi, yi);
+  Pixel px;
+  px.u_h = ep.u_h; px.v_h = ep.v_h; px.k_h = ep.k_h;
+  px.z_pole = -fdiv(E.m, ep.k_h);                                                               // :330
+  px.mode = (ep.k_h > 0.0f) ? 1 : (ep.k_h < 0.0f) ? 2 : ((ep.k_h == 0.0f) && (E.m > 0.0f)) ? 3 : 0;
+  return px;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Band of one (tile, inverse-depth interval [dmin, dmax]): union over the tile's pixels of their dilated epipolar segments,
+// one span per source row, start and length multiples of 8 texels (= whole 1024-byte groups of the source layout).
+// Executed by ONE converged warp (lane l owns tile slots l, l + 32 and band rows l, l + 32).  Writes rows[0..H); returns R
+// (G columns), -1 if a pixel is irregular (pole inside the interval, non-finite end points), or a value > kRMax.
+// ---------------------------------------------------------------------------------------------------------
+__device__ int band_warp(RowSpan* rows, const int* pix, const Epi& E, int w_key, float dmin, float dmax, int hs, int ws, int& ymin_out,
+                         int& H_out) {
+  const int lane = threadIdx.x & 31;
+  constexpr float kEps = 0.05f;
+  float ua[2], va[2], ub[2], vb[2];
+  bool act[2], bad = false;
+  ymin_out = 0; H_out = 0;
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int p = pix[lane + 32 * j];
+    act[j] = p >= 0;
+    ua[j] = va[j] = ub[j] = vb[j] = 0.f;
+    if (act[j]) {
+      const int yi = p / w_key, xi = p - yi * w_key;
+      const EpiPix e = epi_pixel(E, xi, yi);
+      const float dena = e.k_h + E.m * dmin, denb = e.k_h + E.m * dmax;
+      bool ok = (dena > 0.f && denb > 0.f) || (dena < 0.f && denb < 0.f);   // no pole inside the interval (false for nan too)
+      ua[j] = (e.u_h + E.e * dmin) / dena; va[j] = (e.v_h + E.i * dmin) / dena;
+      ub[j] = (e.u_h + E.e * dmax) / denb; vb[j] = (e.v_h + E.i * dmax) / denb;
+      ok = ok && (fabsf(ua[j]) < 1e7f) && (fabsf(va[j]) < 1e7f) && (fabsf(ub[j]) < 1e7f) && (fabsf(vb[j]) < 1e7f);
+      bad = bad || !ok;
+    }
+  }
+  if (__any_sync(kFullMask, bad)) return -1;
+  int ylo[2], yhi[2];
+  int wy0 = 0x7fffffff, wy1 = -0x7fffffff;
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    ylo[j] = 1; yhi[j] = 0;
+    if (act[j]) {
+      ylo[j] = max(0, (int)floorf(fminf(va[j], vb[j]) - 0.5f - kEps));
+      yhi[j] = min(hs - 1, (int)floorf(fmaxf(va[j], vb[j]) - 0.5f + kEps) + 1);
+      if (ylo[j] <= yhi[j]) { wy0 = min(wy0, ylo[j]); wy1 = max(wy1, yhi[j]); }
+    }
+  }
+  wy0 = __reduce_min_sync(kFullMask, wy0);
+  wy1 = __reduce_max_sync(kFullMask, wy1);
+  if (wy0 > wy1) return 0;                          // no sample of the tile touches the source map
+  const int H = wy1 - wy0 + 1;
+  if (H > kMaxRows) return kRMax + H;
+  int sxa[2] = {0, 0}, slen[2] = {0, 0};          // lane r keeps band rows r and r + 32
+  float inv_dv[2], du[2];
+  bool sloped[2];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const float dv = vb[j] - va[j];
+    du[j] = ub[j] - ua[j];
+    sloped[j] = fabsf(dv) > 1e-6f;
+    inv_dv[j] = sloped[j] ? 1.0f / dv : 0.f;
+  }
+  int total = 0;                                    // columns so far (warp-uniform): a band that cannot fit stops early
+  for (int y = wy0; y <= wy1; ++y) {               // warp-uniform bounds
+    int xlo = 0x7fffffff, xhi = -0x7fffffff;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      if (act[j] && y >= ylo[j] && y <= yhi[j]) {
+        float t0 = 0.f, t1 = 1.f;
+        if (sloped[j]) {
+          const float ta = ((float)y - 0.5f - kEps - va[j]) * inv_dv[j], tb = ((float)y + 1.5f + kEps - va[j]) * inv_dv[j];
+          t0 = fmaxf(0.f, fminf(ta, tb) - 1e-4f);
+          t1 = fminf(1.f, fmaxf(ta, tb) + 1e-4f);
+        }
+        if (t0 <= t1) {
+          const float u0 = ua[j] + t0 * du[j], u1 = ua[j] + t1 * du[j];
+          const int a = max(0, (int)floorf(fminf(u0, u1) - 0.5f - kEps));
+          const int b = min(ws - 1, (int)floorf(fmaxf(u0, u1) - 0.5f + kEps) + 1);
+          if (a <= b) { xlo = min(xlo, a); xhi = max(xhi, b); }
+        }
+      }
+    }
+    xlo = __reduce_min_sync(kFullMask, xlo);
+    xhi = __reduce_max_sync(kFullMask, xhi);
+    if (xlo <= xhi) {
+      const int a8 = xlo & ~7, len8 = ((xhi + 8) & ~7) - a8;   // whole groups: [a8, a8 + len8) covers [xlo, xhi]
+      const int r = y - wy0;
+      if (lane == (r & 31)) {
+        if (r < 32) { sxa[0] = a8; slen[0] = len8; } else { sxa[1] = a8; slen[1] = len8; }
+      }
+      total += len8;
+      if (total > kRMax) return total;
+    }
+  }
+  int i0 = slen[0], i1 = slen[1];                  // inclusive prefix sums over <= 64 rows
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int a = __shfl_up_sync(kFullMask, i0, o), b = __shfl_up_sync(kFullMask, i1, o);
+    if (lane >= o) { i0 += a; i1 += b; }
+  }
+  const int tot0 = __shfl_sync(kFullMask, i0, 31), tot1 = __shfl_sync(kFullMask, i1, 31);
+  if (lane < H) { RowSpan r; r.xa = sxa[0]; r.len = slen[0]; r.lenm1 = max(slen[0] - 1, 0); r.offp = i0 - slen[0] - sxa[0]; rows[lane] = r; }
+  if (lane + 32 < H) { RowSpan r; r.xa = sxa[1]; r.len = slen[1]; r.lenm1 = max(slen[1] - 1, 0); r.offp = tot0 + i1 - slen[1] - sxa[1]; rows[lane + 32] = r; }
+  ymin_out = wy0; H_out = H;
+  __syncwarp();
+  return tot0 + tot1;
+}
+
+// Inverse-depth interval of planes [s, s + n) (the schedule need not be monotone), by one converged warp.  False if not finite.
+__device__ bool plane_interval(const float* __restrict__ invd, long long stride, int s, int n, float& dlo, float& dhi) {
+  const int lane = threadIdx.x & 31;
+  dlo = INFINITY; dhi = -INFINITY;
+  float d[kMaxPlanes / 32];
+#pragma unroll
+  for (int k = 0; k < kMaxPlanes / 32; ++k) {
+    const int i = lane + 32 * k;
+    d[k] = (i < n) ? invd[(size_t)(s + i) * stride] : NAN;
+  }
+#pragma unroll
+  for (int k = 0; k < kMaxPlanes / 32; ++k) {       // fminf / fmaxf drop nans: a nan plane has no valid sample
+    dlo = fminf(dlo, d[k]); dhi = fmaxf(dhi, d[k]);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    dlo = fminf(dlo, __shfl_xor_sync(kFullMask, dlo, o));
+    dhi = fmaxf(dhi, __shfl_xor_sync(kFullMask, dhi, o));
+  }
+  return (fabsf(dlo) < INFINITY) && (fabsf(dhi) < INFINITY);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// warp 0: planner
+// ---------------------------------------------------------------------------------------------------------
+__device__ void planner(const PsweepArgs& A, const __nv_bfloat16* key_split, ChunkDesc* descs, unsigned bars, int tw, int th, int tiles_x,
+                        int tiles, long long items) {
+  const int lane = threadIdx.x & 31;
+  const int P = A.h * A.w, C = A.C;
+  const unsigned bar_cready = bars + 8 * kBarCReady, bar_cfree = bars + 8 * kBarCFree;
+  unsigned seq = 0;
+  auto acquire = [&]() -> ChunkDesc* {
+    const unsigned slot = seq % kDescs;
+    if (seq >= kDescs) {
+      WS_T0();
+      mbar_wait(bar_cfree + 8 * slot, ((seq / kDescs) - 1) & 1);
+      if (lane == 0) WS_ADD(0);
+    }
+    return descs + slot;
+  };
+#ifdef RMVD_WS_STATS
+  const long long pl_t0 = clock64();
+#endif
+  auto publish = [&]() {
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar_cready + 8 * (seq % kDescs));
+    ++seq;
+  };
+  int prev_chunks = 1;
+  for (long long item = blockIdx.x; item < items; item += gridDim.x) {
+    const int tile = (int)(item % tiles), n = (int)((item / tiles) % A.N), v = (int)(item / ((long long)tiles * A.N));
+    const int hs = A.hs[v], ws = A.ws[v];
+    const int wg = (ws + 7) >> 3, G = hs * wg;
+    const int by = tile / tiles_x, bx = tile - by * tiles_x;
+    auto pixel_of_slot = [&](int slot) {
+      const int ty = slot / tw, tx = slot - ty * tw;
+      const int y = by * th + ty, x = bx * tw + tx;
+      return (ty < th && y < A.h && x < A.w) ? y * A.w + x : -1;
+    };
+    const int p0 = pixel_of_slot(lane), p1 = pixel_of_slot(lane + 32);
+    const Epi E = epi_from_calib(A.Kk + n * 9, A.Ks[v] + n * 9, A.T[v] + n * 16, A.h, A.w, hs, ws);
+    EpiPix cpix[4];                                   // the four corner pixels of this tile (clipped to the key map)
+    {
+      const int xa = bx * tw, xb = min(xa + tw, A.w) - 1, ya = by * th, yb = min(ya + th, A.h) - 1;
+      cpix[0] = epi_pixel(E, xa, ya); cpix[1] = epi_pixel(E, xb, ya);
+      cpix[2] = epi_pixel(E, xa, yb); cpix[3] = epi_pixel(E, xb, yb);
+    }
+    // magnitudes of the summands of u_h, v_h, k_h over the key map (rounding-error scale of the per-pixel terms)
+    const float mag_u = fabsf(E.a) * (float)A.w + fabsf(E.b) * (float)A.h + fabsf(E.c);
+    const float mag_v = fabsf(E.f) * (float)A.w + fabsf(E.g) * (float)A.h + fabsf(E.h);
+    const float mag_k = fabsf(E.j) * (float)A.w + fabsf(E.k) * (float)A.h + fabsf(E.l);
+    const float* invd = A.invd + (size_t)n * A.ist[0];
+    const long long stride = A.ist[1];
+    const int S_item = A.s_end - A.s_begin;
+    int s = A.s_begin, nchunks = 0;
+    int len_hint = (S_item + max(prev_chunks - 1, 1) - 1) / max(prev_chunks - 1, 1);   // one chunk fewer than the last tile needed
+    while (s < A.s_end) {
+      ChunkDesc* D = acquire();
+      D->pix[lane] = p0; D->pix[lane + 32] = p1;
+      __syncwarp();
+      const int rem = A.s_end - s, L0 = min(rem, kMaxPlanes);
+      int len = min(max(len_hint, 1), L0), R = -1, ymin = 0, H = 0;
+      bool direct = false;
+      for (;;) {
+        float dlo, dhi;
+        WS_T0();
+        const bool finite = plane_interval(invd, stride, s, len, dlo, dhi);
+        R = finite ? band_warp(D->rows, D->pix, E, A.w, dlo, dhi, hs, ws, ymin, H) : -1;
+        if (lane == 0) { WS_ADD(2); WS_CNT(1, 1); }
+        if (R >= 0 && R <= kRMax) break;
+        if (len <= 4) { direct = true; break; }
+        int k = (rem + len - 1) / len;               // balanced split of the remaining planes into more chunks
+        k = (R < 0) ? 2 * k : (k < 8 ? k + 1 : k + (k >> 2));
+        len = max(4, min(len - 1, (rem + k - 1) / k));
+      }
+      // per-plane terms of the coordinate chain, rounded like the reference, and the dead-plane bits: no pixel of the tile
+      // can have a valid sample on a dead plane (1/d <= 0, :499, or the plane's homography sends all four tile corners -- hence,
+      // with the denominator of one sign over the tile, the whole tile -- beyond the same edge of the source map by more than a
+      // pixel); the denominators must dominate the rounding errors of the per-pixel terms by a wide margin.
+#ifdef RMVD_WS_STATS
+      const long long pt_t0 = clock64();
+#endif
+#pragma unroll 1
+      for (int k8 = 0; k8 < kMaxPlanes / 32; ++k8) {
+        const int i = lane + 32 * k8;
+        if (32 * k8 >= len) break;
+        const float d = (i < len) ? invd[(size_t)(s + i) * stride] : 1.0f;
+        PlaneTerm pt;
+        pt.ed = fmul(E.e, d); pt.id = fmul(E.i, d); pt.md = fmul(E.m, d); pt.zs = fdiv(1.0f, d);
+        if (i < len) D->planes[i] = pt;
+        bool dead = !(pt.zs > 0.0f);
+        if (!dead) {
+          const float den_min = 9.5367431640625e-7f *    // 16 * 2^-24
+              (fmaxf(mag_u + fabsf(pt.ed), mag_v + fabsf(pt.id)) + ((float)max(ws, hs) + 5.0f) * (mag_k + fabsf(pt.md)));
+          int npos = 0, nneg = 0, xl = 0, xr = 0, yt = 0, yb = 0;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const float den = cpix[k].k_h + pt.md;
+            const float aden = fabsf(den);
+            const bool okd = (aden >= den_min) && (aden <= kDivHi);
+            const float r = rcp_refined(den);
+            const float ix = __fmaf_rn(cpix[k].u_h + pt.ed, r, -0.5f), iy = __fmaf_rn(cpix[k].v_h + pt.id, r, -0.5f);
+            npos += (okd && den > 0.f); nneg += (okd && den < 0.f);
+            xl += (ix < -3.0f); xr += (ix > (float)ws + 1.0f); yt += (iy < -3.0f); yb += (iy > (float)hs + 1.0f);
+          }
+          dead = (npos == 4 || nneg == 4) && (xl == 4 || xr == 4 || yt == 4 || yb == 4);
+        }
+        const unsigned bits = __ballot_sync(kFullMask, dead && i < len && A.dbg_ix0 == nullptr);
+        if (lane == 0) D->dead[k8] = bits;
+      }
+#ifdef RMVD_WS_STATS
+      if (lane == 0) { atomicAdd(&g_ws_stats[3], (unsigned long long)(clock64() - pt_t0)); WS_CNT(5, 1); WS_CNT(6, R > 0 ? R : 0); WS_CNT(7, len); }
+#endif
+      if (lane == 0) {
+        D->E = E;
+        D->key = key_split + (size_t)n * P * C * 2;
+        D->src = reinterpret_cast<const __nv_bfloat16*>(A.src[v]) + (size_t)n * (C >> 5) * G * 512;
+        D->out_base = (unsigned long long)(((size_t)(A.v0 + v) * A.N + n) * A.out_S) * (unsigned long long)P;
+        D->hs = hs; D->ws = ws; D->wg = wg; D->G = G;
+        D->n = n; D->v = v;
+        D->kind = direct ? kDirect : kGemm;
+        D->first = (s == A.s_begin) ? 1 : 0;
+        D->last = (s + len >= A.s_end) ? 1 : 0;
+        D->s0 = s; D->len = len; D->R = direct ? 0 : R; D->ymin = ymin; D->H = direct ? 0 : H;
+        D->out_plane0 = A.out_s0 + (s - A.s_begin);
+      }
+      publish();
+      s += len;
+      ++nchunks;
+      const int rem2 = A.s_end - s;
+      if (rem2 > 0) { const int k2 = (rem2 + len - 1) / len; len_hint = (rem2 + k2 - 1) / k2; }
+    }
+    prev_chunks = nchunks;
+  }
+#ifdef RMVD_WS_STATS
+  if (lane == 0) atomicAdd(&g_ws_stats[4], (unsigned long long)(clock64() - pl_t0));
+#endif
+  ChunkDesc* D = acquire();
+  if (lane == 0) D->kind = kStop;
+  publish();
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// warp 1: producer.  Lane l owns band rows l and l + 32 of the chunk; per stage it intersects them with the pass.
+// ---------------------------------------------------------------------------------------------------------
+__device__ void producer(const ChunkDesc* descs, unsigned bars, unsigned stage0, int C) {
+  const int lane = threadIdx.x & 31;
+  const int nkc = C / kKC;
+  const unsigned bar_cready = bars + 8 * kBarCReady, bar_cfree = bars + 8 * kBarCFree, bar_full = bars + 8 * kBarFull,
+                 bar_free = bars + 8 * kBarFree;
+  unsigned g = 0;
+  for (unsigned seq = 0;; ++seq) {
+    const unsigned slot = seq % kDescs;
+    {
+      WS_T0();
+      mbar_wait(bar_cready + 8 * slot, (seq / kDescs) & 1);
+      if (lane == 0) WS_ADD(8);
+    }
+    const ChunkDesc* D = descs + slot;
+    const int kind = D->kind;
+    if (kind == kStop) break;
+    const int R = D->R;
+    if (kind == kGemm && R > 0) {
+      const int H = D->H, ymin = D->ymin, wg = D->wg;
+      int cs[2], n8[2], gofs[2];
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int h = lane + 32 * j;
+        cs[j] = 0; n8[j] = 0; gofs[j] = 0;
+        if (h < H) {
+          const RowSpan r = D->rows[h];
+          cs[j] = r.offp + r.xa; n8[j] = r.len; gofs[j] = (ymin + h) * wg + (r.xa >> 3);
+        }
+      }
+      const unsigned char* src = reinterpret_cast<const unsigned char*>(D->src);
+      const size_t kcbytes = (size_t)D->G * 1024;
+      const int npass = (R + kNT - 1) / kNT;
+      for (int pass = 0; pass < npass; ++pass) {
+        const int lo = pass * kNT, hi = min(R, lo + kNT);
+        for (int kc = 0; kc < nkc; ++kc, ++g) {
+          const unsigned sl = g % kStages;
+          if (g >= kStages) {
+            WS_T0();
+            mbar_wait(bar_free + 8 * sl, ((g / kStages) - 1) & 1);   // the MMAs that read this slot are done
+            if (lane == 0) WS_ADD(9);
+          }
+          const unsigned full = bar_full + 8 * sl;
+          if (lane == 0) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(full), "r"((unsigned)(hi - lo) * 128u) : "memory");
+          const unsigned dst0 = stage0 + sl * kStageBytes;
+          const unsigned char* srck = src + (size_t)kc * kcbytes;
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            const int a = max(cs[j], lo), b = min(cs[j] + n8[j], hi);
+            if (a < b) bulk_g2s(dst0 + (unsigned)(a - lo) * 128u, srck + ((size_t)(gofs[j] + ((a - cs[j]) >> 3)) << 10), (unsigned)(b - a) * 128u, full);
+          }
+        }
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar_cfree + 8 * slot);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// warp 2: MMA issuer (one elected lane).  Every chunk has at least one pass on the accumulator ring (an empty one for
+// chunks without a band), so that this warp never falls behind the consumers.
+// ---------------------------------------------------------------------------------------------------------
+__device__ void mma_issuer(const ChunkDesc* descs, unsigned bars, unsigned stage0, unsigned tmem, int C) {
+  const int nkc = C / kKC;
+  const unsigned bar_cready = bars + 8 * kBarCReady, bar_full = bars + 8 * kBarFull, bar_free = bars + 8 * kBarFree,
+                 bar_acc = bars + 8 * kBarAcc, bar_drained = bars + 8 * kBarDrained, bar_aready = bars + 8 * kBarAReady;
+  const unsigned long long desc0 = umma_desc(stage0, 128, 1024);
+  const unsigned idesc0 = umma_idesc_bf16(2 * kPx, 0);
+  unsigned g = 0, ap = 0, tile_seq = 0;
+  for (unsigned seq = 0;; ++seq) {
+    const unsigned slot = seq % kDescs;
+    {
+      WS_T0();
+      mbar_wait(bar_cready + 8 * slot, (seq / kDescs) & 1);
+      WS_ADD(10);
+    }
+    const ChunkDesc* D = descs + slot;
+    const int kind = D->kind;
+    if (kind == kStop) break;
+    if (D->first) {                                   // the key tile of this item is in TMEM
+      WS_T0();
+      mbar_wait(bar_aready, tile_seq & 1);
+      WS_ADD(11);
+      ++tile_seq;
+      asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+    }
+    const int R = (kind == kGemm) ? D->R : 0;
+    const int npass = (R + kNT - 1) / kNT;
+    if (npass == 0) {
+      const unsigned buf = ap % kNBuf, use = ap / kNBuf;
+      if (use >= 1) mbar_wait(bar_drained + 8 * buf, (use - 1) & 1);
+      mbar_arrive(bar_acc + 8 * buf);
+      ++ap;
+      continue;
+    }
+    for (int pass = 0; pass < npass; ++pass, ++ap) {
+      const int ncol = min(R - pass * kNT, kNT);
+      const unsigned idesc = idesc0 | ((unsigned)(((ncol + 15) & ~15) >> 3) << 17);
+      const unsigned buf = ap % kNBuf, use = ap / kNBuf;
+      if (use >= 1) {
+        WS_T0();
+        mbar_wait(bar_drained + 8 * buf, (use - 1) & 1);   // this accumulator's previous contents have been read out
+        WS_ADD(12);
+      }
+      asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+      const unsigned dcol = tmem + buf * kNT;
+      for (int kc = 0; kc < nkc; ++kc, ++g) {
+        const unsigned sl = g % kStages;
+        {
+          WS_T0();
+          mbar_wait(bar_full + 8 * sl, (g / kStages) & 1);
+          WS_ADD(13);
+          WS_CNT(14, 1);
+        }
+        asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+        // descriptors differ only in their start-address field (units of 16 bytes): stage base, then 256 bytes per K = 16 step
+        // (two 16-byte chunks); the hi steps are chunks 0..3, the lo steps chunks 4..7 and re-use the A' slices of the hi steps
+        const unsigned long long d0 = desc0 + (unsigned long long)(sl * (kStageBytes >> 4));
+        const unsigned a_addr = tmem + kTmemA + kc * (kKC / 2);
+        tc_mma(dcol, a_addr, d0, idesc, kc > 0 ? 1u : 0u);
+        tc_mma(dcol, a_addr + 8, d0 + 16, idesc, 1u);
+        tc_mma(dcol, a_addr, d0 + 32, idesc, 1u);
+        tc_mma(dcol, a_addr + 8, d0 + 48, idesc, 1u);
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(bar_free + 8 * sl) : "memory");
+      }
+      asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(bar_acc + 8 * buf) : "memory");
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// consumers
+// ---------------------------------------------------------------------------------------------------------
+// Key tile -> TMEM: TMEM lane 32 q + l = key_hi of tile slot 16 q + l (l < 16) or key_lo of slot 16 q + l - 16 (l >= 16); its
+// channels packed two bf16 per 32-bit column (8 columns per K = 16 step).  The three consumer warps of a quadrant take every
+// third K step.
+constexpr int kKeyIt = (kMaxC / 16 + 2) / 3;
+__device__ __forceinline__ void load_key(const ChunkDesc* D, unsigned tmem, int C, int q, int third, int lane) {
+  const int px = D->pix[16 * q + (lane & 15)];
+  const uint4* src = reinterpret_cast<const uint4*>(D->key + (size_t)max(px, 0) * (C >> 5) * 64 + ((lane < 16) ? 0 : 32));
+  const int nks = C / 16;                              // empty slots read pixel 0 (their G rows are never sampled)
+  uint4 v0[kKeyIt], v1[kKeyIt];
+#pragma unroll
+  for (int i = 0; i < kKeyIt; ++i) {
+    const int ks = third + 3 * i;
+    const int u = (ks >> 1) * 8 + (ks & 1) * 2;        // uint4 index: 128-byte line ks / 2, 16 channels (32 B) at (ks & 1) * 32 B
+    if (ks < nks) { v0[i] = __ldg(src + u); v1[i] = __ldg(src + u + 1); }
+  }
+#pragma unroll
+  for (int i = 0; i < kKeyIt; ++i) {
+    const int ks = third + 3 * i;
+    if (ks < nks) {
+      const unsigned addr = tmem + ((unsigned)(q * 32) << 16) + kTmemA + ks * 8;
+      asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};\n" ::"r"(addr), "r"(v0[i].x),
+                   "r"(v0[i].y), "r"(v0[i].z), "r"(v0[i].w), "r"(v1[i].x), "r"(v1[i].y), "r"(v1[i].z), "r"(v1[i].w)
+                   : "memory");
+    }
+  }
+  asm volatile("tcgen05.wait::st.sync.aligned;\n" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
+}
+
+// dot product of one key pixel with one source texel from the split copies (slow paths only)
+__device__ float dot_thread(const ChunkDesc* D, int C, int p, int y, int x) {
+  float acc = 0.f;
+  for (int c = 0; c < C; ++c) acc = fmaf(key_at(D->key, p, c, C), src_at(D, y, x, c), acc);
+  return acc;
+}
+
+// One sample through the exact chain, evaluated and stored (about one sample in 10^3 of the filtered locate below).
+__device__ __noinline__ void sample_slow(const ChunkDesc* D, int p, int pl, int slot) {
+  const WsConst& K = s_k;
+  const int hs = D->hs, ws = D->ws, R = D->R, C = K.C;
+  const int ymin = D->ymin, H = D->H, Hm1 = max(H - 1, 0), Rm1 = max(R - 1, 0);
+  const float* g = K.G + slot * kGPitch;
+  const Pixel px = pixel_consts(D->E, p, K.w);
+  Sample L;
+  locate(px, D->planes[pl], hs, ws, L);
+  float val = 0.f;
+  if (L.valid) {
+    // Corners outside the map carry weight exactly 0, so they are read from a clamped (finite) column instead of being
+    // branched around; a corner WITH weight outside the predicted spans is a miss and is evaluated directly.
+    const int h0 = L.y0 - ymin;
+    const bool rowA = (unsigned)h0 < (unsigned)H, rowB = (unsigned)(h0 + 1) < (unsigned)H;
+    const RowSpan rA = D->rows[min(max(h0, 0), Hm1)], rB = D->rows[min(max(h0 + 1, 0), Hm1)];
+    const int xl = L.x0, xr = L.x0 + 1;
+    auto in_span = [](const RowSpan& r, int x) { return (unsigned)(x - r.xa) < (unsigned)r.len; };
+    const bool inA_l = rowA && in_span(rA, xl), inA_r = rowA && in_span(rA, xr);
+    const bool inB_l = rowB && in_span(rB, xl), inB_r = rowB && in_span(rB, xr);
+    const bool miss = (R == 0) || (L.nw != 0.f && !inA_l) || (L.ne != 0.f && !inA_r) || (L.sw != 0.f && !inB_l) || (L.se != 0.f && !inB_r);
+    float g_nw = 0.f, g_ne = 0.f, g_sw = 0.f, g_se = 0.f;
+    if (!miss) {
+      const int cA = rA.offp + xl, cB = rB.offp + xl;
+      g_nw = g[min(max(cA, 0), Rm1)]; g_ne = g[min(max(cA + 1, 0), Rm1)];
+      g_sw = g[min(max(cB, 0), Rm1)]; g_se = g[min(max(cB + 1, 0), Rm1)];
+    } else {
+      const int x0c = clampi(L.x0, 0, ws - 1), x1c = clampi(L.x0 + 1, 0, ws - 1);
+      const int y0c = clampi(L.y0, 0, hs - 1), y1c = clampi(L.y0 + 1, 0, hs - 1);
+      g_nw = (L.nw != 0.f) ? dot_thread(D, C, p, y0c, x0c) : 0.f;
+      g_ne = (L.ne != 0.f) ? dot_thread(D, C, p, y0c, x1c) : 0.f;
+      g_sw = (L.sw != 0.f) ? dot_thread(D, C, p, y1c, x0c) : 0.f;
+      g_se = (L.se != 0.f) ? dot_thread(D, C, p, y1c, x1c) : 0.f;
+    }
+    val = (g_nw * L.nw + g_ne * L.ne + g_sw * L.sw + g_se * L.se) * K.inv_scale;
+  }
+  const size_t o = (size_t)D->out_base + (size_t)(D->out_plane0 + pl) * K.P + p;
+  K.corr[o] = val;
+  K.mask[o] = L.valid ? 1.f : 0.f;
+  if (K.dbg_ix0) {
+    K.dbg_ix0[o] = L.x0;
+    K.dbg_iy0[o] = L.y0;
+    if (K.dbg_geom) K.dbg_geom[o] = L.geom ? 1 : 0;
+  }
+}
+
+// Filtered locate (see psweep_tc.cu for the error analysis): only the INTEGER corner and the 0/1 mask have to be the
+// reference's bit for bit.  ix' = fma(nu, rcp(den), -0.5) is within u (3 ws + 6.5) of U - 0.5 and the reference's chain within
+// u (5.5 ws + 10.5) (u = 2^-24): whenever ix' is further than eps = u (16 ws + 64) from an integer, floor(ix') IS the
+// reference's floor.  Interior samples are valid iff the geometric mask holds; samples with a corner column / row outside
+// the map need the in-range weight below 0.9999 by more than eps (mask 0); everything else takes sample_slow().
+struct FastConst {
+  float u_h, v_h, k_h;
+  float sg, zp;           // visibility in the source as one compare: zs * sg > zp (planesweep_corr.py:500-504)
+  float eps_x, eps_y;     // trust margin of an interior floor
+  float epb_x, epb_y;     // trust margin where a corner column / row is outside the map (covers the 0.9999 threshold)
+  int ymin, Hm1;
+  unsigned wsm1, hsm1;
+};
+struct FastOut { float val; int xi, yi; bool valid, geom, settled; };
+
+__device__ __forceinline__ FastOut sample_fast(const RowSpan* __restrict__ rows, const FastConst& K, const float* __restrict__ g,
+                                               const PlaneTerm pt, float inv_scale) {
+  FastOut o;
+  const float den = fadd(K.k_h, pt.md), nu = fadd(K.u_h, pt.ed), nv = fadd(K.v_h, pt.id);      // :334, :343
+  o.geom = (pt.zs > 0.0f) && (pt.zs * K.sg > K.zp);                                             // :499-506
+  const bool den_ok = fabsf(den) <= kDivHi;
+  const float r = rcp_refined(den);
+  const float ix = __fmaf_rn(nu, r, -0.5f), iy = __fmaf_rn(nv, r, -0.5f);
+  const float fx = ix - floorf(ix), fy = iy - floorf(iy);        // exact
+  o.xi = __float2int_rd(ix); o.yi = __float2int_rd(iy);          // saturating; nan -> 0
+  const bool int_x = (unsigned)o.xi < K.wsm1, int_y = (unsigned)o.yi < K.hsm1;
+  const bool trust_x = fminf(fx, 1.0f - fx) > (int_x ? K.eps_x : K.epb_x);   // false for nan
+  const bool trust_y = fminf(fy, 1.0f - fy) > (int_y ? K.eps_y : K.epb_y);
+  o.valid = o.geom && int_x && int_y;
+  const int h0 = o.yi - K.ymin;
+  const bool rows_ok = (unsigned)h0 < (unsigned)K.Hm1;
+  const int hc = rows_ok ? h0 : 0;
+  const RowSpan rA = rows[hc], rB = rows[hc + 1];
+  const bool in_band = rows_ok & ((unsigned)(o.xi - rA.xa) < (unsigned)rA.lenm1) & ((unsigned)(o.xi - rB.xa) < (unsigned)rB.lenm1);
+  const bool use = o.valid && in_band;
+  const float* ga = g + (use ? rA.offp + o.xi : 0);              // unused samples read columns 0, 1 (discarded)
+  const float* gb = g + (use ? rB.offp + o.xi : 0);
+  const float a0 = ga[0], a1 = ga[1], b0 = gb[0], b1 = gb[1];
+  const float top = fmaf(fx, a1 - a0, a0), bot = fmaf(fx, b1 - b0, b0);
+  o.val = use ? fmaf(fy, bot - top, top) * inv_scale : 0.f;
+  o.settled = den_ok && trust_x && trust_y && (in_band || !o.valid);
+  return o;
+}
+
+// warp = 32 adjacent tile slots x one plane per step (one 128-byte row of corr and of mask), two planes in flight per thread
+__device__ __forceinline__ void sample_chunk(const ChunkDesc* D, const float* G, const Pixel& px, int p, int cw, int lane) {
+  if (p < 0) return;
+  const WsConst& W = s_k;
+  const int hs = D->hs, ws = D->ws, len = D->len;
+  const float inv_scale = W.inv_scale;
+  constexpr float kU = 5.9604645e-8f;   // 2^-24
+  FastConst K;
+  K.u_h = px.u_h; K.v_h = px.v_h; K.k_h = px.k_h;
+  K.sg = (px.mode == 2) ? -1.0f : 1.0f;
+  K.zp = (px.mode == 1) ? px.z_pole : (px.mode == 2) ? -px.z_pole : (px.mode == 3) ? -INFINITY : INFINITY;
+  K.eps_x = kU * (16.0f * (float)ws + 64.0f); K.eps_y = kU * (16.0f * (float)hs + 64.0f);
+  K.epb_x = K.eps_x + 1.2e-4f; K.epb_y = K.eps_y + 1.2e-4f;
+  K.ymin = D->ymin; K.Hm1 = max(D->H - 1, 0);
+  K.wsm1 = (unsigned)(ws - 1); K.hsm1 = (unsigned)(hs - 1);
+  const int slot = (cw & 1) * 32 + lane;
+  const float* g = G + slot * kGPitch;
+  const RowSpan* rows = D->rows;
+  const PlaneTerm* planes = D->planes;
+  float* const corr = W.corr; float* const mask = W.mask;
+  int32_t* const dix = W.dbg_ix0;
+  const size_t step = (size_t)kStep * W.P;
+  size_t o = (size_t)D->out_base + (size_t)(D->out_plane0 + (cw >> 1)) * W.P + p;
+  auto emit = [&](size_t oo, int pl, const FastOut& r) {
+    if (r.settled) {
+      __stcs(corr + oo, r.val);
+      __stcs(mask + oo, r.valid ? 1.f : 0.f);
+      if (dix) {
+        dix[oo] = min(max(r.xi, -2), ws);   // sat_index()
+        W.dbg_iy0[oo] = min(max(r.yi, -2), hs);
+        if (W.dbg_geom) W.dbg_geom[oo] = r.geom ? 1 : 0;
+      }
+    } else {
+      sample_slow(D, p, pl, slot);
+    }
+  };
+  const unsigned* dead = D->dead;
+  auto is_dead = [&](int q) { return (dead[q >> 5] >> (q & 31)) & 1u; };
+  int pl = cw >> 1;
+  constexpr int kSU = 2;                                 // samples in flight per thread
+  for (; pl + (kSU - 1) * kStep < len; pl += kSU * kStep, o += kSU * step) {
+    bool all_dead = true;
+#pragma unroll
+    for (int j = 0; j < kSU; ++j) all_dead = all_dead && is_dead(pl + j * kStep);
+    if (all_dead) {                                      // warp-uniform
+#pragma unroll
+      for (int j = 0; j < kSU; ++j) { __stcs(corr + o + j * step, 0.f); __stcs(mask + o + j * step, 0.f); }
+      continue;
+    }
+    FastOut r[kSU];
+#pragma unroll
+    for (int j = 0; j < kSU; ++j) r[j] = sample_fast(rows, K, g, planes[pl + j * kStep], inv_scale);
+#pragma unroll
+    for (int j = 0; j < kSU; ++j) emit(o + j * step, pl + j * kStep, r[j]);
+  }
+  for (; pl < len; pl += kStep, o += step) emit(o, pl, sample_fast(rows, K, g, planes[pl], inv_scale));
+}
+
+// Irregular chunk: every sample located with the reference chain of common.cuh and evaluated directly, the warp sharing each
+// valid sample's channel reduction.
+__device__ void direct_chunk(const PsweepArgs& A, const ChunkDesc* D, int cw, int lane) {
+  const WsConst& W = s_k;
+  const int C = W.C, P = W.P, hs = D->hs, ws = D->ws, len = D->len, n = D->n;
+  const int slot0 = (cw & 1) * 32;
+  const int p = D->pix[slot0 + lane];
+  for (int pl = cw >> 1; pl < len; pl += kStep) {
+    const int s = D->s0 + pl;
+    bool valid = false, geom = false;
+    float wnw = 0.f, wne = 0.f, wsw = 0.f, wse = 0.f;
+    int x0 = 0, y0 = 0, x0c = 0, x1c = 0, y0c = 0, y1c = 0;
+    if (p >= 0) {
+      const int yi = p / A.w, xi = p - yi * A.w;
+      const EpiPix ep = epi_pixel(D->E, xi, yi);
+      const float d = A.invd[n * A.ist[0] + s * A.ist[1] + yi * A.ist[2] + xi * A.ist[3]];
+      float us, vs;
+      epi_sample(D->E, ep, d, us, vs, geom);
+      const Bilinear b = bilinear_setup(pix_to_unnorm(us, ws), pix_to_unnorm(vs, hs), hs, ws);
+      valid = sampling_mask(b.msum) && geom;
+      wnw = b.nw; wne = b.ne; wsw = b.sw; wse = b.se;
+      x0 = sat_index(b.x0f, ws); y0 = sat_index(b.y0f, hs);
+      x0c = clampi(x0, 0, ws - 1); x1c = clampi(x0 + 1, 0, ws - 1);
+      y0c = clampi(y0, 0, hs - 1); y1c = clampi(y0 + 1, 0, hs - 1);
+    }
+    unsigned vm = __ballot_sync(kFullMask, valid);
+    float res = 0.f;
+    while (vm) {
+      const int j = __ffs(vm) - 1;
+      vm &= vm - 1;
+      const int qx0 = __shfl_sync(kFullMask, x0c, j), qx1 = __shfl_sync(kFullMask, x1c, j);
+      const int qy0 = __shfl_sync(kFullMask, y0c, j), qy1 = __shfl_sync(kFullMask, y1c, j);
+      const float nw = __shfl_sync(kFullMask, wnw, j), ne = __shfl_sync(kFullMask, wne, j);
+      const float sw = __shfl_sync(kFullMask, wsw, j), se = __shfl_sync(kFullMask, wse, j);
+      const int pj = D->pix[slot0 + j];
+      float a = 0.f;
+      for (int c = lane; c < C; c += 32) {
+        const float k = key_at(D->key, pj, c, C);
+        a = fmaf(k, src_at(D, qy0, qx0, c) * nw + src_at(D, qy0, qx1, c) * ne + src_at(D, qy1, qx0, c) * sw + src_at(D, qy1, qx1, c) * se, a);
+      }
+      a = warp_sum(a);
+      if (lane == j) res = a;
+    }
+    if (p >= 0) {
+      const size_t o = (size_t)D->out_base + (size_t)(D->out_plane0 + pl) * P + p;
+      W.corr[o] = valid ? res * W.inv_scale : 0.f;
+      W.mask[o] = valid ? 1.f : 0.f;
+      if (W.dbg_ix0) {
+        W.dbg_ix0[o] = x0;
+        W.dbg_iy0[o] = y0;
+        if (W.dbg_geom) W.dbg_geom[o] = geom ? 1 : 0;
+      }
+    }
+  }
+}
+
+__device__ void consumer(const PsweepArgs& A, ChunkDesc* descs, float* G, unsigned bars, unsigned tmem) {
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int cw = warp - 4, q = warp & 3, third = (warp >> 2) - 1;
+  const int C = A.C;
+  const unsigned bar_cready = bars + 8 * kBarCReady, bar_cfree = bars + 8 * kBarCFree, bar_acc = bars + 8 * kBarAcc,
+                 bar_drained = bars + 8 * kBarDrained, bar_aready = bars + 8 * kBarAReady;
+  // key tile of the first item
+  mbar_wait(bar_cready, 0);
+  if (descs[0].kind != kStop) {
+    load_key(descs, tmem, C, q, third, lane);
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar_aready);
+  }
+  Pixel px{};
+  int p = -1;
+  unsigned ap = 0;
+  const int slot_px = 16 * q + (lane & 15);           // G row this lane drains
+  const bool lower = lane < 16;
+#ifdef RMVD_WS_STATS
+  const bool rec = (t == 128);
+  const long long cs_t0 = clock64();
+#endif
+  for (unsigned seq = 0;; ++seq) {
+    const unsigned slot = seq % kDescs;
+    {
+      WS_T0();
+      mbar_wait(bar_cready + 8 * slot, (seq / kDescs) & 1);
+#ifdef RMVD_WS_STATS
+      if (rec) WS_ADD(16);
+#endif
+    }
+    const ChunkDesc* D = descs + slot;
+    const int kind = D->kind;
+    if (kind == kStop) break;
+    if (D->first) {
+      p = D->pix[(cw & 1) * 32 + lane];
+      px = pixel_consts(D->E, max(p, 0), A.w);
+#ifdef RMVD_WS_STATS
+      if (rec) WS_CNT(24, 1);
+#endif
+    }
+    const int R = (kind == kGemm) ? D->R : 0;
+    const int npass = (R + kNT - 1) / kNT;
+    {
+      WS_T0();
+      cons_bar();                                      // every warp has finished sampling the previous chunk: G may be overwritten
+#ifdef RMVD_WS_STATS
+      if (rec) WS_ADD(17);
+#endif
+    }
+#ifdef RMVD_WS_STATS
+    const long long dr_t0 = clock64();
+    long long acc_wait = 0;
+#endif
+    for (int pass = 0; pass < max(npass, 1); ++pass, ++ap) {
+      const unsigned buf = ap % kNBuf;
+#ifdef RMVD_WS_STATS
+      const long long aw0 = clock64();
+#endif
+      mbar_wait(bar_acc + 8 * buf, (ap / kNBuf) & 1);
+#ifdef RMVD_WS_STATS
+      acc_wait += clock64() - aw0;
+#endif
+      asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+      if (pass < npass) {
+#pragma unroll 1
+        for (int hb = 0; hb < kNT / 32; ++hb) {
+          const int b = pass * (kNT / 32) + hb, col0 = b * 32;
+          if (col0 < R && (b % 3) == third) {
+            // Lane l < 16 holds the key_hi row of its pixel, lane l + 16 the key_lo row of the same pixel.  One exchange serves
+            // two columns: the lower lane finishes column 2i, the upper lane column 2i + 1; both halves of the warp store.
+            float a[32];
+            tmem_ld32(tmem + buf * kNT + hb * 32 + ((unsigned)(q * 32) << 16), a);
+            float* gcol = G + slot_px * kGPitch + col0 + (lower ? 0 : 1);
+            const int left = R - col0 - (lower ? 0 : 1);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const float own = lower ? a[2 * i] : a[2 * i + 1];
+              const float v = own + __shfl_xor_sync(kFullMask, lower ? a[2 * i + 1] : a[2 * i], 16);
+              if (2 * i < left) gcol[2 * i] = v;
+            }
+          }
+        }
+      }
+      asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_drained + 8 * buf);
+    }
+#ifdef RMVD_WS_STATS
+    if (rec) { atomicAdd(&g_ws_stats[18], (unsigned long long)acc_wait); atomicAdd(&g_ws_stats[19], (unsigned long long)(clock64() - dr_t0 - acc_wait)); }
+    const long long kl_t0 = clock64();
+#endif
+    if (D->last) {
+      // every MMA of this item has completed (its passes were drained above): the key tile of the next item may replace it
+      const unsigned nslot = (seq + 1) % kDescs;
+      mbar_wait(bar_cready + 8 * nslot, ((seq + 1) / kDescs) & 1);
+      const ChunkDesc* Dn = descs + nslot;
+      if (Dn->kind != kStop) {
+        load_key(Dn, tmem, C, q, third, lane);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_aready);
+      }
+    }
+#ifdef RMVD_WS_STATS
+    if (rec) atomicAdd(&g_ws_stats[20], (unsigned long long)(clock64() - kl_t0));
+    const long long b2_t0 = clock64();
+#endif
+    cons_bar();                                        // G is complete
+#ifdef RMVD_WS_STATS
+    if (rec) atomicAdd(&g_ws_stats[21], (unsigned long long)(clock64() - b2_t0));
+    const long long sm_t0 = clock64();
+#endif
+    if (kind == kGemm) sample_chunk(D, G, px, p, cw, lane);
+    else direct_chunk(A, D, cw, lane);
+    __syncwarp();
+#ifdef RMVD_WS_STATS
+    if (rec) atomicAdd(&g_ws_stats[22], (unsigned long long)(clock64() - sm_t0));
+#endif
+    if (lane == 0) mbar_arrive(bar_cfree + 8 * slot);
+  }
+#ifdef RMVD_WS_STATS
+  if (rec) atomicAdd(&g_ws_stats[23], (unsigned long long)(clock64() - cs_t0));
+#endif
+}
+
+__global__ void __launch_bounds__(kThreads, 1) psweep_ws_kernel(const PsweepArgs A, const __nv_bfloat16* __restrict__ key_split, int tw,
+                                                                int th, int tiles_x, int tiles, long long items) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ unsigned s_tmem;
+  unsigned char* stage = smem_raw + ((1024 - (smem_u32(smem_raw) & 1023)) & 1023);
+  float* G = reinterpret_cast<float*>(stage + kStages * kStageBytes);
+  ChunkDesc* descs = reinterpret_cast<ChunkDesc*>(G + kPx * kGPitch);
+  unsigned long long* bar_mem = reinterpret_cast<unsigned long long*>(descs + kDescs);
+  const unsigned bars = smem_u32(bar_mem);
+  const int t = threadIdx.x, warp = t >> 5;
+
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(&s_tmem)), "r"(kTmemCols));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n");
+  }
+  if (t == 32) {
+    for (int b = 0; b < kNumBars; ++b) {
+      const int count = (b >= kBarDrained && b < kBarCReady) ? kConsWarps            // drained: every consumer warp
+                        : (b >= kBarCFree && b < kBarAReady) ? kConsWarps + 1         // descriptor free: consumers + producer
+                        : (b == kBarAReady) ? kConsWarps : 1;
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(bars + 8 * b), "r"(count));
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;\n");
+    s_k.corr = A.corr; s_k.mask = A.mask; s_k.dbg_ix0 = A.dbg_ix0; s_k.dbg_iy0 = A.dbg_iy0; s_k.dbg_geom = A.dbg_geom;
+    s_k.G = G; s_k.P = A.h * A.w; s_k.C = A.C; s_k.w = A.w;
+    s_k.inv_scale = (A.norm == RMVD_NORM_DIM) ? 1.0f / sqrtf((float)A.C) : 1.0f;    // corr / sqrt(C), :178-179
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+  const unsigned tmem = s_tmem;
+
+  if (warp == 0) {
+    planner(A, key_split, descs, bars, tw, th, tiles_x, tiles, items);
+  } else if (warp == 1) {
+    producer(descs, bars, smem_u32(stage), A.C);
+  } else if (warp == 2) {
+    if (elect_one()) mma_issuer(descs, bars, smem_u32(stage), tmem, A.C);
+  } else if (warp >= 4) {
+    consumer(A, descs, G, bars, tmem);
+  }
+
+  asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem), "r"(kTmemCols));
+}
+
+static size_t smem_bytes() {
+  return 1024 + (size_t)kStages * kStageBytes + sizeof(float) * kPx * kGPitch + sizeof(ChunkDesc) * kDescs + 8 * kNumBars;
+}
+
+}  // namespace ws
+
+size_t psweep_ws_src_bytes(int N, int C, int hs, int ws) {
+  return (size_t)N * C * hs * ((ws + 7) & ~7) * sizeof(float);
+}
+
+bool psweep_ws_eligible(const PsweepArgs& A, int nviews) {
+  if (A.C % 32 != 0 || A.C > ws::kMaxC || A.ist[2] != 0 || A.ist[3] != 0) return false;
+  for (int v = 0; v < nviews; ++v)
+    if (A.hs[v] >= 32768 || A.ws[v] >= 32768) return false;
+  return true;
+}
+
+int repack_grouped_batch(const float* const* srcs, void* const* dsts, const int* hs, const int* wss, int count, int N, int C, int l2norm,
+                         cudaStream_t st) {
+  if (count < 1 || count > kMaxViews || (long long)N * count > 65535) return (int)cudaErrorInvalidValue;
+  ws::GroupBatch B;
+  int gmax = 0;
+  for (int i = 0; i < kMaxViews; ++i) {
+    const int j = i < count ? i : 0;
+    B.src[i] = srcs[j]; B.dst[i] = reinterpret_cast<__nv_bfloat16*>(dsts[j]); B.hs[i] = hs[j]; B.ws[i] = wss[j];
+    if (i < count) {
+      const int wg = (wss[i] + 7) >> 3, tiles = ((wg + 3) >> 2) * hs[i];
+      if (tiles > gmax) gmax = tiles;
+    }
+  }
+  if (l2norm) {
+    dim3 grid(gmax, 1, N * count);
+    ws::nchw_to_grouped_kernel<true><<<grid, 256, 0, st>>>(B, C, N);
+  } else {
+    dim3 grid(gmax, (C + ws::kRpCh - 1) / ws::kRpCh, N * count);
+    ws::nchw_to_grouped_kernel<false><<<grid, 256, 0, st>>>(B, C, N);
+  }
+  return (int)cudaGetLastError();
+}
+
+int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, cudaStream_t st) {
+  static int num_sms = 0;
+  static bool attr_set = false;
+  if (!attr_set) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(ws::psweep_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws::smem_bytes());
+    if (e != cudaSuccess) return (int)e;
+    attr_set = true;
+  }
+  // Tile rectangle (tw x th <= 64 key pixels): fewest tiles wins, taller tiles weighted by the growth of their bands (one more
+  // source row per tile row).  Widths are rounded up to multiples of 8 pixels where that fits.
+  int tw = A.w, th = 1;
+  {
+    double best = 1e30;
+    for (int h = 1; h <= ws::kPx && h <= A.h; ++h) {
+      const int wmax = ws::kPx / h;
+      const int nseg = (A.w + wmax - 1) / wmax;
+      int wt = (A.w + nseg - 1) / nseg;
+      if (((wt + 7) & ~7) <= wmax) wt = (wt + 7) & ~7;
+      wt = wt < A.w ? wt : A.w;
+      const double f = h <= 3 ? 1.0 + 0.05 * (h - 1) : (h <= 8 ? 1.2 + 0.175 * (h - 4) : 1.9 + 0.25 * (h - 8));
+      const double cost = f * ((A.w + wt - 1) / wt) * ((A.h + h - 1) / h);
+      if (cost < best - 1e-9) { best = cost; tw = wt; th = h; }
+    }
+  }
+  const int tiles_x = (A.w + tw - 1) / tw, tiles_y = (A.h + th - 1) / th;
+  const int tiles = tiles_x * tiles_y;
+  const long long items = (long long)tiles * A.N * nviews;
+  const unsigned grid = (unsigned)(items < (long long)num_sms ? items : (long long)num_sms);
+#ifdef RMVD_WS_STATS
+  {
+    unsigned long long z[32] = {0};
+    cudaMemcpyToSymbolAsync(ws::g_ws_stats, z, sizeof(z), 0, cudaMemcpyHostToDevice, st);
+  }
+#endif
+  ws::psweep_ws_kernel<<<grid, ws::kThreads, ws::smem_bytes(), st>>>(A, reinterpret_cast<const __nv_bfloat16*>(key_split), tw, th, tiles_x, tiles,
+                                                                     items);
+#ifdef RMVD_WS_STATS
+  {
+    unsigned long long h[32];
+    cudaStreamSynchronize(st);
+    cudaMemcpyFromSymbol(h, ws::g_ws_stats, sizeof(h));
+    const double c = (double)grid, ch = (double)(h[5] ? h[5] : 1);
+    fprintf(stderr, "[psweep_ws] ctas=%u items=%lld chunks=%llu (%.2f per item) mean_R=%.1f mean_len=%.1f band evals per chunk %.2f\n", grid, items, h[5],
+            (double)h[5] / (double)items, (double)h[6] / ch, (double)h[7] / ch, (double)h[1] / ch);
+    fprintf(stderr, "[psweep_ws] per CTA kcycles: planner total %.0f (wait cfree %.0f, band %.0f, plane terms %.0f) | producer wait cready %.0f free %.0f | "
+                    "mma wait cready %.0f aready %.0f drained %.0f full %.0f (stages %.0f)\n",
+            h[4] / c / 1e3, h[0] / c / 1e3, h[2] / c / 1e3, h[3] / c / 1e3, h[8] / c / 1e3, h[9] / c / 1e3, h[10] / c / 1e3, h[11] / c / 1e3, h[12] / c / 1e3,
+            h[13] / c / 1e3, h[14] / c);
+    fprintf(stderr, "[psweep_ws] consumer (warp 4) per CTA kcycles: total %.0f = wait cready %.0f + bar1 %.0f + wait acc %.0f + drain %.0f + key %.0f + bar2 %.0f + "
+                    "sample %.0f ; tiles %.1f\n",
+            h[23] / c / 1e3, h[16] / c / 1e3, h[17] / c / 1e3, h[18] / c / 1e3, h[19] / c / 1e3, h[20] / c / 1e3, h[21] / c / 1e3, h[22] / c / 1e3, h[24] / c);
+  }
+#endif
+  return (int)cudaGetLastError();
+}
+
+}  // namespace rmvd
