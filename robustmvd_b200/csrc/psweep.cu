@@ -361,9 +361,9 @@ static int repack(const float* src, float* dst, int N, int C, int P, int l2norm,
 using namespace rmvd;
 
 extern "C" size_t rmvd_psweep_workspace_bytes(int N, int C, int h, int w, int V, const int* hs, const int* ws) {
-  size_t tot = (((size_t)N * C * h * w * sizeof(float)) + 255) / 256 * 256;  // channels-last key copy
+  size_t tot = (psweep_ws_key_bytes(N, C, h, w) + 255) / 256 * 256;          // key copy (whole tiles of 64 pixels)
   for (int v = 0; v < V; ++v) tot += (psweep_ws_src_bytes(N, C, hs[v], ws[v]) + 255) / 256 * 256;   // rows padded to 8 texels
-  return tot;
+  return tot + 256;                                                                                  // work-item counter
 }
 
 extern "C" int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* feat_src, const float* intrinsics_key,
@@ -408,11 +408,12 @@ extern "C" int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* f
   }
 
   char* wsp = (char*)workspace;
+  unsigned* counter = (unsigned*)(wsp + rmvd_psweep_workspace_bytes(N, C, h, w, V, hs, ws) - 256);
   float* key_nhwc = (float*)wsp;
-  wsp += (((size_t)N * C * h * w * sizeof(float)) + 255) / 256 * 256;
+  wsp += (psweep_ws_key_bytes(N, C, h, w) + 255) / 256 * 256;
   const int l2 = normalize_mode == RMVD_NORM_BEFORE;
   if (wsk) {
-    int rc = repack_split(feat_key, key_nhwc, N, C, h * w, l2, st);
+    int rc = repack_key_tiles(feat_key, key_nhwc, N, C, h, w, l2, st);
     if (rc) return rc;
   } else if (tc) {
     // repacked together with the first group of source maps below (one launch)
@@ -451,7 +452,7 @@ extern "C" int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* f
       A.ws[j] = ws[v];
     }
     if (wsk) {
-      int rc = repack_grouped_batch(rp_src, rp_dst, hs + v0, ws + v0, rp_n, N, C, l2, st);
+      int rc = repack_grouped_batch(rp_src, rp_dst, hs + v0, ws + v0, rp_n, N, C, l2, counter, st);
       if (rc) return rc;
     } else if (tc) {
       int rc = repack_split_batch(rp_src, rp_dst, rp_P, rp_n, N, C, l2, st);
@@ -460,7 +461,7 @@ extern "C" int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* f
     A.N = N; A.C = C; A.h = h; A.w = w; A.S = S; A.s_begin = s_begin; A.s_end = s_end;
     A.norm = normalize_mode; A.out_S = out_S; A.out_s0 = out_s0; A.v0 = v0;
     A.corr = corr; A.mask = mask; A.dbg_ix0 = dbg_ix0; A.dbg_iy0 = dbg_iy0; A.dbg_geom = dbg_geom;
-    int rc = wsk ? launch_psweep_ws(A, key_nhwc, nv, st)
+    int rc = wsk ? launch_psweep_ws(A, key_nhwc, nv, counter, st)
                 : tc ? launch_psweep_tc(A, key_nhwc, nv, st)
                 : band ? launch_psweep_band(A, key_nhwc, nv, st) : dispatch_corr<false>(A, nv, st);
     if (rc) return rc;

@@ -42,12 +42,16 @@ int repack_split_batch(const float* const* srcs, void* const* dsts, const int* P
                        cudaStream_t st);
 int launch_psweep_tc(const PsweepArgs& A, const void* key_split, int nviews, cudaStream_t st);
 
-// psweep_ws.cu: persistent warp-specialised tcgen05 kernel (one CTA per SM).  The key map uses repack_split()'s layout, the
-// source maps the grouped split layout of repack_grouped_batch() (rows padded to multiples of 8 texels: psweep_ws_src_bytes).
+// psweep_ws.cu: persistent warp-specialised tcgen05 kernel (one CTA per SM).  The key map is repacked tile by tile
+// (repack_key_tiles: psweep_ws_key_bytes), the source maps into the grouped split layout of repack_grouped_batch() (rows
+// padded to multiples of 8 texels: psweep_ws_src_bytes).
 bool psweep_ws_eligible(const PsweepArgs& A, int nviews);
 size_t psweep_ws_src_bytes(int N, int C, int hs, int ws);
+size_t psweep_ws_key_bytes(int N, int C, int h, int w);
+int repack_key_tiles(const float* key, void* dst, int N, int C, int h, int w, int l2norm, cudaStream_t st);
+// `counter`: 4 bytes of device memory (the kernel's work-item counter), zeroed by the repack launch
 int repack_grouped_batch(const float* const* srcs, void* const* dsts, const int* hs, const int* ws, int count, int N, int C, int l2norm,
-                         cudaStream_t st);
-int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, cudaStream_t st);
+                         unsigned* counter, cudaStream_t st);
+int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, unsigned* counter, cudaStream_t st);
 
 }  // namespace rmvd

@@ -17,6 +17,12 @@
 //                          planner / producer / MMA warps already work on chunk i + 1 (or the next tile); the key tile
 //                          of the next item goes to TMEM during the last chunk of the current one.
 //
+// Key operand layout ("tile-ordered split", written by nchw_to_keytiles_kernel): per (sample, tile) C / 16 blocks of 4 KB, block ks =
+// the 128 A' rows (TMEM lane 32 q + l = key_hi of tile slot 16 q + l for l < 16, key_lo of slot 16 q + l - 16 for l >= 16) x 16
+// channels as [8-row group 0..15][chunk 0..1][row 0..7][8 bf16]: the canonical layout tcgen05.cp.128x256b copies into 8 TMEM
+// columns (tools/utccp_probe.cu).  A tile's key therefore travels through the same stage ring as the band (one bulk copy per
+// 16 KB) and reaches TMEM without touching a register; the copy is issued by the MMA thread in order with its MMAs.
+//
 // Source operand layout ("grouped split", written by nchw_to_grouped_kernel): per (sample, 32-channel block kc, group of 8
 // consecutive texels of one source row) one 1024-byte block [chunk j = 0..7][texel r = 0..7][8 bf16]; chunks 0..3 hold
 // the hi halves of channels 8j..8j+7, chunks 4..7 the lo halves (x = hi + lo to 2^-17).  Rows are padded to a multiple of
@@ -34,7 +40,7 @@
 namespace rmvd {
 namespace ws {
 
-constexpr int kThreads = 512;
+constexpr int kThreads = 640;                // 4 control warps (planner, producer, MMA, spare) + 16 consumer warps
 constexpr int kPx = 64;                      // key pixels per tile (A' has 2 * kPx = 128 rows: key_hi, key_lo)
 constexpr int kNT = 128;                     // band texels per pass = N of one MMA = columns of one accumulator
 constexpr int kNBuf = 3;                     // accumulators: a whole chunk (<= 3 passes) can sit in TMEM
@@ -50,7 +56,9 @@ static_assert(kGPitch % 32 == 2, "G pitch must be 2 mod 32");
 constexpr int kMaxRows = 64;                 // source rows a band may span
 constexpr int kMaxPlanes = 256;              // planes per chunk
 constexpr int kDescs = 3;                    // chunk descriptors in flight
-constexpr int kConsWarps = 12;
+constexpr int kSchedMax = 1024;              // planes of the inverse-depth schedule the planner keeps in shared memory
+constexpr int kConsWarps = 16;
+constexpr int kRegsControl = 64, kRegsConsumer = 104;   // setmaxnreg moves registers inside the CTA's own allocation (20 warps x 96): 4 * 64 + 16 * 104 = 1920
 constexpr int kConsThreads = kConsWarps * 32;
 constexpr int kStep = kConsWarps / 2;        // planes between two sampling steps of a warp
 
@@ -66,7 +74,7 @@ struct __align__(16) ChunkDesc {
   int pix[kPx];                    // key pixel (y * w + x) of every tile slot, -1 for empty slots
   unsigned dead[kMaxPlanes / 32];  // planes without any valid sample in this tile
   Epi E;
-  const __nv_bfloat16* key;        // split key map of the sample: [pixel][C/32][hi 32 | lo 32]
+  const __nv_bfloat16* key;        // tile-ordered split key block of this (sample, tile)
   const __nv_bfloat16* src;        // grouped split source map of the (view, sample)
   unsigned long long out_base;     // element offset of plane index 0 of this (view, sample) in the outputs
   int hs, ws, wg, G;               // wg: 8-texel groups per source row, G: groups per map
@@ -86,8 +94,8 @@ __shared__ WsConst s_k;
 
 // barrier slots
 constexpr int kBarFull = 0, kBarFree = kBarFull + kStages, kBarAcc = kBarFree + kStages, kBarDrained = kBarAcc + kNBuf,
-              kBarCReady = kBarDrained + kNBuf, kBarCFree = kBarCReady + kDescs, kBarAReady = kBarCFree + kDescs,
-              kNumBars = kBarAReady + 1;
+              kBarCReady = kBarDrained + kNBuf, kBarCFree = kBarCReady + kDescs, kBarAFree = kBarCFree + kDescs,
+              kBarJobReady = kBarAFree + 1, kBarJobDone = kBarJobReady + 1, kNumBars = kBarJobDone + 1;
 
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
 #ifdef RMVD_WS_WATCHDOG
@@ -170,11 +178,15 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned
                : "memory");
 }
 
-// key map, split channels-last lines (nchw_to_split_tile_kernel of psweep_tc.cu): element (p, c)
-__device__ __forceinline__ size_t key_index(size_t p, int c, int C) { return (p * (size_t)(C >> 5) + (size_t)(c >> 5)) * 64 + (c & 31); }
-__device__ __forceinline__ float key_at(const __nv_bfloat16* key, int p, int c, int C) {
-  const size_t o = key_index((size_t)p, c, C);
-  return __bfloat162float(key[o]) + __bfloat162float(key[o + 32]);
+// key tile, tile-ordered split layout: element (tile slot, channel c) of the hi rows in bf16 units; the lo row of the same slot sits
+// 16 rows (two 8-row groups = 256 elements) further
+__device__ __forceinline__ int key_index(int slot, int c) {
+  const int r = 32 * (slot >> 4) + (slot & 15);
+  return (c >> 4) * 2048 + (r >> 3) * 128 + ((c >> 3) & 1) * 64 + (r & 7) * 8 + (c & 7);
+}
+__device__ __forceinline__ float key_at(const __nv_bfloat16* key, int slot, int c) {
+  const int o = key_index(slot, c);
+  return __bfloat162float(key[o]) + __bfloat162float(key[o + 256]);
 }
 // source map, grouped split layout: element (y, x, c) in bf16 units; the lo half sits 256 elements (4 chunks) further
 __device__ __forceinline__ size_t src_index(int G, int wg, int y, int x, int c) {
@@ -195,6 +207,7 @@ struct GroupBatch {
   const float* src[kMaxViews];
   __nv_bfloat16* dst[kMaxViews];
   int hs[kMaxViews], ws[kMaxViews];
+  unsigned* counter;               // work-item counter of the plane-sweep launch that follows: zeroed here
 };
 
 template <bool kNorm>
@@ -202,6 +215,7 @@ __global__ void __launch_bounds__(256) nchw_to_grouped_kernel(const GroupBatch B
   __shared__ float tile[kRpCh][33];
   __shared__ float s_norm[32];
   const int which = blockIdx.z / N, n = blockIdx.z - which * N;
+  if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0) *B.counter = 0u;
   const int hs = B.hs[which], ws = B.ws[which];
   const int wg = (ws + 7) >> 3, tpr = (wg + 3) >> 2;        // groups per row, 32-texel tiles per row
   if ((int)blockIdx.x >= tpr * hs) return;                   // maps of different sizes share the grid of the largest
@@ -262,6 +276,72 @@ __global__ void __launch_bounds__(256) nchw_to_grouped_kernel(const GroupBatch B
         *reinterpret_cast<uint4*>(o) = hi4;
         *reinterpret_cast<uint4*>(o + 256) = lo4;
       }
+    }
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// NCHW fp32 key map -> tile-ordered split copy.  CTA = one tile x 64 channels (one 16 KB stage of the plane-sweep kernel);
+// kNorm: L2-normalised along C first, the CTA then walks all channel blocks itself.
+// ---------------------------------------------------------------------------------------------------------
+template <bool kNorm>
+__global__ void __launch_bounds__(256) nchw_to_keytiles_kernel(const float* __restrict__ key, __nv_bfloat16* __restrict__ dst, int C, int h, int w,
+                                                               int tw, int th, int tiles_x) {
+  __shared__ float tile[64][66];                    // [channel][tile slot]; pitch 66: conflict-free chunk reads below
+  __shared__ float s_norm[64];
+  const int tiles = gridDim.x, tl = blockIdx.x, n = blockIdx.z;
+  const int by = tl / tiles_x, bx = tl - by * tiles_x;
+  const size_t P = (size_t)h * w;
+  const float* __restrict__ src = key + (size_t)n * C * P;
+  __nv_bfloat16* __restrict__ out = dst + ((size_t)n * tiles + tl) * (size_t)C * 128;   // C * 256 bytes per tile
+  const int t = threadIdx.x;
+  // this thread's tile slot for the loads: slot = t & 63, channels (t >> 6) + 4 k
+  const int slot = t & 63, sy = slot / tw, sx = slot - sy * tw;
+  const int py = by * th + sy, pxx = bx * tw + sx;
+  const bool in = (sy < th) && (py < h) && (pxx < w);
+  const size_t poff = in ? (size_t)py * w + pxx : 0;
+  float nrm = 1.0f;
+  if (kNorm) {
+    float acc = 0.f;
+    for (int c = t >> 6; c < C; c += 4) {
+      const float v = in ? __ldg(src + (size_t)c * P + poff) : 0.f;
+      acc = fmaf(v, v, acc);
+    }
+    tile[t >> 6][slot] = acc;
+    __syncthreads();
+    if (t < 64) s_norm[t] = sqrtf(tile[0][t] + tile[1][t] + tile[2][t] + tile[3][t]) + 1e-9f;
+    __syncthreads();
+    nrm = s_norm[slot];
+  }
+  const int cb0 = kNorm ? 0 : blockIdx.y * 64, cb1 = kNorm ? C : min(C, cb0 + 64);
+  for (int c0 = cb0; c0 < cb1; c0 += 64) {
+    const int nc = min(64, C - c0);                 // multiple of 32
+    float v[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      const int c = (t >> 6) + 4 * k;
+      v[k] = (c < nc && in) ? __ldg(src + (size_t)(c0 + c) * P + poff) : 0.f;
+    }
+#pragma unroll
+    for (int k = 0; k < 16; ++k) tile[(t >> 6) + 4 * k][slot] = kNorm ? fdiv(v[k], nrm) : v[k];
+    __syncthreads();
+    // 16-byte chunks of the block in output order: idx = ((ks * 16 + g) * 2 + chunk) * 8 + rr
+    for (int idx = t; idx < (nc >> 4) * 256; idx += 256) {
+      const int rr = idx & 7, chunk = (idx >> 3) & 1, g = (idx >> 4) & 15, ks = idx >> 8;
+      const int r = 8 * g + rr, l = r & 31;
+      const int sl = 16 * (r >> 5) + (l & 15);
+      const bool lo_row = l >= 16;
+      uint4 o4;
+      unsigned* op = reinterpret_cast<unsigned*>(&o4);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float a = tile[ks * 16 + chunk * 8 + 2 * e][sl], b = tile[ks * 16 + chunk * 8 + 2 * e + 1][sl];
+        const __nv_bfloat162 hi = __floats2bfloat162_rn(a, b);
+        const __nv_bfloat162 lo = __floats2bfloat162_rn(a - __low2float(hi), b - __high2float(hi));
+        op[e] = lo_row ? *reinterpret_cast<const unsigned*>(&lo) : *reinterpret_cast<const unsigned*>(&hi);
+      }
+      *reinterpret_cast<uint4*>(out + (size_t)(c0 >> 4) * 2048 + (size_t)idx * 8) = o4;
     }
     __syncthreads();
   }
@@ -339,8 +419,11 @@ __device__ int band_warp(RowSpan* rows, const int* pix, const Epi& E, int w_key,
       const EpiPix e = epi_pixel(E, xi, yi);
       const float dena = e.k_h + E.m * dmin, denb = e.k_h + E.m * dmax;
       bool ok = (dena > 0.f && denb > 0.f) || (dena < 0.f && denb < 0.f);   // no pole inside the interval (false for nan too)
-      ua[j] = (e.u_h + E.e * dmin) / dena; va[j] = (e.v_h + E.i * dmin) / dena;
-      ub[j] = (e.u_h + E.e * dmax) / denb; vb[j] = (e.v_h + E.i * dmax) / denb;
+      // approximate reciprocals (relative error 2^-22): far inside the 0.05-texel dilation for coordinates near the map (< 32768),
+      // irrelevant beyond it (the spans are clipped to the map)
+      const float ra = __fdividef(1.0f, dena), rb = __fdividef(1.0f, denb);
+      ua[j] = (e.u_h + E.e * dmin) * ra; va[j] = (e.v_h + E.i * dmin) * ra;
+      ub[j] = (e.u_h + E.e * dmax) * rb; vb[j] = (e.v_h + E.i * dmax) * rb;
       ok = ok && (fabsf(ua[j]) < 1e7f) && (fabsf(va[j]) < 1e7f) && (fabsf(ub[j]) < 1e7f) && (fabsf(vb[j]) < 1e7f);
       bad = bad || !ok;
     }
@@ -370,7 +453,7 @@ __device__ int band_warp(RowSpan* rows, const int* pix, const Epi& E, int w_key,
     const float dv = vb[j] - va[j];
     du[j] = ub[j] - ua[j];
     sloped[j] = fabsf(dv) > 1e-6f;
-    inv_dv[j] = sloped[j] ? 1.0f / dv : 0.f;
+    inv_dv[j] = sloped[j] ? __fdividef(1.0f, dv) : 0.f;
   }
   int total = 0;                                    // columns so far (warp-uniform): a band that cannot fit stops early
   for (int y = wy0; y <= wy1; ++y) {               // warp-uniform bounds
@@ -441,70 +524,105 @@ __device__ bool plane_interval(const float* __restrict__ invd, long long stride,
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// warp 0: planner
+// warps 0 and 3: planning.  Warp 0 walks the work items and finds each chunk's band; warp 3 fills the per-plane table of the
+// same descriptor at the same time (the two meet on a one-entry mailbox before the descriptor is published).
 // ---------------------------------------------------------------------------------------------------------
+struct PlanJob { int item, slot, s, len, stop; };   // plane-table job: planes [s, s + len) of `item` into descriptor `slot`
+
+struct ItemGeo { int tile, n, v, hs, ws, by, bx; };
+__device__ __forceinline__ ItemGeo item_geo(const PsweepArgs& A, int item, int tiles, int tiles_x) {
+  ItemGeo g;
+  const int q = item / tiles;
+  g.tile = item - q * tiles;
+  g.v = q / A.N;
+  g.n = q - g.v * A.N;
+  g.hs = A.hs[g.v]; g.ws = A.ws[g.v];
+  g.by = g.tile / tiles_x; g.bx = g.tile - g.by * tiles_x;
+  return g;
+}
+
+// inverse-depth schedule of sample n -> shared memory (planes [s_begin, s_end), at most kSchedMax); returns whether every entry
+// is finite and the sequence monotone (the interval of a plane range is then its two end points)
+__device__ bool load_schedule(const PsweepArgs& A, int n, float* sched) {
+  const int lane = threadIdx.x & 31, S_item = A.s_end - A.s_begin;
+  const float* invd = A.invd + (size_t)n * A.ist[0];
+  __syncwarp();
+  for (int i = lane; i < S_item; i += 32) sched[i] = invd[(size_t)(A.s_begin + i) * A.ist[1]];
+  __syncwarp();
+  bool asc = true, desc = true, fin = true;
+  for (int i = lane; i < S_item; i += 32) {
+    const float a = sched[i], b = sched[min(i + 1, S_item - 1)];
+    asc = asc && (a <= b); desc = desc && (a >= b); fin = fin && (fabsf(a) < INFINITY);
+  }
+  return __all_sync(kFullMask, fin) && (__all_sync(kFullMask, asc) || __all_sync(kFullMask, desc));
+}
+
 __device__ void planner(const PsweepArgs& A, const __nv_bfloat16* key_split, ChunkDesc* descs, unsigned bars, int tw, int th, int tiles_x,
-                        int tiles, long long items) {
+                        int tiles, int items, unsigned* counter, float* sched, PlanJob* job) {
   const int lane = threadIdx.x & 31;
   const int P = A.h * A.w, C = A.C;
-  const unsigned bar_cready = bars + 8 * kBarCReady, bar_cfree = bars + 8 * kBarCFree;
+  const unsigned bar_cready = bars + 8 * kBarCReady, bar_cfree = bars + 8 * kBarCFree, bar_jready = bars + 8 * kBarJobReady,
+                 bar_jdone = bars + 8 * kBarJobDone;
+  const int S_item = A.s_end - A.s_begin;
+  const bool cached = S_item <= kSchedMax;
   unsigned seq = 0;
-  auto acquire = [&]() -> ChunkDesc* {
-    const unsigned slot = seq % kDescs;
-    if (seq >= kDescs) {
-      WS_T0();
-      mbar_wait(bar_cfree + 8 * slot, ((seq / kDescs) - 1) & 1);
-      if (lane == 0) WS_ADD(0);
-    }
-    return descs + slot;
-  };
 #ifdef RMVD_WS_STATS
   const long long pl_t0 = clock64();
 #endif
-  auto publish = [&]() {
-    __syncwarp();
-    if (lane == 0) mbar_arrive(bar_cready + 8 * (seq % kDescs));
-    ++seq;
-  };
   int prev_chunks = 1;
-  for (long long item = blockIdx.x; item < items; item += gridDim.x) {
-    const int tile = (int)(item % tiles), n = (int)((item / tiles) % A.N), v = (int)(item / ((long long)tiles * A.N));
-    const int hs = A.hs[v], ws = A.ws[v];
-    const int wg = (ws + 7) >> 3, G = hs * wg;
-    const int by = tile / tiles_x, bx = tile - by * tiles_x;
+  Epi E{};
+  int cur_n = -1, cur_v = -1;
+  bool sched_mono = false;
+  // Work items are handed out in index order through a global counter (the first gridDim.x statically): tiles differ in cost
+  // by a factor of three, and neighbouring CTAs keep working on neighbouring tiles (shared source rows in L2).
+  int item = blockIdx.x;
+  while (item < items) {
+    unsigned nxt = 0;
+    if (lane == 0) nxt = atomicAdd(counter, 1u);      // fetched now, needed after this item's chunks
+    const ItemGeo g = item_geo(A, item, tiles, tiles_x);
+    const int hs = g.hs, ws = g.ws;
     auto pixel_of_slot = [&](int slot) {
       const int ty = slot / tw, tx = slot - ty * tw;
-      const int y = by * th + ty, x = bx * tw + tx;
+      const int y = g.by * th + ty, x = g.bx * tw + tx;
       return (ty < th && y < A.h && x < A.w) ? y * A.w + x : -1;
     };
     const int p0 = pixel_of_slot(lane), p1 = pixel_of_slot(lane + 32);
-    const Epi E = epi_from_calib(A.Kk + n * 9, A.Ks[v] + n * 9, A.T[v] + n * 16, A.h, A.w, hs, ws);
-    EpiPix cpix[4];                                   // the four corner pixels of this tile (clipped to the key map)
-    {
-      const int xa = bx * tw, xb = min(xa + tw, A.w) - 1, ya = by * th, yb = min(ya + th, A.h) - 1;
-      cpix[0] = epi_pixel(E, xa, ya); cpix[1] = epi_pixel(E, xb, ya);
-      cpix[2] = epi_pixel(E, xa, yb); cpix[3] = epi_pixel(E, xb, yb);
+    if (g.n != cur_n || g.v != cur_v) {                // calibration of this (sample, view): once per run of items
+      E = epi_from_calib(A.Kk + g.n * 9, A.Ks[g.v] + g.n * 9, A.T[g.v] + g.n * 16, A.h, A.w, hs, ws);
+      cur_v = g.v;
     }
-    // magnitudes of the summands of u_h, v_h, k_h over the key map (rounding-error scale of the per-pixel terms)
-    const float mag_u = fabsf(E.a) * (float)A.w + fabsf(E.b) * (float)A.h + fabsf(E.c);
-    const float mag_v = fabsf(E.f) * (float)A.w + fabsf(E.g) * (float)A.h + fabsf(E.h);
-    const float mag_k = fabsf(E.j) * (float)A.w + fabsf(E.k) * (float)A.h + fabsf(E.l);
-    const float* invd = A.invd + (size_t)n * A.ist[0];
-    const long long stride = A.ist[1];
-    const int S_item = A.s_end - A.s_begin;
+    if (cached && g.n != cur_n && (cur_n < 0 || A.ist[0] != 0)) sched_mono = load_schedule(A, g.n, sched);   // warp 3 is idle here
+    cur_n = g.n;
+    const float* invd = A.invd + (size_t)g.n * A.ist[0];
     int s = A.s_begin, nchunks = 0;
     int len_hint = (S_item + max(prev_chunks - 1, 1) - 1) / max(prev_chunks - 1, 1);   // one chunk fewer than the last tile needed
     while (s < A.s_end) {
-      ChunkDesc* D = acquire();
-      D->pix[lane] = p0; D->pix[lane + 32] = p1;
-      __syncwarp();
+      const unsigned slot = seq % kDescs;
+      if (seq >= kDescs) {
+        WS_T0();
+        mbar_wait(bar_cfree + 8 * slot, ((seq / kDescs) - 1) & 1);
+        if (lane == 0) WS_ADD(0);
+      }
+      ChunkDesc* D = descs + slot;
       const int rem = A.s_end - s, L0 = min(rem, kMaxPlanes);
       int len = min(max(len_hint, 1), L0), R = -1, ymin = 0, H = 0;
+      if (lane == 0) { job->item = item; job->slot = (int)slot; job->s = s; job->len = len; job->stop = 0; mbar_arrive(bar_jready); }
+      D->pix[lane] = p0; D->pix[lane + 32] = p1;
+      __syncwarp();
       bool direct = false;
       for (;;) {
         float dlo, dhi;
         WS_T0();
-        const bool finite = plane_interval(invd, stride, s, len, dlo, dhi);
+        bool finite;
+        if (cached && sched_mono) {
+          const float da = sched[s - A.s_begin], db = sched[s - A.s_begin + len - 1];
+          dlo = fminf(da, db); dhi = fmaxf(da, db);
+          finite = true;
+        } else if (cached) {
+          finite = plane_interval(sched, 1, s - A.s_begin, len, dlo, dhi);
+        } else {
+          finite = plane_interval(invd, A.ist[1], s, len, dlo, dhi);
+        }
         R = finite ? band_warp(D->rows, D->pix, E, A.w, dlo, dhi, hs, ws, ymin, H) : -1;
         if (lane == 0) { WS_ADD(2); WS_CNT(1, 1); }
         if (R >= 0 && R <= kRMax) break;
@@ -513,71 +631,124 @@ __device__ void planner(const PsweepArgs& A, const __nv_bfloat16* key_split, Chu
         k = (R < 0) ? 2 * k : (k < 8 ? k + 1 : k + (k >> 2));
         len = max(4, min(len - 1, (rem + k - 1) / k));
       }
-      // per-plane terms of the coordinate chain, rounded like the reference, and the dead-plane bits: no pixel of the tile
-      // can have a valid sample on a dead plane (1/d <= 0, :499, or the plane's homography sends all four tile corners -- hence,
-      // with the denominator of one sign over the tile, the whole tile -- beyond the same edge of the source map by more than a
-      // pixel); the denominators must dominate the rounding errors of the per-pixel terms by a wide margin.
-#ifdef RMVD_WS_STATS
-      const long long pt_t0 = clock64();
-#endif
-#pragma unroll 1
-      for (int k8 = 0; k8 < kMaxPlanes / 32; ++k8) {
-        const int i = lane + 32 * k8;
-        if (32 * k8 >= len) break;
-        const float d = (i < len) ? invd[(size_t)(s + i) * stride] : 1.0f;
-        PlaneTerm pt;
-        pt.ed = fmul(E.e, d); pt.id = fmul(E.i, d); pt.md = fmul(E.m, d); pt.zs = fdiv(1.0f, d);
-        if (i < len) D->planes[i] = pt;
-        bool dead = !(pt.zs > 0.0f);
-        if (!dead) {
-          const float den_min = 9.5367431640625e-7f *    // 16 * 2^-24
-              (fmaxf(mag_u + fabsf(pt.ed), mag_v + fabsf(pt.id)) + ((float)max(ws, hs) + 5.0f) * (mag_k + fabsf(pt.md)));
-          int npos = 0, nneg = 0, xl = 0, xr = 0, yt = 0, yb = 0;
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const float den = cpix[k].k_h + pt.md;
-            const float aden = fabsf(den);
-            const bool okd = (aden >= den_min) && (aden <= kDivHi);
-            const float r = rcp_refined(den);
-            const float ix = __fmaf_rn(cpix[k].u_h + pt.ed, r, -0.5f), iy = __fmaf_rn(cpix[k].v_h + pt.id, r, -0.5f);
-            npos += (okd && den > 0.f); nneg += (okd && den < 0.f);
-            xl += (ix < -3.0f); xr += (ix > (float)ws + 1.0f); yt += (iy < -3.0f); yb += (iy > (float)hs + 1.0f);
-          }
-          dead = (npos == 4 || nneg == 4) && (xl == 4 || xr == 4 || yt == 4 || yb == 4);
-        }
-        const unsigned bits = __ballot_sync(kFullMask, dead && i < len && A.dbg_ix0 == nullptr);
-        if (lane == 0) D->dead[k8] = bits;
-      }
-#ifdef RMVD_WS_STATS
-      if (lane == 0) { atomicAdd(&g_ws_stats[3], (unsigned long long)(clock64() - pt_t0)); WS_CNT(5, 1); WS_CNT(6, R > 0 ? R : 0); WS_CNT(7, len); }
-#endif
       if (lane == 0) {
+        const int wg = (ws + 7) >> 3, G = hs * wg;
         D->E = E;
-        D->key = key_split + (size_t)n * P * C * 2;
-        D->src = reinterpret_cast<const __nv_bfloat16*>(A.src[v]) + (size_t)n * (C >> 5) * G * 512;
-        D->out_base = (unsigned long long)(((size_t)(A.v0 + v) * A.N + n) * A.out_S) * (unsigned long long)P;
+        D->key = key_split + ((size_t)g.n * tiles + g.tile) * (size_t)C * 128;
+        D->src = reinterpret_cast<const __nv_bfloat16*>(A.src[g.v]) + (size_t)g.n * (C >> 5) * G * 512;
+        D->out_base = (unsigned long long)(((size_t)(A.v0 + g.v) * A.N + g.n) * A.out_S) * (unsigned long long)P;
         D->hs = hs; D->ws = ws; D->wg = wg; D->G = G;
-        D->n = n; D->v = v;
+        D->n = g.n; D->v = g.v;
         D->kind = direct ? kDirect : kGemm;
         D->first = (s == A.s_begin) ? 1 : 0;
         D->last = (s + len >= A.s_end) ? 1 : 0;
         D->s0 = s; D->len = len; D->R = direct ? 0 : R; D->ymin = ymin; D->H = direct ? 0 : H;
         D->out_plane0 = A.out_s0 + (s - A.s_begin);
+#ifdef RMVD_WS_STATS
+        WS_CNT(5, 1); WS_CNT(6, R > 0 ? R : 0); WS_CNT(7, len);
+#endif
       }
-      publish();
+      {
+        WS_T0();
+        mbar_wait(bar_jdone, seq & 1);                 // the plane table of this descriptor is complete
+        if (lane == 0) WS_ADD(3);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_cready + 8 * slot);
+      ++seq;
       s += len;
       ++nchunks;
       const int rem2 = A.s_end - s;
       if (rem2 > 0) { const int k2 = (rem2 + len - 1) / len; len_hint = (rem2 + k2 - 1) / k2; }
     }
     prev_chunks = nchunks;
+    item = (int)__shfl_sync(kFullMask, nxt, 0) + (int)gridDim.x;
   }
 #ifdef RMVD_WS_STATS
   if (lane == 0) atomicAdd(&g_ws_stats[4], (unsigned long long)(clock64() - pl_t0));
 #endif
-  ChunkDesc* D = acquire();
-  if (lane == 0) D->kind = kStop;
-  publish();
+  const unsigned slot = seq % kDescs;
+  if (seq >= kDescs) mbar_wait(bar_cfree + 8 * slot, ((seq / kDescs) - 1) & 1);
+  if (lane == 0) { descs[slot].kind = kStop; job->stop = 1; mbar_arrive(bar_jready); }
+  __syncwarp();
+  if (lane == 0) mbar_arrive(bar_cready + 8 * slot);
+}
+
+// warp 3: per-plane terms of the coordinate chain, rounded like the reference, and the dead-plane bits: no pixel of the tile can
+// have a valid sample on a dead plane (1/d <= 0, :499, or the plane's homography sends all four tile corners -- hence, with the
+// denominator of one sign over the tile, the whole tile -- beyond the same edge of the source map by more than a pixel); the
+// denominators must dominate the rounding errors of the per-pixel terms by a wide margin.  The job covers the longest chunk the
+// planner may settle on; planes beyond the final length are simply not used.
+__device__ void plane_tabler(const PsweepArgs& A, ChunkDesc* descs, unsigned bars, int tw, int th, int tiles_x, int tiles, const float* sched,
+                             const PlanJob* job) {
+  const int lane = threadIdx.x & 31;
+  const unsigned bar_jready = bars + 8 * kBarJobReady, bar_jdone = bars + 8 * kBarJobDone;
+  const bool cached = (A.s_end - A.s_begin) <= kSchedMax;
+  Epi E{};
+  float mag_u = 0.f, mag_v = 0.f, mag_k = 0.f;
+  EpiPix cpix[4] = {};
+  int cur_n = -1, cur_v = -1, cur_item = -1, hs = 1, ws = 1;
+  const float* invd = A.invd;
+  for (unsigned seq = 0;; ++seq) {
+    mbar_wait(bar_jready, seq & 1);
+    if (job->stop) break;
+    const int item = job->item, s = job->s, len = job->len;
+    ChunkDesc* D = descs + job->slot;
+#ifdef RMVD_WS_STATS
+    const long long pt_t0 = clock64();
+#endif
+    if (item != cur_item) {
+      const ItemGeo g = item_geo(A, item, tiles, tiles_x);
+      hs = g.hs; ws = g.ws;
+      if (g.n != cur_n || g.v != cur_v) {
+        E = epi_from_calib(A.Kk + g.n * 9, A.Ks[g.v] + g.n * 9, A.T[g.v] + g.n * 16, A.h, A.w, hs, ws);
+        // magnitudes of the summands of u_h, v_h, k_h over the key map (rounding-error scale of the per-pixel terms)
+        mag_u = fabsf(E.a) * (float)A.w + fabsf(E.b) * (float)A.h + fabsf(E.c);
+        mag_v = fabsf(E.f) * (float)A.w + fabsf(E.g) * (float)A.h + fabsf(E.h);
+        mag_k = fabsf(E.j) * (float)A.w + fabsf(E.k) * (float)A.h + fabsf(E.l);
+        cur_n = g.n; cur_v = g.v;
+        invd = A.invd + (size_t)g.n * A.ist[0];
+      }
+      const int xa = g.bx * tw, xb = min(xa + tw, A.w) - 1, ya = g.by * th, yb = min(ya + th, A.h) - 1;
+      cpix[0] = epi_pixel(E, xa, ya); cpix[1] = epi_pixel(E, xb, ya);      // the four corner pixels of the tile
+      cpix[2] = epi_pixel(E, xa, yb); cpix[3] = epi_pixel(E, xb, yb);
+      cur_item = item;
+    }
+    const float edge_x = (float)ws + 1.0f, edge_y = (float)hs + 1.0f, span = (float)max(ws, hs) + 5.0f;
+#pragma unroll 1
+    for (int k8 = 0; 32 * k8 < len; ++k8) {
+      const int i = lane + 32 * k8;
+      const float d = (i < len) ? (cached ? sched[s - A.s_begin + i] : invd[(size_t)(s + i) * A.ist[1]]) : 1.0f;
+      PlaneTerm pt;
+      pt.ed = fmul(E.e, d); pt.id = fmul(E.i, d); pt.md = fmul(E.m, d); pt.zs = fdiv(1.0f, d);
+      bool dead = !(pt.zs > 0.0f);
+      if (dead) pt.zs = NAN;                           // never visible in the key view (:499): every compare with it is false
+      if (i < len) D->planes[i] = pt;
+      if (!dead) {
+        const float den_min = 9.5367431640625e-7f *    // 16 * 2^-24
+            (fmaxf(mag_u + fabsf(pt.ed), mag_v + fabsf(pt.id)) + span * (mag_k + fabsf(pt.md)));
+        int npos = 0, nneg = 0, xl = 0, xr = 0, yt = 0, yb = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float den = cpix[k].k_h + pt.md;
+          const float aden = fabsf(den);
+          const bool okd = (aden >= den_min) && (aden <= kDivHi);
+          const float r = rcp_refined(den);
+          const float ix = __fmaf_rn(cpix[k].u_h + pt.ed, r, -0.5f), iy = __fmaf_rn(cpix[k].v_h + pt.id, r, -0.5f);
+          npos += (okd && den > 0.f); nneg += (okd && den < 0.f);
+          xl += (ix < -3.0f); xr += (ix > edge_x); yt += (iy < -3.0f); yb += (iy > edge_y);
+        }
+        dead = (npos == 4 || nneg == 4) && (xl == 4 || xr == 4 || yt == 4 || yb == 4);
+      }
+      const unsigned bits = __ballot_sync(kFullMask, dead && i < len && A.dbg_ix0 == nullptr);
+      if (lane == 0) D->dead[k8] = bits;
+    }
+#ifdef RMVD_WS_STATS
+    if (lane == 0) atomicAdd(&g_ws_stats[15], (unsigned long long)(clock64() - pt_t0));
+#endif
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar_jdone);
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -600,6 +771,19 @@ __device__ void producer(const ChunkDesc* descs, unsigned bars, unsigned stage0,
     const int kind = D->kind;
     if (kind == kStop) break;
     const int R = D->R;
+    if (D->first) {
+      // the key tile of this item: C / 64 stages of [4 K steps][128 A' rows][32 bytes], copied to TMEM by the MMA thread
+      const unsigned char* ksrc = reinterpret_cast<const unsigned char*>(D->key);
+      for (int i = 0; i < (C + 63) / 64; ++i, ++g) {
+        const unsigned sl = g % kStages;
+        if (g >= kStages) mbar_wait(bar_free + 8 * sl, ((g / kStages) - 1) & 1);
+        if (lane == 0) {
+          const unsigned bytes = (unsigned)min(4, C / 16 - 4 * i) * 4096u, full = bar_full + 8 * sl;
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(full), "r"(bytes) : "memory");
+          bulk_g2s(stage0 + sl * kStageBytes, ksrc + (size_t)i * kStageBytes, bytes, full);
+        }
+      }
+    }
     if (kind == kGemm && R > 0) {
       const int H = D->H, ymin = D->ymin, wg = D->wg;
       int cs[2], n8[2], gofs[2];
@@ -648,10 +832,11 @@ __device__ void producer(const ChunkDesc* descs, unsigned bars, unsigned stage0,
 __device__ void mma_issuer(const ChunkDesc* descs, unsigned bars, unsigned stage0, unsigned tmem, int C) {
   const int nkc = C / kKC;
   const unsigned bar_cready = bars + 8 * kBarCReady, bar_full = bars + 8 * kBarFull, bar_free = bars + 8 * kBarFree,
-                 bar_acc = bars + 8 * kBarAcc, bar_drained = bars + 8 * kBarDrained, bar_aready = bars + 8 * kBarAReady;
+                 bar_acc = bars + 8 * kBarAcc, bar_drained = bars + 8 * kBarDrained, bar_afree = bars + 8 * kBarAFree;
   const unsigned long long desc0 = umma_desc(stage0, 128, 1024);
   const unsigned idesc0 = umma_idesc_bf16(2 * kPx, 0);
-  unsigned g = 0, ap = 0, tile_seq = 0;
+  unsigned g = 0, ap = 0, af_seq = 0;
+  bool mma_pending = false;                          // MMAs issued since the last key copy
   for (unsigned seq = 0;; ++seq) {
     const unsigned slot = seq % kDescs;
     {
@@ -662,12 +847,28 @@ __device__ void mma_issuer(const ChunkDesc* descs, unsigned bars, unsigned stage
     const ChunkDesc* D = descs + slot;
     const int kind = D->kind;
     if (kind == kStop) break;
-    if (D->first) {                                   // the key tile of this item is in TMEM
-      WS_T0();
-      mbar_wait(bar_aready, tile_seq & 1);
-      WS_ADD(11);
-      ++tile_seq;
-      asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+    if (D->first) {
+      // Key tile -> TMEM (A' columns) by tcgen05.cp, one 128 x 256-bit copy per K = 16 step.  The copies execute in issue order with
+      // the MMAs that follow; the MMAs of the previous item that still read A' are waited for explicitly.
+      if (mma_pending) {
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(bar_afree) : "memory");
+        WS_T0();
+        mbar_wait(bar_afree, af_seq & 1);
+        WS_ADD(11);
+        ++af_seq;
+        mma_pending = false;
+      }
+      for (int i = 0; i < (C + 63) / 64; ++i, ++g) {
+        const unsigned sl = g % kStages;
+        mbar_wait(bar_full + 8 * sl, (g / kStages) & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+        const int nks = min(4, C / 16 - 4 * i);
+        for (int k = 0; k < nks; ++k) {
+          const unsigned long long kd = umma_desc(stage0 + sl * kStageBytes + k * 4096, 128, 256);
+          asm volatile("tcgen05.cp.cta_group::1.128x256b [%0], %1;\n" ::"r"(tmem + kTmemA + (4 * i + k) * 8), "l"(kd) : "memory");
+        }
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(bar_free + 8 * sl) : "memory");
+      }
     }
     const int R = (kind == kGemm) ? D->R : 0;
     const int npass = (R + kNT - 1) / kNT;
@@ -709,6 +910,7 @@ __device__ void mma_issuer(const ChunkDesc* descs, unsigned bars, unsigned stage
         asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(bar_free + 8 * sl) : "memory");
       }
       asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(bar_acc + 8 * buf) : "memory");
+      mma_pending = true;
     }
   }
 }
@@ -716,39 +918,10 @@ __device__ void mma_issuer(const ChunkDesc* descs, unsigned bars, unsigned stage
 // ---------------------------------------------------------------------------------------------------------
 // consumers
 // ---------------------------------------------------------------------------------------------------------
-// Key tile -> TMEM: TMEM lane 32 q + l = key_hi of tile slot 16 q + l (l < 16) or key_lo of slot 16 q + l - 16 (l >= 16); its
-// channels packed two bf16 per 32-bit column (8 columns per K = 16 step).  The three consumer warps of a quadrant take every
-// third K step.
-constexpr int kKeyIt = (kMaxC / 16 + 2) / 3;
-__device__ __forceinline__ void load_key(const ChunkDesc* D, unsigned tmem, int C, int q, int third, int lane) {
-  const int px = D->pix[16 * q + (lane & 15)];
-  const uint4* src = reinterpret_cast<const uint4*>(D->key + (size_t)max(px, 0) * (C >> 5) * 64 + ((lane < 16) ? 0 : 32));
-  const int nks = C / 16;                              // empty slots read pixel 0 (their G rows are never sampled)
-  uint4 v0[kKeyIt], v1[kKeyIt];
-#pragma unroll
-  for (int i = 0; i < kKeyIt; ++i) {
-    const int ks = third + 3 * i;
-    const int u = (ks >> 1) * 8 + (ks & 1) * 2;        // uint4 index: 128-byte line ks / 2, 16 channels (32 B) at (ks & 1) * 32 B
-    if (ks < nks) { v0[i] = __ldg(src + u); v1[i] = __ldg(src + u + 1); }
-  }
-#pragma unroll
-  for (int i = 0; i < kKeyIt; ++i) {
-    const int ks = third + 3 * i;
-    if (ks < nks) {
-      const unsigned addr = tmem + ((unsigned)(q * 32) << 16) + kTmemA + ks * 8;
-      asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};\n" ::"r"(addr), "r"(v0[i].x),
-                   "r"(v0[i].y), "r"(v0[i].z), "r"(v0[i].w), "r"(v1[i].x), "r"(v1[i].y), "r"(v1[i].z), "r"(v1[i].w)
-                   : "memory");
-    }
-  }
-  asm volatile("tcgen05.wait::st.sync.aligned;\n" ::: "memory");
-  asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
-}
-
 // dot product of one key pixel with one source texel from the split copies (slow paths only)
-__device__ float dot_thread(const ChunkDesc* D, int C, int p, int y, int x) {
+__device__ float dot_thread(const ChunkDesc* D, int C, int slot, int y, int x) {
   float acc = 0.f;
-  for (int c = 0; c < C; ++c) acc = fmaf(key_at(D->key, p, c, C), src_at(D, y, x, c), acc);
+  for (int c = 0; c < C; ++c) acc = fmaf(key_at(D->key, slot, c), src_at(D, y, x, c), acc);
   return acc;
 }
 
@@ -781,10 +954,10 @@ __device__ __noinline__ void sample_slow(const ChunkDesc* D, int p, int pl, int 
     } else {
       const int x0c = clampi(L.x0, 0, ws - 1), x1c = clampi(L.x0 + 1, 0, ws - 1);
       const int y0c = clampi(L.y0, 0, hs - 1), y1c = clampi(L.y0 + 1, 0, hs - 1);
-      g_nw = (L.nw != 0.f) ? dot_thread(D, C, p, y0c, x0c) : 0.f;
-      g_ne = (L.ne != 0.f) ? dot_thread(D, C, p, y0c, x1c) : 0.f;
-      g_sw = (L.sw != 0.f) ? dot_thread(D, C, p, y1c, x0c) : 0.f;
-      g_se = (L.se != 0.f) ? dot_thread(D, C, p, y1c, x1c) : 0.f;
+      g_nw = (L.nw != 0.f) ? dot_thread(D, C, slot, y0c, x0c) : 0.f;
+      g_ne = (L.ne != 0.f) ? dot_thread(D, C, slot, y0c, x1c) : 0.f;
+      g_sw = (L.sw != 0.f) ? dot_thread(D, C, slot, y1c, x0c) : 0.f;
+      g_se = (L.se != 0.f) ? dot_thread(D, C, slot, y1c, x1c) : 0.f;
     }
     val = (g_nw * L.nw + g_ne * L.ne + g_sw * L.sw + g_se * L.se) * K.inv_scale;
   }
@@ -802,7 +975,9 @@ __device__ __noinline__ void sample_slow(const ChunkDesc* D, int p, int pl, int 
 // reference's bit for bit.  ix' = fma(nu, rcp(den), -0.5) is within u (3 ws + 6.5) of U - 0.5 and the reference's chain within
 // u (5.5 ws + 10.5) (u = 2^-24): whenever ix' is further than eps = u (16 ws + 64) from an integer, floor(ix') IS the
 // reference's floor.  Interior samples are valid iff the geometric mask holds; samples with a corner column / row outside
-// the map need the in-range weight below 0.9999 by more than eps (mask 0); everything else takes sample_slow().
+// the map need the in-range weight below 0.9999 by more than eps (mask 0); everything else takes sample_slow().  The
+// reciprocal is MUFU's (relative error <= 2^-23 = 2u, i.e. <= 2u (ws + 2) on ix'): the margin u (10.5 ws + 53.5) left by the
+// reference's own bound covers it several times (tools/filter_check.py perturbs the reciprocal by +-2 ulp).
 struct FastConst {
   float u_h, v_h, k_h;
   float sg, zp;           // visibility in the source as one compare: zs * sg > zp (planesweep_corr.py:500-504)
@@ -817,9 +992,10 @@ __device__ __forceinline__ FastOut sample_fast(const RowSpan* __restrict__ rows,
                                                const PlaneTerm pt, float inv_scale) {
   FastOut o;
   const float den = fadd(K.k_h, pt.md), nu = fadd(K.u_h, pt.ed), nv = fadd(K.v_h, pt.id);      // :334, :343
-  o.geom = (pt.zs > 0.0f) && (pt.zs * K.sg > K.zp);                                             // :499-506
+  o.geom = pt.zs * K.sg > K.zp;                                  // :499-506 (zs is NaN where 1/d <= 0)
   const bool den_ok = fabsf(den) <= kDivHi;
-  const float r = rcp_refined(den);
+  float r;                                                        // 1 ulp reciprocal: inside the trust margins (see above)
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(den));
   const float ix = __fmaf_rn(nu, r, -0.5f), iy = __fmaf_rn(nv, r, -0.5f);
   const float fx = ix - floorf(ix), fy = iy - floorf(iy);        // exact
   o.xi = __float2int_rd(ix); o.yi = __float2int_rd(iy);          // saturating; nan -> 0
@@ -934,10 +1110,9 @@ __device__ void direct_chunk(const PsweepArgs& A, const ChunkDesc* D, int cw, in
       const int qy0 = __shfl_sync(kFullMask, y0c, j), qy1 = __shfl_sync(kFullMask, y1c, j);
       const float nw = __shfl_sync(kFullMask, wnw, j), ne = __shfl_sync(kFullMask, wne, j);
       const float sw = __shfl_sync(kFullMask, wsw, j), se = __shfl_sync(kFullMask, wse, j);
-      const int pj = D->pix[slot0 + j];
       float a = 0.f;
       for (int c = lane; c < C; c += 32) {
-        const float k = key_at(D->key, pj, c, C);
+        const float k = key_at(D->key, slot0 + j, c);
         a = fmaf(k, src_at(D, qy0, qx0, c) * nw + src_at(D, qy0, qx1, c) * ne + src_at(D, qy1, qx0, c) * sw + src_at(D, qy1, qx1, c) * se, a);
       }
       a = warp_sum(a);
@@ -958,17 +1133,9 @@ __device__ void direct_chunk(const PsweepArgs& A, const ChunkDesc* D, int cw, in
 
 __device__ void consumer(const PsweepArgs& A, ChunkDesc* descs, float* G, unsigned bars, unsigned tmem) {
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  const int cw = warp - 4, q = warp & 3, third = (warp >> 2) - 1;
-  const int C = A.C;
+  const int cw = warp - 4, q = warp & 3, part = (warp >> 2) - 1;   // TMEM lane quadrant, which of its four warps
   const unsigned bar_cready = bars + 8 * kBarCReady, bar_cfree = bars + 8 * kBarCFree, bar_acc = bars + 8 * kBarAcc,
-                 bar_drained = bars + 8 * kBarDrained, bar_aready = bars + 8 * kBarAReady;
-  // key tile of the first item
-  mbar_wait(bar_cready, 0);
-  if (descs[0].kind != kStop) {
-    load_key(descs, tmem, C, q, third, lane);
-    __syncwarp();
-    if (lane == 0) mbar_arrive(bar_aready);
-  }
+                 bar_drained = bars + 8 * kBarDrained;
   Pixel px{};
   int p = -1;
   unsigned ap = 0;
@@ -1024,7 +1191,7 @@ __device__ void consumer(const PsweepArgs& A, ChunkDesc* descs, float* G, unsign
 #pragma unroll 1
         for (int hb = 0; hb < kNT / 32; ++hb) {
           const int b = pass * (kNT / 32) + hb, col0 = b * 32;
-          if (col0 < R && (b % 3) == third) {
+          if (col0 < R && hb == part) {
             // Lane l < 16 holds the key_hi row of its pixel, lane l + 16 the key_lo row of the same pixel.  One exchange serves
             // two columns: the lower lane finishes column 2i, the upper lane column 2i + 1; both halves of the warp store.
             float a[32];
@@ -1048,17 +1215,6 @@ __device__ void consumer(const PsweepArgs& A, ChunkDesc* descs, float* G, unsign
     if (rec) { atomicAdd(&g_ws_stats[18], (unsigned long long)acc_wait); atomicAdd(&g_ws_stats[19], (unsigned long long)(clock64() - dr_t0 - acc_wait)); }
     const long long kl_t0 = clock64();
 #endif
-    if (D->last) {
-      // every MMA of this item has completed (its passes were drained above): the key tile of the next item may replace it
-      const unsigned nslot = (seq + 1) % kDescs;
-      mbar_wait(bar_cready + 8 * nslot, ((seq + 1) / kDescs) & 1);
-      const ChunkDesc* Dn = descs + nslot;
-      if (Dn->kind != kStop) {
-        load_key(Dn, tmem, C, q, third, lane);
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar_aready);
-      }
-    }
 #ifdef RMVD_WS_STATS
     if (rec) atomicAdd(&g_ws_stats[20], (unsigned long long)(clock64() - kl_t0));
     const long long b2_t0 = clock64();
@@ -1082,13 +1238,15 @@ __device__ void consumer(const PsweepArgs& A, ChunkDesc* descs, float* G, unsign
 }
 
 __global__ void __launch_bounds__(kThreads, 1) psweep_ws_kernel(const PsweepArgs A, const __nv_bfloat16* __restrict__ key_split, int tw,
-                                                                int th, int tiles_x, int tiles, long long items) {
+                                                                int th, int tiles_x, int tiles, int items, unsigned* counter) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ unsigned s_tmem;
   unsigned char* stage = smem_raw + ((1024 - (smem_u32(smem_raw) & 1023)) & 1023);
   float* G = reinterpret_cast<float*>(stage + kStages * kStageBytes);
   ChunkDesc* descs = reinterpret_cast<ChunkDesc*>(G + kPx * kGPitch);
   unsigned long long* bar_mem = reinterpret_cast<unsigned long long*>(descs + kDescs);
+  float* sched = reinterpret_cast<float*>(bar_mem + kNumBars);
+  PlanJob* job = reinterpret_cast<PlanJob*>(sched + kSchedMax);
   const unsigned bars = smem_u32(bar_mem);
   const int t = threadIdx.x, warp = t >> 5;
 
@@ -1099,8 +1257,8 @@ __global__ void __launch_bounds__(kThreads, 1) psweep_ws_kernel(const PsweepArgs
   if (t == 32) {
     for (int b = 0; b < kNumBars; ++b) {
       const int count = (b >= kBarDrained && b < kBarCReady) ? kConsWarps            // drained: every consumer warp
-                        : (b >= kBarCFree && b < kBarAReady) ? kConsWarps + 1         // descriptor free: consumers + producer
-                        : (b == kBarAReady) ? kConsWarps : 1;
+                        : (b >= kBarCFree && b < kBarAFree) ? kConsWarps + 1          // descriptor free: consumers + producer
+                        : 1;
       asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(bars + 8 * b), "r"(count));
     }
     asm volatile("fence.mbarrier_init.release.cluster;\n");
@@ -1113,13 +1271,19 @@ __global__ void __launch_bounds__(kThreads, 1) psweep_ws_kernel(const PsweepArgs
   asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
   const unsigned tmem = s_tmem;
 
-  if (warp == 0) {
-    planner(A, key_split, descs, bars, tw, th, tiles_x, tiles, items);
-  } else if (warp == 1) {
-    producer(descs, bars, smem_u32(stage), A.C);
-  } else if (warp == 2) {
-    if (elect_one()) mma_issuer(descs, bars, smem_u32(stage), tmem, A.C);
-  } else if (warp >= 4) {
+  if (warp < 4) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;\n" ::"n"(kRegsControl));
+    if (warp == 0) {
+      planner(A, key_split, descs, bars, tw, th, tiles_x, tiles, items, counter, sched, job);
+    } else if (warp == 1) {
+      producer(descs, bars, smem_u32(stage), A.C);
+    } else if (warp == 2) {
+      if (elect_one()) mma_issuer(descs, bars, smem_u32(stage), tmem, A.C);
+    } else {
+      plane_tabler(A, descs, bars, tw, th, tiles_x, tiles, sched, job);
+    }
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" ::"n"(kRegsConsumer));
     consumer(A, descs, G, bars, tmem);
   }
 
@@ -1129,13 +1293,55 @@ __global__ void __launch_bounds__(kThreads, 1) psweep_ws_kernel(const PsweepArgs
 }
 
 static size_t smem_bytes() {
-  return 1024 + (size_t)kStages * kStageBytes + sizeof(float) * kPx * kGPitch + sizeof(ChunkDesc) * kDescs + 8 * kNumBars;
+  return 1024 + (size_t)kStages * kStageBytes + sizeof(float) * kPx * kGPitch + sizeof(ChunkDesc) * kDescs + 8 * kNumBars +
+         sizeof(float) * kSchedMax + sizeof(PlanJob);
 }
 
 }  // namespace ws
 
 size_t psweep_ws_src_bytes(int N, int C, int hs, int ws) {
   return (size_t)N * C * hs * ((ws + 7) & ~7) * sizeof(float);
+}
+
+// Tile rectangle (tw x th <= 64 key pixels): fewest tiles wins, taller tiles weighted by the growth of their bands (one more
+// source row per tile row: 32 x 2 costs ~5 % more per tile than 64 x 1, 16 x 4 ~20 %, 8 x 8 ~90 %).  Widths are rounded up to
+// multiples of 8 pixels where that fits, so output rows of a warp start on 32-byte boundaries.
+void psweep_ws_tile_shape(int h, int w, int* tw_out, int* th_out) {
+  int tw = w, th = 1;
+  double best = 1e30;
+  for (int hh = 1; hh <= ws::kPx && hh <= h; ++hh) {
+    const int wmax = ws::kPx / hh;
+    const int nseg = (w + wmax - 1) / wmax;
+    int wt = (w + nseg - 1) / nseg;
+    if (((wt + 7) & ~7) <= wmax) wt = (wt + 7) & ~7;
+    wt = wt < w ? wt : w;
+    const double f = hh <= 3 ? 1.0 + 0.05 * (hh - 1) : (hh <= 8 ? 1.2 + 0.175 * (hh - 4) : 1.9 + 0.25 * (hh - 8));
+    const double cost = f * ((w + wt - 1) / wt) * ((h + hh - 1) / hh);
+    if (cost < best - 1e-9) { best = cost; tw = wt; th = hh; }
+  }
+  *tw_out = tw; *th_out = th;
+}
+
+size_t psweep_ws_key_bytes(int N, int C, int h, int w) {
+  int tw, th;
+  psweep_ws_tile_shape(h, w, &tw, &th);
+  const size_t tiles = (size_t)((w + tw - 1) / tw) * ((h + th - 1) / th);
+  return (size_t)N * tiles * C * 256;
+}
+
+int repack_key_tiles(const float* key, void* dst, int N, int C, int h, int w, int l2norm, cudaStream_t st) {
+  int tw, th;
+  psweep_ws_tile_shape(h, w, &tw, &th);
+  const int tiles_x = (w + tw - 1) / tw, tiles = tiles_x * ((h + th - 1) / th);
+  if (N > 65535) return (int)cudaErrorInvalidValue;
+  if (l2norm) {
+    dim3 grid(tiles, 1, N);
+    ws::nchw_to_keytiles_kernel<true><<<grid, 256, 0, st>>>(key, reinterpret_cast<__nv_bfloat16*>(dst), C, h, w, tw, th, tiles_x);
+  } else {
+    dim3 grid(tiles, (C + 63) / 64, N);
+    ws::nchw_to_keytiles_kernel<false><<<grid, 256, 0, st>>>(key, reinterpret_cast<__nv_bfloat16*>(dst), C, h, w, tw, th, tiles_x);
+  }
+  return (int)cudaGetLastError();
 }
 
 bool psweep_ws_eligible(const PsweepArgs& A, int nviews) {
@@ -1146,9 +1352,10 @@ bool psweep_ws_eligible(const PsweepArgs& A, int nviews) {
 }
 
 int repack_grouped_batch(const float* const* srcs, void* const* dsts, const int* hs, const int* wss, int count, int N, int C, int l2norm,
-                         cudaStream_t st) {
+                         unsigned* counter, cudaStream_t st) {
   if (count < 1 || count > kMaxViews || (long long)N * count > 65535) return (int)cudaErrorInvalidValue;
   ws::GroupBatch B;
+  B.counter = counter;
   int gmax = 0;
   for (int i = 0; i < kMaxViews; ++i) {
     const int j = i < count ? i : 0;
@@ -1168,7 +1375,7 @@ int repack_grouped_batch(const float* const* srcs, void* const* dsts, const int*
   return (int)cudaGetLastError();
 }
 
-int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, cudaStream_t st) {
+int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, unsigned* counter, cudaStream_t st) {
   static int num_sms = 0;
   static bool attr_set = false;
   if (!attr_set) {
@@ -1179,26 +1386,14 @@ int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, cud
     if (e != cudaSuccess) return (int)e;
     attr_set = true;
   }
-  // Tile rectangle (tw x th <= 64 key pixels): fewest tiles wins, taller tiles weighted by the growth of their bands (one more
-  // source row per tile row).  Widths are rounded up to multiples of 8 pixels where that fits.
-  int tw = A.w, th = 1;
-  {
-    double best = 1e30;
-    for (int h = 1; h <= ws::kPx && h <= A.h; ++h) {
-      const int wmax = ws::kPx / h;
-      const int nseg = (A.w + wmax - 1) / wmax;
-      int wt = (A.w + nseg - 1) / nseg;
-      if (((wt + 7) & ~7) <= wmax) wt = (wt + 7) & ~7;
-      wt = wt < A.w ? wt : A.w;
-      const double f = h <= 3 ? 1.0 + 0.05 * (h - 1) : (h <= 8 ? 1.2 + 0.175 * (h - 4) : 1.9 + 0.25 * (h - 8));
-      const double cost = f * ((A.w + wt - 1) / wt) * ((A.h + h - 1) / h);
-      if (cost < best - 1e-9) { best = cost; tw = wt; th = h; }
-    }
-  }
+  int tw, th;
+  psweep_ws_tile_shape(A.h, A.w, &tw, &th);
   const int tiles_x = (A.w + tw - 1) / tw, tiles_y = (A.h + th - 1) / th;
   const int tiles = tiles_x * tiles_y;
-  const long long items = (long long)tiles * A.N * nviews;
-  const unsigned grid = (unsigned)(items < (long long)num_sms ? items : (long long)num_sms);
+  const long long items_ll = (long long)tiles * A.N * nviews;
+  if (items_ll > 0x7fff0000LL) return (int)cudaErrorInvalidValue;
+  const int items = (int)items_ll;
+  const unsigned grid = (unsigned)(items < num_sms ? items : num_sms);
 #ifdef RMVD_WS_STATS
   {
     unsigned long long z[32] = {0};
@@ -1206,18 +1401,18 @@ int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, cud
   }
 #endif
   ws::psweep_ws_kernel<<<grid, ws::kThreads, ws::smem_bytes(), st>>>(A, reinterpret_cast<const __nv_bfloat16*>(key_split), tw, th, tiles_x, tiles,
-                                                                     items);
+                                                                     items, counter);
 #ifdef RMVD_WS_STATS
   {
     unsigned long long h[32];
     cudaStreamSynchronize(st);
     cudaMemcpyFromSymbol(h, ws::g_ws_stats, sizeof(h));
     const double c = (double)grid, ch = (double)(h[5] ? h[5] : 1);
-    fprintf(stderr, "[psweep_ws] ctas=%u items=%lld chunks=%llu (%.2f per item) mean_R=%.1f mean_len=%.1f band evals per chunk %.2f\n", grid, items, h[5],
+    fprintf(stderr, "[psweep_ws] ctas=%u items=%d chunks=%llu (%.2f per item) mean_R=%.1f mean_len=%.1f band evals per chunk %.2f\n", grid, items, h[5],
             (double)h[5] / (double)items, (double)h[6] / ch, (double)h[7] / ch, (double)h[1] / ch);
-    fprintf(stderr, "[psweep_ws] per CTA kcycles: planner total %.0f (wait cfree %.0f, band %.0f, plane terms %.0f) | producer wait cready %.0f free %.0f | "
+    fprintf(stderr, "[psweep_ws] per CTA kcycles: planner total %.0f (wait cfree %.0f, band %.0f, wait plane table %.0f; table warp busy %.0f) | producer wait cready %.0f free %.0f | "
                     "mma wait cready %.0f aready %.0f drained %.0f full %.0f (stages %.0f)\n",
-            h[4] / c / 1e3, h[0] / c / 1e3, h[2] / c / 1e3, h[3] / c / 1e3, h[8] / c / 1e3, h[9] / c / 1e3, h[10] / c / 1e3, h[11] / c / 1e3, h[12] / c / 1e3,
+            h[4] / c / 1e3, h[0] / c / 1e3, h[2] / c / 1e3, h[3] / c / 1e3, h[15] / c / 1e3, h[8] / c / 1e3, h[9] / c / 1e3, h[10] / c / 1e3, h[11] / c / 1e3, h[12] / c / 1e3,
             h[13] / c / 1e3, h[14] / c);
     fprintf(stderr, "[psweep_ws] consumer (warp 4) per CTA kcycles: total %.0f = wait cready %.0f + bar1 %.0f + wait acc %.0f + drain %.0f + key %.0f + bar2 %.0f + "
                     "sample %.0f ; tiles %.1f\n",
