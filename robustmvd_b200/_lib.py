@@ -10,6 +10,7 @@ from ctypes import c_char_p, c_float, c_int, c_int64, c_size_t, c_void_p, POINTE
 from . import _build
 
 _lib = None
+ABI_VERSION = 1
 
 EXPORTS = (
     "rmvd_abi_version", "rmvd_status_string", "rmvd_psweep_workspace_bytes", "rmvd_psweep_corr_fwd",
@@ -67,11 +68,21 @@ def load():
     """Load (once) ``csrc/librmvd_b200.so``.  Raises RmvdError when it has not been built."""
     global _lib
     if _lib is None:
-        if not os.path.exists(_build.LIB):
-            raise RmvdError(f"{_build.LIB} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
-                            "(robustmvd_b200 has no CPU or PyTorch fallback)")
-        lib = ctypes.CDLL(_build.LIB)
+        path = os.environ.get("RMVD_LIB_PATH") or _build.LIB    # RMVD_LIB_PATH: another build of the same sources (A/B timing only)
+        if path == _build.LIB:
+            if not os.path.exists(path):
+                raise RmvdError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                                "(robustmvd_b200 has no CPU or PyTorch fallback)")
+            if _build.is_stale():
+                # a source file is newer than the library: never run the old binary silently
+                try:
+                    _build.build()
+                except RuntimeError as e:
+                    raise RmvdError(f"{path} is older than its sources and could not be rebuilt: {e}") from e
+        lib = ctypes.CDLL(path)
         _declare(lib)
+        if lib.rmvd_abi_version() != ABI_VERSION:
+            raise RmvdError(f"{path}: ABI version {lib.rmvd_abi_version()}, this binding expects {ABI_VERSION}")
         _lib = lib
     return _lib
 

@@ -1319,6 +1319,11 @@ void psweep_ws_tile_shape(int h, int w, int* tw_out, int* th_out) {
     const double cost = f * ((w + wt - 1) / wt) * ((h + hh - 1) / hh);
     if (cost < best - 1e-9) { best = cost; tw = wt; th = hh; }
   }
+  static const char* const ov = getenv("RMVD_WS_TILE");        // experiments: "tw,th"
+  if (ov) {
+    int a = 0, b = 0;
+    if (sscanf(ov, "%d,%d", &a, &b) == 2 && a > 0 && b > 0 && a * b <= ws::kPx) { tw = a < w ? a : w; th = b < h ? b : h; }
+  }
   *tw_out = tw; *th_out = th;
 }
 
