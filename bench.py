@@ -1,18 +1,27 @@
 #!/usr/bin/env python
 """Benchmark of the plane-sweep cost-volume hot path (BASELINE.json metric: cost-volume voxels/s @384x1280).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--frames F]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--frames F] [--no-secondary]
 
-Workload (configs[1]): robust_mvd plane-sweep correlation at the KITTI shape 384x1280 -> 48x160 features, C = 256,
+Headline workload (configs[1]): robust_mvd plane-sweep correlation at the KITTI shape 384x1280 -> 48x160 features, C = 256,
 S = 256 planes, 2 source views.  One step = one call of PlanesweepCorrelation.forward on a batch of F frames per GPU
-(default 8: 189 MB of features in, 252 MB of corr + mask out, i.e. larger than the 126 MB L2, so consecutive steps
+(default 16: 377 MB of features in, 503 MB of corr + mask out, i.e. larger than the 126 MB L2, so consecutive steps
 cannot be served from cache).  N > 1: one process per GPU (torchrun), each rank sweeps its own frames (weak scaling
 by samples, no data-path collective); the time is the max over ranks.
 
 Prints ONE JSON line (see the round contract): value = voxels/s with inputs resident in HBM; e2e = the same through
 the block API from pinned HOST buffers with the H2D / D2H copies inside the timed region; roofline = algorithmic
-bytes / device time against MEASURED_PEAKS.json; cpu_baseline = oracle/torch_cpu.py (the reference's operator sequence
-on the host cores) on a bounded sample.
+bytes / device time against MEASURED_PEAKS.json; cpu_baseline = the reference's own files on the host cores
+(oracle/_ref, kind "reference") or, where they are absent, oracle/torch_cpu.py (kind "port"), on a bounded sample.
+The other BASELINE.json configs ride on the same line:
+
+  secondary          configs[1] at one frame (the reference's eval batch size), configs[3] shape at one frame (V = 2, 10),
+                     configs[2] MVSNet variance volume + regression (each with roofline, cpu_baseline, e2e)
+  torch_gpu_baseline the reference's operator sequence (oracle/torch_cpu.py) on stock torch CUDA ops on the same B200, and the
+                     mask / index agreement of our kernel with CUDA-ATen grid_sample
+  e2e_model          model.run(**sample) of robust_mvd from host images to host depth (configs[0] shape of work)
+  sweep              configs[4]: planes x views grid at the configs[1] spatial shape, samples sharded over the ranks
+  slab               (N > 1) configs[3]: depth slabs over the ranks with the fused peer-store gather
 """
 import argparse
 import json
@@ -34,14 +43,15 @@ KW = dict(num_sampling_points=CFG["S"], min_depth=CFG["min_depth"], max_depth=CF
 METRIC = "planesweep_cost_volume_voxels_per_s"
 
 
-def voxels(frames):
-    return frames * CFG["V"] * CFG["S"] * CFG["h"] * CFG["w"]
+def voxels(frames, cfg=CFG, V=None, S=None):
+    return frames * (V or cfg["V"]) * (S or cfg["S"]) * cfg["h"] * cfg["w"]
 
 
-def algorithmic_bytes(frames):
+def algorithmic_bytes(frames, cfg=CFG, V=None, S=None):
     """features read once, corr + mask written once."""
-    P = CFG["h"] * CFG["w"]
-    return 4 * frames * CFG["C"] * P * (1 + CFG["V"]) + 2 * 4 * frames * CFG["V"] * CFG["S"] * P
+    P = cfg["h"] * cfg["w"]
+    V, S = V or cfg["V"], S or cfg["S"]
+    return 4 * frames * cfg["C"] * P * (1 + V) + 2 * 4 * frames * V * S * P
 
 
 def measured_peaks():
@@ -84,12 +94,32 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
-def make_inputs(frames, seed):
-    inp = syn.planesweep_inputs(CFG["h"], CFG["w"], CFG["C"], CFG["V"], n=frames, seed=seed)
-    return inp
+def make_inputs(frames, seed, cfg=CFG, V=None):
+    return syn.planesweep_inputs(cfg["h"], cfg["w"], cfg["C"], V or cfg["V"], n=frames, seed=seed)
 
 
-def cpu_reference_step(inp1):
+# ------------------------------------------------------------------------------------------------------------------
+# CPU baselines (the only places where bench.py executes anything under oracle/)
+# ------------------------------------------------------------------------------------------------------------------
+def _reference_block():
+    """The reference's own PlanesweepCorrelation (unmodified file under /root/reference or oracle/_ref), or None."""
+    try:
+        from tools import ref_loader
+        if ref_loader.available():
+            return ref_loader.planesweep_corr().PlanesweepCorrelation()
+    except Exception:  # noqa: BLE001
+        pass
+    return None
+
+
+def cpu_reference_step(inp1, block=None):
+    import torch
+    if block is not None:
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a))  # noqa: E731
+        with torch.no_grad():
+            return block(feat_key=t(inp1["feat_key"]), intrinsics_key=t(inp1["intrinsics_key"]),
+                         feat_sources=[t(f) for f in inp1["feat_sources"]],
+                         source_to_key_transforms=[t(x) for x in inp1["transforms"]], **KW)
     from oracle import torch_cpu
     return torch_cpu.planesweep_correlation(inp1["feat_key"], inp1["intrinsics_key"], inp1["feat_sources"],
                                             inp1["transforms"], **KW)
@@ -100,15 +130,38 @@ def time_cpu_baseline(steps, warmup):
     import torch
     torch.set_num_threads(os.cpu_count())
     inp1 = make_inputs(1, 1234)
+    block = _reference_block()
     for _ in range(warmup):
-        cpu_reference_step(inp1)
+        cpu_reference_step(inp1, block)
     t0 = time.perf_counter()
     for _ in range(steps):
-        cpu_reference_step(inp1)
+        cpu_reference_step(inp1, block)
     dt = (time.perf_counter() - t0) / steps
-    return dict(value=voxels(1) / dt, unit="voxels/s", cores=torch.get_num_threads(), kind="port",
-                sample=f"1 frame of the workload per step ({steps} steps, {dt * 1e3:.0f} ms/frame); oracle/torch_cpu.py = "
-                       "the reference's matmul + grid_sample sequence on torch CPU", ms_per_frame=dt * 1e3)
+    what = ("the reference's own planesweep_corr.py (unmodified, oracle/_ref or /root/reference) on torch CPU" if block is not None
+            else "oracle/torch_cpu.py = the reference's matmul + grid_sample sequence on torch CPU")
+    return dict(value=voxels(1) / dt, unit="voxels/s", cores=torch.get_num_threads(), kind="reference" if block is not None else "port",
+                sample=f"1 frame of the workload per step ({steps} steps, {dt * 1e3:.0f} ms/frame); {what}", ms_per_frame=dt * 1e3)
+
+
+def time_cpu_mvs(planes=24):
+    """MVSNet variance volume (a bounded slab of `planes` of the 192 planes) and regression (full size) on the host cores."""
+    import torch
+    from oracle import torch_cpu
+    torch.set_num_threads(os.cpu_count())
+    c3 = syn.CFG3
+    m = syn.mvs_inputs(c3["h"], c3["w"], c3["C"], c3["V"], c3["D"])
+    t0 = time.perf_counter()
+    torch_cpu.mvs_variance(m["feats"], m["proj"], m["depth"][:, :planes])
+    dt_var = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    torch_cpu.mvs_regress(m["cost"], m["depth"])
+    dt_reg = time.perf_counter() - t0
+    P = c3["h"] * c3["w"]
+    return (dict(value=planes * P / dt_var, unit="voxels/s", cores=torch.get_num_threads(), kind="port",
+                 sample=f"{planes} of {c3['D']} planes, all {c3['V']} views ({dt_var * 1e3:.0f} ms); oracle/torch_cpu.mvs_variance = "
+                        "homo_warp + running sums of mvsnet.py:123-136 on torch CPU"),
+            dict(value=P / dt_reg, unit="pixels/s", cores=torch.get_num_threads(), kind="port",
+                 sample=f"full volume, {dt_reg * 1e3:.0f} ms; softmax + depth_regression + 4-bin confidence (mvsnet.py:140-160) on torch CPU"))
 
 
 def base_line(args, frames, world):
@@ -133,6 +186,264 @@ def run_reference(args):
                  "frames_per_s": 1e3 / cb["ms_per_frame"], "cpu_baseline": cb, "gpu_launches": 0,
                  "e2e": {"value": cb["value"], "unit": "voxels/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
     print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# secondary records (rank 0, after the headline measurement)
+# ------------------------------------------------------------------------------------------------------------------
+def _cold_warm(torch, fn, flush, reps=10):
+    """ms per call: cold (256 MB scratch write before every call) and warm (back to back), CUDA events on the current stream."""
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    cold = []
+    for _ in range(reps):
+        flush.fill_(1)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        cold.append(a.elapsed_time(b))
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return float(np.median(cold)), a.elapsed_time(b) / reps
+
+
+def secondary_records(torch, dev, peaks, with_cpu):
+    from robustmvd_b200.blocks import utils as bu
+    from robustmvd_b200.blocks.planesweep_corr import PlanesweepCorrelation
+    cu = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)  # noqa: E731
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    hbm = peaks["hbm_gbs"]
+    out = []
+
+    def psweep(name, cfg, V, frames=1):
+        inp = make_inputs(frames, 4321, cfg, V)
+        kw = dict(feat_key=cu(inp["feat_key"]), intrinsics_key=cu(inp["intrinsics_key"]), feat_sources=[cu(f) for f in inp["feat_sources"]],
+                  source_to_key_transforms=[cu(t) for t in inp["transforms"]], num_sampling_points=cfg["S"], min_depth=cfg["min_depth"],
+                  max_depth=cfg["max_depth"])
+        blk = PlanesweepCorrelation()
+        cold, warm = _cold_warm(torch, lambda: blk(**kw), flush)
+        ab = algorithmic_bytes(frames, cfg, V)
+        out.append({"name": name, "metric": METRIC, "unit": "voxels/s", "value": voxels(frames, cfg, V) / (cold * 1e-3), "ms_cold": cold,
+                    "ms_warm": warm, "frames": frames, "views": V,
+                    "roofline": {"bound": "hbm", "achieved": ab / cold / 1e6, "peak": hbm, "unit": "GB/s", "frac": ab / cold / 1e6 / hbm,
+                                 "algorithmic_bytes_per_launch": ab, "timing": "ms_cold"}})
+
+    psweep("configs[1] at one frame (the reference's evaluation batch size)", CFG, 2)
+    psweep("configs[3] shape (ETH3D 768x1152 -> 96x144, C=256, S=256), one frame, 2 source views, one GPU", syn.CFG4, 2)
+    psweep("configs[3] shape, one frame, 10 source views, one GPU", syn.CFG4, 10)
+
+    # configs[2]: MVSNet variance volume + regression at the DTU shape
+    c3 = syn.CFG3
+    m = syn.mvs_inputs(c3["h"], c3["w"], c3["C"], c3["V"], c3["D"])
+    feats, proj, depth, cost = cu(m["feats"]), cu(m["proj"]), cu(m["depth"]), cu(m["cost"])
+    P = c3["h"] * c3["w"]
+    cpu_var, cpu_reg = time_cpu_mvs() if with_cpu else (None, None)
+    cold, warm = _cold_warm(torch, lambda: bu.mvs_variance_volume(feats, proj, depth), flush, reps=5)
+    ab = 4 * c3["C"] * P * c3["V"] + 4 * c3["C"] * c3["D"] * P
+    # e2e: pinned host features in, variance volume back in pinned host memory
+    h_feats = torch.from_numpy(m["feats"]).pin_memory()
+    h_var = torch.empty((1, c3["C"], c3["D"], c3["h"], c3["w"]), dtype=torch.float32).pin_memory()
+
+    def var_e2e():
+        f = h_feats.to(dev, non_blocking=True)
+        h_var.copy_(bu.mvs_variance_volume(f, proj, depth), non_blocking=True)
+        torch.cuda.synchronize()
+    var_e2e()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        var_e2e()
+    ms_e2e = (time.perf_counter() - t0) / 3 * 1e3
+    out.append({"name": "configs[2]: MVSNet variance cost volume, DTU 896x1216 -> 224x304, C=32, 5 views, 192 planes",
+                "metric": "mvs_variance_voxels_per_s", "unit": "voxels/s", "value": c3["D"] * P / (cold * 1e-3), "ms_cold": cold, "ms_warm": warm,
+                "roofline": {"bound": "hbm", "achieved": ab / cold / 1e6, "peak": hbm, "unit": "GB/s", "frac": ab / cold / 1e6 / hbm,
+                             "algorithmic_bytes_per_launch": ab, "timing": "ms_cold"},
+                "e2e": {"value": c3["D"] * P / (ms_e2e * 1e-3), "unit": "voxels/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h_feats.numel() * 4,
+                        "d2h_bytes_per_step": h_var.numel() * 4, "api": "blocks.utils.mvs_variance_volume from pinned host features, volume copied back"},
+                "cpu_baseline": cpu_var})
+    cold, warm = _cold_warm(torch, lambda: bu.mvs_regress(cost, depth), flush)
+    ab = 4 * c3["D"] * P + 8 * P
+    h_cost = torch.from_numpy(m["cost"]).pin_memory()
+    h_depth = torch.empty((1, c3["h"], c3["w"]), dtype=torch.float32).pin_memory()
+
+    def reg_e2e():
+        r = bu.mvs_regress(h_cost.to(dev, non_blocking=True), depth)
+        h_depth.copy_(r["depth"], non_blocking=True)
+        torch.cuda.synchronize()
+    reg_e2e()
+    t0 = time.perf_counter()
+    for _ in range(5):
+        reg_e2e()
+    ms_e2e = (time.perf_counter() - t0) / 5 * 1e3
+    out.append({"name": "configs[2]: softmax + expected depth + 4-bin confidence over the regularised cost [1,192,224,304]",
+                "metric": "mvs_regress_pixels_per_s", "unit": "pixels/s", "value": P / (cold * 1e-3), "ms_cold": cold, "ms_warm": warm,
+                "roofline": {"bound": "hbm", "achieved": ab / cold / 1e6, "peak": hbm, "unit": "GB/s", "frac": ab / cold / 1e6 / hbm,
+                             "algorithmic_bytes_per_launch": ab, "timing": "ms_cold"},
+                "e2e": {"value": P / (ms_e2e * 1e-3), "unit": "pixels/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h_cost.numel() * 4,
+                        "d2h_bytes_per_step": h_depth.numel() * 4, "api": "blocks.utils.mvs_regress from a pinned host cost volume, depth copied back"},
+                "cpu_baseline": cpu_reg})
+    return out
+
+
+def torch_gpu_baseline(torch, dev):
+    """The reference's operator sequence on stock torch CUDA ops (same B200), and our kernel's agreement with it."""
+    from oracle import torch_cpu
+    from robustmvd_b200.blocks.planesweep_corr import PlanesweepCorrelation
+    inp = make_inputs(1, 1234)
+    cu = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)  # noqa: E731
+    fk, fs = cu(inp["feat_key"]), [cu(f) for f in inp["feat_sources"]]
+
+    def ref():
+        return torch_cpu.planesweep_correlation(fk, inp["intrinsics_key"], fs, inp["transforms"], device=dev, return_torch=True, **KW)
+    for _ in range(2):
+        rc, rm, _ = ref()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    reps = 5
+    for _ in range(reps):
+        ref()
+    torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) / reps * 1e3
+    corrs, masks, _ = PlanesweepCorrelation()(feat_key=fk, intrinsics_key=cu(inp["intrinsics_key"]), feat_sources=fs,
+                                              source_to_key_transforms=[cu(t) for t in inp["transforms"]], **KW)
+    mism = sum(int((m != r).sum().item()) for m, r in zip(masks, rm))
+    # corr compared where both masks agree (a flipped mask zeroes one side)
+    err = max(float(((c - r).abs() * (m == q)).max().item() / max(float(r.abs().max().item()), 1e-30)) for c, r, m, q in zip(corrs, rc, masks, rm))
+    return {"what": "oracle/torch_cpu.py's operator sequence (all-pairs matmul + 2x grid_sample + thresholds, planesweep_corr.py:152-195) "
+                    "with device='cuda': stock PyTorch on the same B200, configs[1], one frame per step",
+            "value": voxels(1) / (ms * 1e-3), "unit": "voxels/s", "ms_per_frame": ms, "timing": "wall clock around 5 synchronised calls",
+            "mask_mismatches_vs_cuda_aten": mism, "mask_elements": int(sum(m.numel() for m in masks)), "corr_max_rel_err_vs_cuda_aten": err}
+
+
+def e2e_model_record(torch, dev, reps=5):
+    """model.run(**sample): host images -> host depth through the reference's model API (robust_mvd, random init)."""
+    import robustmvd_b200 as rmvd
+    torch.manual_seed(0)
+    model = rmvd.create_model("robust_mvd", pretrained=False, weights=None, num_gpus=1)
+    sample = syn.model_sample(384, 1280, 2)
+    pred, _ = model.run(**sample)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        pred, _ = model.run(**sample)
+    torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) / reps * 1e3
+    nin = sum(int(np.asarray(im).nbytes) for im in sample["images"])
+    return {"what": "robustmvd_b200.create_model('robust_mvd', pretrained=False).run(**sample): 3 host images 384x1280 (key + 2 sources) "
+                    "-> host depth map; random-init weights, encoder / decoder in cuDNN, correlation + fusion in this library",
+            "value": 1e3 / ms, "unit": "frames/s", "ms_per_frame": ms, "h2d_bytes_per_step": nin, "d2h_bytes_per_step": int(pred["depth"].nbytes),
+            "timing": "wall clock around %d synchronised calls" % reps}
+
+
+def sweep_records(torch, dist, dev, world, peaks, frames=4):
+    """configs[4]: S in {64,128,256,512} x V in {2,4,6,8,10} at the configs[1] spatial shape, `frames` samples per rank and step."""
+    from robustmvd_b200.blocks.planesweep_corr import PlanesweepCorrelation
+    cu = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)  # noqa: E731
+    blk = PlanesweepCorrelation()
+    cells = []
+    for V in (2, 4, 6, 8, 10):
+        inp = make_inputs(frames, 99 + int(os.environ.get("RANK", "0")), CFG, V)
+        fk, Kk = cu(inp["feat_key"]), cu(inp["intrinsics_key"])
+        fs, Ts = [cu(f) for f in inp["feat_sources"]], [cu(t) for t in inp["transforms"]]
+        for S in (64, 128, 256, 512):
+            kw = dict(feat_key=fk, intrinsics_key=Kk, feat_sources=fs, source_to_key_transforms=Ts, num_sampling_points=S,
+                      min_depth=CFG["min_depth"], max_depth=CFG["max_depth"])
+            for _ in range(2):
+                blk(**kw)
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            reps = 6
+            e0.record()
+            for _ in range(reps):
+                blk(**kw)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = torch.tensor([e0.elapsed_time(e1) / reps], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            ms = float(ms.item())
+            ab = algorithmic_bytes(frames, CFG, V, S)
+            cells.append({"S": S, "V": V, "ms_per_step": ms, "voxels_per_s": voxels(frames, CFG, V, S) * world / (ms * 1e-3),
+                          "frac_of_hbm": ab / ms / 1e6 / peaks["hbm_gbs"]})
+    return {"what": "configs[4]: planes x source views at 384x1280 -> 48x160, C=256; %d samples per GPU and step, samples sharded over %d GPU(s), "
+                    "no collective; time = max over ranks; back-to-back steps (working set of the small cells fits L2)" % (frames, world),
+            "cells": cells}
+
+
+def slab_records(torch, dist, dev, world, rank):
+    """configs[3]: depth slabs over the ranks, corr / mask gathered by peer stores from inside the plane-sweep kernel."""
+    from robustmvd_b200 import parallel
+    from robustmvd_b200.blocks.planesweep_corr import PlanesweepCorrelation
+    from robustmvd_b200.blocks import utils as bu
+    cfg = syn.CFG4
+    cu = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)  # noqa: E731
+
+    def timed(fn, steps=20, warmup=3):
+        for _ in range(warmup):
+            fn()
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1) / steps], dtype=torch.float64, device=dev)
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    recs = []
+    for V in (2, 10):
+        inp = syn.planesweep_inputs(cfg["h"], cfg["w"], cfg["C"], V, seed=77)      # same seed on every rank: replicated features
+        kw = dict(feat_key=cu(inp["feat_key"]), intrinsics_key=cu(inp["intrinsics_key"]), feat_sources=[cu(f) for f in inp["feat_sources"]],
+                  source_to_key_transforms=[cu(t) for t in inp["transforms"]], num_sampling_points=cfg["S"], min_depth=cfg["min_depth"],
+                  max_depth=cfg["max_depth"])
+        blk = PlanesweepCorrelation()
+        gather = parallel.SlabGather(blk, V, 1, cfg["S"], cfg["h"], cfg["w"], dev)
+        corrs, masks, _ = gather(**kw)
+        full_c, full_m, _ = blk(**kw)
+        torch.cuda.synchronize()
+        ok = all(torch.equal(a, b) for a, b in zip(corrs, full_c)) and all(torch.equal(a, b) for a, b in zip(masks, full_m))
+        okt = torch.tensor([int(ok)], device=dev)
+        dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+        ms_full = timed(lambda: blk(**kw))
+        ms_slab = timed(lambda: blk(plane_range=parallel.slab_range(cfg["S"], world, rank), **kw))
+        ms_total = timed(lambda: gather(**kw))
+        out_bytes = 8 * V * cfg["S"] * cfg["h"] * cfg["w"]
+        recs.append({"views": V, "frames": 1, "ms_1gpu": ms_full, "ms_slab_compute_only": ms_slab, "ms_slab_total": ms_total,
+                     "speedup": ms_full / ms_total, "bit_exact": bool(okt.item()), "mode": gather.mode,
+                     "nvlink_bytes_received_per_rank": out_bytes * (world - 1) // world,
+                     "nvlink_floor_ms_at_770GBs": out_bytes * (world - 1) / world / 770e9 * 1e3})
+    # regression with D partitioned (configs[2] cost shape)
+    c3 = syn.CFG3
+    m = syn.mvs_inputs(c3["h"], c3["w"], 4, 2, c3["D"], seed=5)
+    D = c3["D"]
+    lo, hi = parallel.slab_range(D, world, rank)
+    cost, depth = cu(m["cost"]), cu(m["depth"])
+    cs = cost[:, lo:hi].contiguous()
+    reg = parallel.SlabRegress(1, D, c3["h"], c3["w"], dev)
+    r = reg(cs, depth)
+    r0 = bu.mvs_regress(cost, depth)
+    rel = float(((r["depth"] - r0["depth"]).abs() / r0["depth"].abs()).max().item())
+    agree = float((r["depth_index"] == r0["depth_index"]).float().mean().item())
+    ms_full = timed(lambda: bu.mvs_regress(cost, depth))
+    ms_slab = timed(lambda: reg(cs, depth))
+    return {"what": "configs[3]: robust_mvd correlation at the ETH3D shape 96x144 (C=256, S=256, one frame), planes split over %d GPUs; every rank "
+                    "ends with the full [V,N,S,h,w] corr and mask (LearnedFusion reads planes as channels)" % world,
+            "planesweep": recs,
+            "regress": {"what": "softmax over D sharded (cost [1,192,224,304]): partials (m, Z, A, I) exchanged, merged, 4-bin confidence",
+                        "ms_1gpu": ms_full, "ms_slab_total": ms_slab, "speedup": ms_full / ms_slab, "depth_rel_err": rel, "index_agreement": agree,
+                        "mode": reg.mode}}
 
 
 def run_ours(args):
@@ -227,9 +538,27 @@ def run_ours(args):
         b.record()
     torch.cuda.synchronize()
     ms_call = float(np.mean([a.elapsed_time(b) for a, b in ev]))
+    peaks, which = measured_peaks()
+
+    extra = {}
+    if not args.no_secondary:
+        del pipe, out_host
+        extra["sweep"] = sweep_records(torch, dist, dev, world, peaks)
+        if world > 1:
+            try:
+                extra["slab"] = slab_records(torch, dist, dev, world, rank)
+            except Exception as e:  # noqa: BLE001  (a failed slab leg must not lose the headline line)
+                extra["slab"] = {"error": repr(e)[:400]}
+        if rank == 0:
+            for key, fn in (("secondary", lambda: secondary_records(torch, dev, peaks, not args.no_cpu_baseline)),
+                            ("torch_gpu_baseline", lambda: torch_gpu_baseline(torch, dev)),
+                            ("e2e_model", lambda: e2e_model_record(torch, dev))):
+                try:
+                    extra[key] = fn()
+                except Exception as e:  # noqa: BLE001
+                    extra[key] = {"error": repr(e)[:400]}
 
     if rank == 0:
-        peaks, which = measured_peaks()
         ab = algorithmic_bytes(frames)
         # duration of the launch group: the back-to-back timed region (GPU-bound, no gaps between calls) when the step is the
         # bare call; the per-call event pairs (which can include host gaps) only when an L2 flush sits between the steps
@@ -243,6 +572,7 @@ def run_ours(args):
             "frames_per_s": frames * world / (ms_step * 1e-3),
             "e2e": {"value": voxels(frames) * world / (ms_e2e * 1e-3), "unit": "voxels/s", "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "h2d_gbs_per_rank": h2d / ms_e2e / 1e6, "d2h_gbs_per_rank": d2h / ms_e2e / 1e6,
                     "ms_per_step_blocking": ms_e2e_blocking,
                     "value_blocking": voxels(frames) * world / (ms_e2e_blocking * 1e-3),
                     "api": "HostPlanesweepPipeline.run(wait=False) per step + finish(): PlanesweepCorrelation.forward per chunk "
@@ -250,13 +580,15 @@ def run_ours(args):
                            "H2D / kernels / D2H of consecutive chunks AND of consecutive steps overlap on 3 streams "
                            "(double-buffered device inputs).  *_blocking: each step waits for its last byte before the next "
                            "starts (latency of one batch)" % args.e2e_chunk},
-            "gpu_launches": args.steps * 2,   # one repack launch (key + V source maps) + one plane-sweep kernel per step
+            "gpu_launches": args.steps * 3,   # key repack + source repack (all views) + one persistent plane-sweep kernel per step
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": achieved / peaks["hbm_gbs"], "traffic": ncu_traffic(frames), "peak_source": which,
-                         "kernel": "rmvd_psweep_corr_fwd = nchw_to_split_tile_kernel (key + V sources, one launch) + psweep_tc_kernel (tcgen05 + TMA)",
+                         "kernel": "rmvd_psweep_corr_fwd = nchw_to_keytiles_kernel + nchw_to_grouped_kernel (split copies) + "
+                                   "psweep_ws_kernel (persistent, tcgen05 + TMEM + bulk copies)",
                          "algorithmic_bytes_per_launch": ab, "ms_per_launch": ms_launch, "ms_per_call_event_pairs": ms_call},
             "clocks": clocks,
         })
+        line.update(extra)
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = time_cpu_baseline(3, 1)
         if world > 1:
@@ -264,12 +596,14 @@ def run_ours(args):
             os.dup2(saved_stdout, 1)
         print(json.dumps(line), flush=True)
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 
 def ncu_traffic(frames):
-    """DRAM bytes (read + write) of one call's kernels from the committed ncu --set full capture (profiles/roofline_traffic.json,
-    written from the capture by hand; bytes are per call of 8 frames), or None when the run does not match the capture."""
+    """DRAM bytes (read + write) of one call's kernels, summed over the launches of the call from the committed ncu --set full
+    capture (profiles/roofline_traffic.json, written by tools/ncu_traffic.py from the .ncu-rep), or None when the run does not
+    match the capture."""
     path = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if not os.path.exists(path):
         return None
@@ -283,8 +617,9 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--frames", type=int, default=16, help="frames per GPU per step (16 x 240 tiles = 12.97 waves of 296 CTA slots)")
+    ap.add_argument("--frames", type=int, default=16, help="frames per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="headline line only (no secondary / baseline / sweep / slab records)")
     ap.add_argument("--e2e-chunk", default="2", help="frames per chunk of the host pipeline (e2e leg); a,b,c = schedule, last repeats")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -23,7 +23,8 @@
 extern "C" {
 #endif
 
-#define RMVD_ABI_VERSION 1
+#define RMVD_ABI_VERSION 2
+#define RMVD_MAX_PEERS 8      /* ranks of one depth-slab communicator (GPUs of one NVSwitch box) */
 
 #define RMVD_OK 0
 #define RMVD_E_NULL (-1)      /* required pointer is NULL */
@@ -76,6 +77,28 @@ int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* feat_src, co
                          int normalize_mode, float* corr, float* mask, int out_S, int out_s0,
                          int32_t* dbg_ix0, int32_t* dbg_iy0, uint8_t* dbg_geom, void* workspace,
                          size_t workspace_bytes, void* stream);
+
+/*
+ * Depth-slab form of rmvd_psweep_corr_fwd for G = num_peers GPUs of one NVLink / NVSwitch box (partition 1; the
+ * reference has no counterpart -- its only multi-GPU mode is nn.DataParallel over the batch, rmvd/models/helpers.py:161-170).
+ * Rank `rank` computes planes [s_begin, s_end) and its sampling loop stores every corr / mask row into the [V,N,out_S,h,w]
+ * tensors of ALL ranks (corr_peers[g], mask_peers[g]: peer-mapped device pointers, entry `rank` = this rank's own tensors), at
+ * plane index out_s0 + (s - s_begin): the all-gather that the consumer (LearnedFusion, learned_fusion.py:13-17: planes are
+ * channels) needs happens inside the kernel over NVLink.  The kernel ends with a handshake: the last CTA writes `epoch` to slot
+ * `rank` of every rank's flag array (flag_peers[g]: peer-mapped uint32[num_peers], zero before the first call) and waits until
+ * its own array holds >= epoch in every slot.  Hence, when the call's kernel has completed on this rank's stream, all ranks'
+ * slabs are present in this rank's tensors.  `epoch` must increase by one per call of the communicator; callers alternate
+ * between two sets of output tensors so that a rank that runs ahead never overwrites rows a slower rank is still reading.
+ * All ranks must issue the call (same shapes, own slab); num_peers <= RMVD_MAX_PEERS; the debug outputs are not available.
+ * Requires the persistent tcgen05 kernel (C % 32 == 0, C <= 256, per-plane hypotheses): RMVD_E_MODE otherwise.
+ */
+int rmvd_psweep_corr_fwd_peers(const float* feat_key, const float* const* feat_src, const float* intrinsics_key,
+                               const float* const* intrinsics_src, const float* const* src_to_key,
+                               const float* invdepths, const int64_t* inv_stride_host, int N, int C, int h, int w,
+                               int V, const int* hs_host, const int* ws_host, int S, int s_begin, int s_end,
+                               int normalize_mode, int out_S, int out_s0, int num_peers, int rank,
+                               float* const* corr_peers, float* const* mask_peers, uint32_t* const* flag_peers,
+                               uint32_t epoch, void* workspace, size_t workspace_bytes, void* stream);
 
 /*
  * Backward of rmvd_psweep_corr_fwd with respect to the feature maps.  The reference obtains it from
@@ -172,6 +195,24 @@ int rmvd_softargmax_combine(const float* partials, int G, int B, int h, int w, f
  */
 int rmvd_softargmax_confidence(const float* cost_slab, const float* merged, int B, int Dl, int h, int w,
                                int D, int d_begin, float* conf_part, void* stream);
+
+/*
+ * rmvd_mvs_regress_fwd with D sharded over the num_peers GPUs of one NVLink / NVSwitch box, as ONE kernel per rank (SURVEY.md 8e,
+ * partition 1b; replaces rmvd_softargmax_partial + all-gather + rmvd_softargmax_combine + rmvd_softargmax_confidence +
+ * all-reduce).  Rank g holds planes [lo_g, lo_g + Dl_g) of the regularised cost (balanced contiguous partition: the first
+ * D % num_peers ranks hold one plane more) in a peer-mapped buffer cost_peers[g] laid out [B, Dl_max, h*w], Dl_max =
+ * ceil(D / num_peers).  The kernel computes the (m, Z, A, I) partials of its slab (mvsnet.py:140-141 as an online softmax),
+ * stores them into slot `rank` of every rank's parts_peers[g] ([num_peers, 4, B*h*w] floats), meets the other ranks on
+ * flag_peers[g] (uint32 [2 * num_peers], zero before the first call; `epoch` increases by one per call), merges, and evaluates the
+ * 4-bin confidence (mvsnet.py:143-160) reading the four cost values from the ranks that own them.  A second handshake ends the
+ * kernel: when it has completed, no rank reads this rank's cost slab or partial buffer any more.  Every rank obtains the full
+ * depth / confidence / depth_index / expected_index (each optional, [B,h,w]).  depths: [B, D] on every rank.  local_counters:
+ * device uint32 [2], zero.  All ranks must issue the call.
+ */
+int rmvd_softargmax_slab_fused(const float* const* cost_peers, const float* depths, int B, int D, int h, int w, int num_peers,
+                               int rank, float* const* parts_peers, uint32_t* const* flag_peers, uint32_t epoch,
+                               uint32_t* local_counters, float* depth, float* confidence, int64_t* depth_index,
+                               float* expected_index, void* stream);
 
 /*
  * soft_argmin / entropy of Vis-MVSNet (blocks/utils.py:51-68) along dim 1: volume [B,D,h,w] ->

@@ -10,14 +10,15 @@ from ctypes import c_char_p, c_float, c_int, c_int64, c_size_t, c_void_p, POINTE
 from . import _build
 
 _lib = None
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 EXPORTS = (
     "rmvd_abi_version", "rmvd_status_string", "rmvd_psweep_workspace_bytes", "rmvd_psweep_corr_fwd",
+    "rmvd_psweep_corr_fwd_peers",
     "rmvd_psweep_warp_fwd", "rmvd_psweep_bwd_workspace_bytes", "rmvd_psweep_corr_bwd",
     "rmvd_corr_grid_fwd", "rmvd_warp_grid_fwd", "rmvd_mvs_variance_fwd",
     "rmvd_homo_warp_fwd", "rmvd_mvs_regress_fwd", "rmvd_softargmax_partial", "rmvd_softargmax_combine",
-    "rmvd_softargmax_confidence", "rmvd_soft_argmin_fwd", "rmvd_view_fusion_fwd", "rmvd_homography_groupcorr_fwd", "rmvd_homography_warp_fwd", "rmvd_vis_cost_volume_fwd", "rmvd_cvp_proj_cost_fwd", "rmvd_cvp_projections", "rmvd_debug_div_check",
+    "rmvd_softargmax_confidence", "rmvd_softargmax_slab_fused", "rmvd_soft_argmin_fwd", "rmvd_view_fusion_fwd", "rmvd_homography_groupcorr_fwd", "rmvd_homography_warp_fwd", "rmvd_vis_cost_volume_fwd", "rmvd_cvp_proj_cost_fwd", "rmvd_cvp_projections", "rmvd_debug_div_check",
 )
 
 
@@ -37,6 +38,8 @@ def _declare(lib):
     lib.rmvd_psweep_workspace_bytes.argtypes = [c_int, c_int, c_int, c_int, c_int, PI, PI]
     lib.rmvd_psweep_corr_fwd.argtypes = [P, PP, P, PP, PP, P, PL] + [c_int] * 5 + [PI, PI] + [c_int] * 4 + \
         [P, P, c_int, c_int, P, P, P, P, c_size_t, P]
+    lib.rmvd_psweep_corr_fwd_peers.argtypes = [P, PP, P, PP, PP, P, PL] + [c_int] * 5 + [PI, PI] + [c_int] * 8 + \
+        [PP, PP, PP, ctypes.c_uint32, P, c_size_t, P]
     lib.rmvd_psweep_bwd_workspace_bytes.restype = c_size_t
     lib.rmvd_psweep_bwd_workspace_bytes.argtypes = [c_int, c_int, c_int, c_int, c_int, PI, PI]
     lib.rmvd_psweep_corr_bwd.argtypes = [P, PP, P, PP, PP, P, PL] + [c_int] * 5 + [PI, PI] + [c_int] * 4 + \
@@ -50,6 +53,7 @@ def _declare(lib):
     lib.rmvd_softargmax_partial.argtypes = [P, P] + [c_int] * 5 + [P, P]
     lib.rmvd_softargmax_combine.argtypes = [P] + [c_int] * 4 + [P, P]
     lib.rmvd_softargmax_confidence.argtypes = [P, P] + [c_int] * 6 + [P, P]
+    lib.rmvd_softargmax_slab_fused.argtypes = [PP, P] + [c_int] * 6 + [PP, PP, ctypes.c_uint32, P, P, P, P, P, P]
     lib.rmvd_soft_argmin_fwd.argtypes = [P] + [c_int] * 4 + [c_float, P, P, P, P, P]
     lib.rmvd_view_fusion_fwd.argtypes = [PP, PP, PP] + [c_int] * 5 + [P, P, P, P]
     lib.rmvd_homography_groupcorr_fwd.argtypes = [P, P, P, PL] + [c_int] * 6 + [P, P]
@@ -107,6 +111,14 @@ def ptr_array(tensors):
     arr = (c_void_p * len(tensors))()
     for i, t in enumerate(tensors):
         arr[i] = ptr(t).value
+    return arr
+
+
+def raw_ptr_array(addresses):
+    """Host array of device pointers given as integers (peer-mapped addresses of symmetric memory)."""
+    arr = (c_void_p * len(addresses))()
+    for i, a in enumerate(addresses):
+        arr[i] = int(a)
     return arr
 
 

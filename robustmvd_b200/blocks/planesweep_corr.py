@@ -28,6 +28,27 @@ def _f32c(t):
     return t.detach().to(torch.float32).contiguous()
 
 
+def _calib(t, N, rows, device, what):
+    """Calibration tensor for the C ABI: float32, contiguous, exactly ``[N, rows, rows]``.  The kernels index these arrays as
+    ``K + n * 9`` / ``T + n * 16`` and only see pointers, so shapes are settled here: the reference slices ``[:, i, j]`` and thus also
+    takes ``[N,3,4]`` transforms (padded with the row 0 0 0 1) and batch-1 tensors that broadcast over N (expanded)."""
+    t = _f32c(_to_torch(t, device))
+    if t.ndim == 2:
+        t = t[None]
+    if t.ndim != 3:
+        raise _lib.RmvdError(f"{what}: expected [N,{rows},{rows}], got {tuple(t.shape)}")
+    if rows == 4 and tuple(t.shape[1:]) == (3, 4):
+        last = torch.tensor([0.0, 0.0, 0.0, 1.0], dtype=torch.float32, device=t.device).expand(t.shape[0], 1, 4)
+        t = torch.cat([t, last], 1)
+    if tuple(t.shape[1:]) != (rows, rows):
+        raise _lib.RmvdError(f"{what}: expected [N,{rows},{rows}], got {tuple(t.shape)}")
+    if t.shape[0] == 1 and N > 1:
+        t = t.expand(N, rows, rows)
+    if t.shape[0] != N:
+        raise _lib.RmvdError(f"{what}: batch {t.shape[0]} does not match the feature batch {N}")
+    return t.contiguous()
+
+
 def _corr_norm_mode(normalize):
     """TorchCorr semantics (:170-179): "dim" -> /sqrt(C); True / "before" -> L2-normalise both inputs."""
     if normalize == "dim":
@@ -54,10 +75,10 @@ def compute_sampling_invdepths(min_depth, max_depth, num_samples, sampling_type=
     Evaluated on the HOST with the reference's own operation order (S values per sample): torch's CUDA division
     by a scalar multiplies by the reciprocal, which would move the last bit of the schedule.
     """
-    if isinstance(min_depth, (np.float32, float)):
-        min_depth = torch.tensor([min_depth])
-    if isinstance(max_depth, (np.float32, float)):
-        max_depth = torch.tensor([max_depth])
+    if isinstance(min_depth, (np.float32, float, int)):
+        min_depth = torch.tensor([float(min_depth)])
+    if isinstance(max_depth, (np.float32, float, int)):
+        max_depth = torch.tensor([float(max_depth)])
     min_depth = _to_torch(min_depth).cpu()[..., None]
     max_depth = _to_torch(max_depth).cpu()[..., None]
     min_invdepth = 1 / max_depth
@@ -300,9 +321,9 @@ class PlanesweepCorrelation(nn.Module):
         s0, s1 = (0, S) if plane_range is None else plane_range
         Sl = s1 - s0
         srcs = [_f32c(f) for f in feat_sources]
-        Kk = _f32c(_to_torch(intrinsics_key, dev))
-        Ks = [_f32c(_to_torch(k, dev)) for k in intrinsics_sources]
-        Ts = [_f32c(_to_torch(t, dev)) for t in source_to_key_transforms]
+        Kk = _calib(intrinsics_key, N, 3, dev, "intrinsics_key")
+        Ks = [_calib(k, N, 3, dev, "intrinsics_sources") for k in intrinsics_sources]
+        Ts = [_calib(t, N, 4, dev, "source_to_key_transforms") for t in source_to_key_transforms]
         hs = [f.shape[2] for f in srcs]
         ws = [f.shape[3] for f in srcs]
         grad_corr = _f32c(grad_corr)
@@ -323,7 +344,7 @@ class PlanesweepCorrelation(nn.Module):
     @torch.no_grad()
     def _forward_impl(self, feat_key, intrinsics_key, feat_sources, source_to_key_transforms, intrinsics_sources=None,
                       num_sampling_points=None, min_depth=None, max_depth=None, sampling_invdepths=None,
-                      sampling_type="linear_invdepth", plane_range=None, debug=False, out=None, norm_mode=None):
+                      sampling_type="linear_invdepth", plane_range=None, debug=False, out=None, norm_mode=None, peers=None):
         self.reset()
         dev = feat_key.device
         if intrinsics_sources is None:  # :441-442
@@ -340,15 +361,32 @@ class PlanesweepCorrelation(nn.Module):
         s0, s1 = (0, S) if plane_range is None else plane_range
         Sl = s1 - s0
         srcs = [_f32c(f) for f in feat_sources]
-        Kk = _f32c(intrinsics_key)
-        Ks = [_f32c(k) for k in intrinsics_sources]
-        Ts = [_f32c(t) for t in source_to_key_transforms]
+        Kk = _calib(intrinsics_key, N, 3, dev, "intrinsics_key")
+        Ks = [_calib(k, N, 3, dev, "intrinsics_sources") for k in intrinsics_sources]
+        Ts = [_calib(t, N, 4, dev, "source_to_key_transforms") for t in source_to_key_transforms]
+        for f in srcs:
+            if f.ndim != 4 or f.shape[0] != N or f.shape[1] != C:
+                raise _lib.RmvdError(f"feat_sources: expected [{N},{C},hs,ws], got {tuple(f.shape)}")
         hs = [f.shape[2] for f in srcs]
         ws = [f.shape[3] for f in srcs]
         ist = _lib.i64_array(_inv_strides(inv_c, N))
         lib = _lib.load()
         if V == 0:
             return self.corrs, self.masks, inv
+        if peers is not None:
+            # depth-slab mode (parallel.SlabGather): rows go to every rank's [V,N,S,h,w] tensors from inside the kernel
+            assert not self.warp_only and not debug and out is None
+            nb = lib.rmvd_psweep_workspace_bytes(N, C, h, w, V, _lib.int_array(hs), _lib.int_array(ws))
+            wsp = _workspace(nb, dev)
+            G = len(peers["corr"])
+            st = lib.rmvd_psweep_corr_fwd_peers(
+                _lib.ptr(feat_key), _lib.ptr_array(srcs), _lib.ptr(Kk), _lib.ptr_array(Ks), _lib.ptr_array(Ts),
+                _lib.ptr(inv_c), ist, N, C, h, w, V, _lib.int_array(hs), _lib.int_array(ws), S, s0, s1,
+                _corr_norm_mode(self.normalize) if norm_mode is None else norm_mode, S, s0, G, peers["rank"],
+                _lib.raw_ptr_array(peers["corr"]), _lib.raw_ptr_array(peers["mask"]), _lib.raw_ptr_array(peers["flags"]),
+                peers["epoch"], _lib.ptr(wsp), wsp.numel(), _lib.stream_ptr())
+            _lib.check(st, "rmvd_psweep_corr_fwd_peers")
+            return None, None, inv
         if not self.warp_only:
             if out is None:
                 corr = torch.empty((V, N, Sl, h, w), dtype=torch.float32, device=dev)

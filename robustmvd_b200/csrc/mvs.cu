@@ -478,6 +478,218 @@ __global__ void __launch_bounds__(kRegWarps * 32) mvs_regress_kernel(const float
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Vectorised form of the regression (no probability volume): CTA = 4 plane groups x 32 lanes x VEC adjacent pixels, eight
+// VEC-wide loads in flight per thread; 128 threads and ~56 registers keep every CTA of a DTU-sized volume resident at once
+// (one wave, no tail).  VEC = 2 needs an even pixel count (8-byte aligned rows).
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kVecWarps = 4;
+
+template <int VEC>
+__device__ __forceinline__ void soft_accumulate(const float* __restrict__ x, const float* __restrict__ dv, int D, size_t P, int index0, int g,
+                                                SoftState* st) {
+  constexpr int kB = 8;
+  int d = g;
+  for (; d + (kB - 1) * kVecWarps < D; d += kB * kVecWarps) {
+    float xv[kB][VEC], dz[kB];
+#pragma unroll
+    for (int k = 0; k < kB; ++k) {
+      const float* q = x + (size_t)(d + k * kVecWarps) * P;
+      if (VEC == 2) { const float2 t = __ldg(reinterpret_cast<const float2*>(q)); xv[k][0] = t.x; xv[k][VEC - 1] = t.y; }
+      else xv[k][0] = __ldg(q);
+    }
+#pragma unroll
+    for (int k = 0; k < kB; ++k) dz[k] = __ldg(dv + d + k * kVecWarps);
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) {
+      float mx = st[v].m;
+#pragma unroll
+      for (int k = 0; k < kB; ++k) mx = fmaxf(mx, xv[k][v]);
+      const float r = __expf(st[v].m - mx);                // exp(-inf) = 0 on the first batch
+      st[v].Z *= r; st[v].A *= r; st[v].I *= r; st[v].m = mx;
+#pragma unroll
+      for (int k = 0; k < kB; ++k) {
+        const float e = __expf(xv[k][v] - mx);
+        st[v].Z += e;
+        st[v].A = fmaf(e, dz[k], st[v].A);
+        st[v].I = fmaf(e, (float)(index0 + d + k * kVecWarps), st[v].I);
+      }
+    }
+  }
+  for (; d < D; d += kVecWarps)
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) soft_push(st[v], __ldg(x + (size_t)d * P + v), __ldg(dv + d), (float)(index0 + d));
+}
+
+template <int VEC>
+__global__ void __launch_bounds__(kVecWarps * 32) mvs_regress_vec_kernel(const float* __restrict__ cost, const float* __restrict__ depths, int B, int D,
+                                                                         int P, int index0, int mode, float* __restrict__ depth_out,
+                                                                         float* __restrict__ conf_out, long long* __restrict__ index_out,
+                                                                         float* __restrict__ eidx_out, float* __restrict__ partial) {
+  __shared__ SoftState s_state[kVecWarps][32 * VEC];
+  const int b = blockIdx.y;
+  const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int p = (blockIdx.x * 32 + lane) * VEC;
+  const bool act = p < P;                                    // P is a multiple of VEC: p + VEC - 1 < P too
+  const float* x = cost + (size_t)b * D * P + p;
+  SoftState st[VEC];
+#pragma unroll
+  for (int v = 0; v < VEC; ++v) st[v] = SoftState{-INFINITY, 0.f, 0.f, 0.f};
+  if (act) soft_accumulate<VEC>(x, depths + (size_t)b * D, D, (size_t)P, index0, g, st);
+#pragma unroll
+  for (int v = 0; v < VEC; ++v) s_state[g][lane * VEC + v] = st[v];
+  __syncthreads();
+  // the 64 (32 * VEC) pixels of the CTA are finished by its first 32 * VEC threads, one pixel each
+  const int j = threadIdx.x;
+  if (j < 32 * VEC) {
+    SoftState t = s_state[0][j];
+#pragma unroll
+    for (int k = 1; k < kVecWarps; ++k) soft_merge(t, s_state[k][j]);
+    const int pp = blockIdx.x * 32 * VEC + j;
+    if (pp < P) {
+      const size_t o = (size_t)b * P + pp;
+      if (mode == 1) {
+        const size_t BP = (size_t)B * P;
+        partial[o] = t.m; partial[BP + o] = t.Z; partial[2 * BP + o] = t.A; partial[3 * BP + o] = t.I;
+      } else {
+        const float depth = t.A / t.Z, eidx = t.I / t.Z;
+        if (depth_out) depth_out[o] = depth;
+        if (eidx_out) eidx_out[o] = eidx;
+        int idx = (int)eidx;  // .long() truncates (mvsnet.py:153-156)
+        idx = idx < 0 ? 0 : (idx > D - 1 ? D - 1 : idx);
+        if (index_out) index_out[o] = idx;
+        if (conf_out) {  // prob_volume_sum4[idx] = p[idx-1] + p[idx] + p[idx+1] + p[idx+2], zero padded (:145-158)
+          const float* xc = cost + (size_t)b * D * P + pp;
+          float acc = 0.f;
+#pragma unroll
+          for (int k = -1; k <= 2; ++k) {
+            const int dd = idx + k;
+            if (dd >= 0 && dd < D) acc += expf(__ldg(xc + (size_t)dd * P) - t.m);
+          }
+          conf_out[o] = acc / t.Z;
+        }
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Regression with D sharded over the G GPUs of one box, ONE kernel per rank (partition 1b).  Persistent grid (every
+// CTA resident).  Phase 1: online-softmax partials (m, Z, A, I) of this rank's planes, stored into slot `rank` of EVERY rank's
+// partial buffer through peer-mapped pointers.  Handshake (flags in symmetric memory, system-scope release / acquire).  Phase 2,
+// every rank for all pixels: merge of the G partials, expected depth / index, and the 4-bin confidence around the global index,
+// its four cost values read from whichever rank owns them (peer loads).  Second handshake: no rank leaves while another may still
+// read its cost slab.  No NCCL call, no second collective for the confidence.
+// ---------------------------------------------------------------------------------------------------------
+struct SlabRegressArgs {
+  int n, rank;
+  const float* cost[RMVD_MAX_PEERS];     // [B, Dl_max, P] of every rank (slab of rank g: planes slab_lo(g) ...)
+  float* parts[RMVD_MAX_PEERS];          // [n, 4, B * P] of every rank
+  unsigned* flags[RMVD_MAX_PEERS];       // uint32 [2 * n] of every rank
+  unsigned epoch;
+  unsigned* counters;                    // local uint32 [2], zero
+};
+
+__device__ __forceinline__ void slab_handshake(const SlabRegressArgs& A, int which, unsigned nblocks) {
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned prev = atomicAdd(A.counters + which, 1u);
+    if (prev == nblocks - 1) {
+      A.counters[which] = 0u;
+      __threadfence_system();
+      for (int g = 0; g < A.n; ++g)
+        asm volatile("st.release.sys.global.u32 [%0], %1;\n" ::"l"(A.flags[g] + which * A.n + A.rank), "r"(A.epoch) : "memory");
+    }
+    for (int g = 0; g < A.n; ++g) {
+      unsigned have = 0, polls = 0;
+      for (;;) {
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];\n" : "=r"(have) : "l"(A.flags[A.rank] + which * A.n + g) : "memory");
+        if ((int)(have - A.epoch) >= 0) break;
+        __nanosleep(100);
+        if (++polls > (1u << 24)) __trap();            // a peer never arrived: fail loudly rather than hang
+      }
+    }
+  }
+  __syncthreads();
+}
+
+template <int VEC>
+__global__ void __launch_bounds__(kVecWarps * 32) softargmax_slab_fused_kernel(const __grid_constant__ SlabRegressArgs A, const float* __restrict__ depths,
+                                                                               int B, int D, int P, float* __restrict__ depth_out,
+                                                                               float* __restrict__ conf_out, long long* __restrict__ index_out,
+                                                                               float* __restrict__ eidx_out) {
+  __shared__ SoftState s_state[kVecWarps][32 * VEC];
+  const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int base = D / A.n, extra = D % A.n;
+  const int lo = A.rank * base + min(A.rank, extra), Dl = base + (A.rank < extra ? 1 : 0), Dmax = base + (extra ? 1 : 0);
+  const int tiles_p = (P + 32 * VEC - 1) / (32 * VEC), tiles = tiles_p * B;
+  const size_t BP = (size_t)B * P;
+  // phase 1
+  for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+    const int b = tile / tiles_p, tp = tile - b * tiles_p;
+    const int p = (tp * 32 + lane) * VEC;
+    SoftState st[VEC];
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) st[v] = SoftState{-INFINITY, 0.f, 0.f, 0.f};
+    if (p < P && Dl > 0) soft_accumulate<VEC>(A.cost[A.rank] + (size_t)b * Dmax * P + p, depths + (size_t)b * D + lo, Dl, (size_t)P, lo, g, st);
+    __syncthreads();
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) s_state[g][lane * VEC + v] = st[v];
+    __syncthreads();
+    const int j = threadIdx.x;
+    if (j < 32 * VEC) {
+      SoftState t = s_state[0][j];
+#pragma unroll
+      for (int k = 1; k < kVecWarps; ++k) soft_merge(t, s_state[k][j]);
+      const int pp = tp * 32 * VEC + j;
+      if (pp < P) {
+        const size_t o = (size_t)A.rank * 4 * BP + (size_t)b * P + pp;
+        for (int r = 0; r < A.n; ++r) {                // this rank's partial into every rank's buffer (NVLink stores)
+          float* q = A.parts[r] + o;
+          q[0] = t.m; q[BP] = t.Z; q[2 * BP] = t.A; q[3 * BP] = t.I;
+        }
+      }
+    }
+  }
+  slab_handshake(A, 0, gridDim.x);
+  // phase 2
+  const float* mine = A.parts[A.rank];
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < (long long)BP; i += (long long)gridDim.x * blockDim.x) {
+    SoftState t{-INFINITY, 0.f, 0.f, 0.f};
+    for (int r = 0; r < A.n; ++r) {
+      const float* q = mine + (size_t)r * 4 * BP + i;
+      // written by peers during this kernel: read past L1 (volatile)
+      const volatile float* qv = q;
+      SoftState o{qv[0], qv[BP], qv[2 * BP], qv[3 * BP]};
+      soft_merge(t, o);
+    }
+    const float depth = t.A / t.Z, eidx = t.I / t.Z;
+    if (depth_out) depth_out[i] = depth;
+    if (eidx_out) eidx_out[i] = eidx;
+    int idx = (int)eidx;
+    idx = idx < 0 ? 0 : (idx > D - 1 ? D - 1 : idx);
+    if (index_out) index_out[i] = idx;
+    if (conf_out) {
+      const int b = (int)(i / P), pp = (int)(i - (long long)b * P);
+      float acc = 0.f;
+#pragma unroll
+      for (int k = -1; k <= 2; ++k) {
+        const int dd = idx + k;
+        if (dd >= 0 && dd < D) {
+          // owner of plane dd: the first `extra` ranks hold base + 1 planes
+          const int cut = extra * (base + 1);
+          const int r = dd < cut ? dd / (base + 1) : extra + (dd - cut) / max(base, 1);
+          const int rlo = r * base + min(r, extra);
+          acc += expf(__ldg(A.cost[r] + ((size_t)b * Dmax + (dd - rlo)) * P + pp) - t.m);
+        }
+      }
+      conf_out[i] = acc / t.Z;
+    }
+  }
+  slab_handshake(A, 1, gridDim.x);
+}
+
 // merge G slab partials [G,4,B*P] -> merged [4,B*P] = (m, Z, depth, eidx)
 __global__ void softargmax_combine_kernel(const float* __restrict__ parts, int G, long long BP, float* __restrict__ merged) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -598,6 +810,18 @@ extern "C" int rmvd_mvs_regress_fwd(const float* cost, const float* depths, int 
   if (!cost || !depths) return RMVD_E_NULL;
   if (B <= 0 || D <= 0 || h <= 0 || w <= 0 || B > 65535) return RMVD_E_SHAPE;
   const int P = h * w;
+  if (!prob) {
+    if (P % 2 == 0) {
+      dim3 grid((P + 63) / 64, B);
+      mvs_regress_vec_kernel<2><<<grid, kVecWarps * 32, 0, (cudaStream_t)stream>>>(cost, depths, B, D, P, 0, 0, depth, confidence,
+                                                                                   (long long*)depth_index, expected_index, nullptr);
+    } else {
+      dim3 grid((P + 31) / 32, B);
+      mvs_regress_vec_kernel<1><<<grid, kVecWarps * 32, 0, (cudaStream_t)stream>>>(cost, depths, B, D, P, 0, 0, depth, confidence,
+                                                                                   (long long*)depth_index, expected_index, nullptr);
+    }
+    return (int)cudaGetLastError();
+  }
   dim3 grid((P + 31) / 32, B);
   mvs_regress_kernel<<<grid, kRegWarps * 32, 0, (cudaStream_t)stream>>>(cost, depths, B, D, P, 0, 0, depth, confidence,
                                                                         (long long*)depth_index, expected_index, prob,
@@ -610,10 +834,15 @@ extern "C" int rmvd_softargmax_partial(const float* cost_slab, const float* dept
   if (!cost_slab || !depths_slab || !partial) return RMVD_E_NULL;
   if (B <= 0 || Dl <= 0 || h <= 0 || w <= 0 || d_begin < 0 || B > 65535) return RMVD_E_SHAPE;
   const int P = h * w;
-  dim3 grid((P + 31) / 32, B);
-  mvs_regress_kernel<<<grid, kRegWarps * 32, 0, (cudaStream_t)stream>>>(cost_slab, depths_slab, B, Dl, P, d_begin, 1,
-                                                                        nullptr, nullptr, nullptr, nullptr, nullptr,
-                                                                        partial);
+  if (P % 2 == 0) {
+    dim3 grid((P + 63) / 64, B);
+    mvs_regress_vec_kernel<2><<<grid, kVecWarps * 32, 0, (cudaStream_t)stream>>>(cost_slab, depths_slab, B, Dl, P, d_begin, 1, nullptr, nullptr,
+                                                                                 nullptr, nullptr, partial);
+  } else {
+    dim3 grid((P + 31) / 32, B);
+    mvs_regress_vec_kernel<1><<<grid, kVecWarps * 32, 0, (cudaStream_t)stream>>>(cost_slab, depths_slab, B, Dl, P, d_begin, 1, nullptr, nullptr,
+                                                                                 nullptr, nullptr, partial);
+  }
   return (int)cudaGetLastError();
 }
 
@@ -632,6 +861,45 @@ extern "C" int rmvd_softargmax_confidence(const float* cost_slab, const float* m
   const int P = h * w;
   dim3 grid((P + 255) / 256, B);
   softargmax_confidence_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(cost_slab, merged, B, Dl, P, D, d_begin, conf_part);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int rmvd_softargmax_slab_fused(const float* const* cost_peers, const float* depths, int B, int D, int h, int w, int num_peers,
+                                          int rank, float* const* parts_peers, uint32_t* const* flag_peers, uint32_t epoch,
+                                          uint32_t* local_counters, float* depth, float* confidence, int64_t* depth_index,
+                                          float* expected_index, void* stream) {
+  if (!cost_peers || !depths || !parts_peers || !flag_peers || !local_counters) return RMVD_E_NULL;
+  if (B <= 0 || D <= 0 || h <= 0 || w <= 0) return RMVD_E_SHAPE;
+  if (num_peers < 1 || num_peers > RMVD_MAX_PEERS || rank < 0 || rank >= num_peers) return RMVD_E_RANGE;
+  SlabRegressArgs A{};
+  A.n = num_peers; A.rank = rank; A.epoch = epoch; A.counters = local_counters;
+  for (int g = 0; g < num_peers; ++g) {
+    if (!cost_peers[g] || !parts_peers[g] || !flag_peers[g]) return RMVD_E_NULL;
+    A.cost[g] = cost_peers[g]; A.parts[g] = parts_peers[g]; A.flags[g] = flag_peers[g];
+  }
+  const int P = h * w;
+  static int slots[2] = {0, 0};                        // resident CTAs of the two instantiations on this device
+  const int vi = (P % 2 == 0) ? 1 : 0;
+  if (!slots[vi]) {
+    int dev = 0, sms = 0, per_sm = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (e == cudaSuccess)
+      e = vi ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, softargmax_slab_fused_kernel<2>, kVecWarps * 32, 0)
+             : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, softargmax_slab_fused_kernel<1>, kVecWarps * 32, 0);
+    if (e != cudaSuccess) return (int)e;
+    slots[vi] = sms * per_sm;
+  }
+  const int VEC = vi ? 2 : 1;
+  const long long tiles = (long long)((P + 32 * VEC - 1) / (32 * VEC)) * B;
+  // every CTA waits inside the kernel for the other ranks: the grid must be resident as a whole (leave a quarter of the slots free)
+  const int grid = (int)(tiles < (long long)(slots[vi] * 3 / 4) ? tiles : (long long)(slots[vi] * 3 / 4));
+  if (vi)
+    softargmax_slab_fused_kernel<2><<<grid, kVecWarps * 32, 0, (cudaStream_t)stream>>>(A, depths, B, D, P, depth, confidence, (long long*)depth_index,
+                                                                                       expected_index);
+  else
+    softargmax_slab_fused_kernel<1><<<grid, kVecWarps * 32, 0, (cudaStream_t)stream>>>(A, depths, B, D, P, depth, confidence, (long long*)depth_index,
+                                                                                       expected_index);
   return (int)cudaGetLastError();
 }
 

@@ -366,19 +366,20 @@ extern "C" size_t rmvd_psweep_workspace_bytes(int N, int C, int h, int w, int V,
   return tot + 256;                                                                                  // work-item counter
 }
 
-extern "C" int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* feat_src, const float* intrinsics_key,
-                                    const float* const* intrinsics_src, const float* const* src_to_key,
-                                    const float* invdepths, const int64_t* inv_stride, int N, int C, int h, int w,
-                                    int V, const int* hs, const int* ws, int S, int s_begin, int s_end,
-                                    int normalize_mode, float* corr, float* mask, int out_S, int out_s0,
-                                    int32_t* dbg_ix0, int32_t* dbg_iy0, uint8_t* dbg_geom, void* workspace,
-                                    size_t workspace_bytes, void* stream) {
+static int psweep_corr_fwd_impl(const float* feat_key, const float* const* feat_src, const float* intrinsics_key,
+                                const float* const* intrinsics_src, const float* const* src_to_key,
+                                const float* invdepths, const int64_t* inv_stride, int N, int C, int h, int w,
+                                int V, const int* hs, const int* ws, int S, int s_begin, int s_end,
+                                int normalize_mode, float* corr, float* mask, int out_S, int out_s0,
+                                int32_t* dbg_ix0, int32_t* dbg_iy0, uint8_t* dbg_geom, void* workspace,
+                                size_t workspace_bytes, void* stream, const PsweepPeers* peers) {
   if (!feat_key || !feat_src || !intrinsics_key || !intrinsics_src || !src_to_key || !invdepths || !inv_stride ||
       !hs || !ws || !corr || !mask)
     return RMVD_E_NULL;
-  if (N <= 0 || C <= 0 || h <= 0 || w <= 0 || V <= 0 || S <= 0 || out_S <= 0) return RMVD_E_SHAPE;
+  if (N <= 0 || C <= 0 || h <= 0 || w <= 0 || V <= 0 || S <= 0 || out_S < 0) return RMVD_E_SHAPE;
   if (s_begin < 0 || s_end > S || s_begin > s_end || out_s0 < 0 || out_s0 + (s_end - s_begin) > out_S)
     return RMVD_E_RANGE;
+  if (out_S == 0 && (s_begin != s_end || peers)) return RMVD_E_SHAPE;   // an empty slab of a single-GPU call is a no-op (below)
   if (normalize_mode != RMVD_NORM_NONE && normalize_mode != RMVD_NORM_DIM && normalize_mode != RMVD_NORM_BEFORE)
     return RMVD_E_MODE;
   if ((dbg_ix0 == nullptr) != (dbg_iy0 == nullptr)) return RMVD_E_NULL;
@@ -387,7 +388,7 @@ extern "C" int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* f
     if (hs[v] <= 0 || ws[v] <= 0 || hs[v] >= 32768 || ws[v] >= 32768) return RMVD_E_SHAPE;
   }
   if (workspace_bytes < rmvd_psweep_workspace_bytes(N, C, h, w, V, hs, ws) || !workspace) return RMVD_E_WORKSPACE;
-  if (s_begin == s_end) return RMVD_OK;
+  if (s_begin == s_end && !peers) return RMVD_OK;     // (an empty slab of the peer mode still takes part in the handshake)
   cudaStream_t st = (cudaStream_t)stream;
 
   // kernel choice: tcgen05 kernel (C % 32 == 0, per-plane hypotheses) > banded fp32 kernel (C % 32 == 0, source map
@@ -406,6 +407,7 @@ extern "C" int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* f
     tc = tc && psweep_tc_eligible(T, 0);
     wsk = wsk && psweep_ws_eligible(T, 0) && (long long)N * (V < kMaxViews ? V : kMaxViews) <= 65535;
   }
+  if (peers && (!wsk || V > kMaxViews)) return RMVD_E_MODE;
 
   char* wsp = (char*)workspace;
   unsigned* counter = (unsigned*)(wsp + rmvd_psweep_workspace_bytes(N, C, h, w, V, hs, ws) - 256);
@@ -461,12 +463,44 @@ extern "C" int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* f
     A.N = N; A.C = C; A.h = h; A.w = w; A.S = S; A.s_begin = s_begin; A.s_end = s_end;
     A.norm = normalize_mode; A.out_S = out_S; A.out_s0 = out_s0; A.v0 = v0;
     A.corr = corr; A.mask = mask; A.dbg_ix0 = dbg_ix0; A.dbg_iy0 = dbg_iy0; A.dbg_geom = dbg_geom;
-    int rc = wsk ? launch_psweep_ws(A, key_nhwc, nv, counter, st)
+    int rc = wsk ? launch_psweep_ws(A, key_nhwc, nv, counter, peers, st)
                 : tc ? launch_psweep_tc(A, key_nhwc, nv, st)
                 : band ? launch_psweep_band(A, key_nhwc, nv, st) : dispatch_corr<false>(A, nv, st);
     if (rc) return rc;
   }
   return RMVD_OK;
+}
+
+extern "C" int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* feat_src, const float* intrinsics_key,
+                                    const float* const* intrinsics_src, const float* const* src_to_key,
+                                    const float* invdepths, const int64_t* inv_stride, int N, int C, int h, int w,
+                                    int V, const int* hs, const int* ws, int S, int s_begin, int s_end,
+                                    int normalize_mode, float* corr, float* mask, int out_S, int out_s0,
+                                    int32_t* dbg_ix0, int32_t* dbg_iy0, uint8_t* dbg_geom, void* workspace,
+                                    size_t workspace_bytes, void* stream) {
+  return psweep_corr_fwd_impl(feat_key, feat_src, intrinsics_key, intrinsics_src, src_to_key, invdepths, inv_stride, N, C, h, w, V, hs, ws,
+                              S, s_begin, s_end, normalize_mode, corr, mask, out_S, out_s0, dbg_ix0, dbg_iy0, dbg_geom, workspace,
+                              workspace_bytes, stream, nullptr);
+}
+
+extern "C" int rmvd_psweep_corr_fwd_peers(const float* feat_key, const float* const* feat_src, const float* intrinsics_key,
+                                          const float* const* intrinsics_src, const float* const* src_to_key,
+                                          const float* invdepths, const int64_t* inv_stride, int N, int C, int h, int w,
+                                          int V, const int* hs, const int* ws, int S, int s_begin, int s_end,
+                                          int normalize_mode, int out_S, int out_s0, int num_peers, int rank,
+                                          float* const* corr_peers, float* const* mask_peers, uint32_t* const* flag_peers,
+                                          uint32_t epoch, void* workspace, size_t workspace_bytes, void* stream) {
+  if (!corr_peers || !mask_peers || !flag_peers) return RMVD_E_NULL;
+  if (num_peers < 1 || num_peers > RMVD_MAX_PEERS || rank < 0 || rank >= num_peers) return RMVD_E_RANGE;
+  PsweepPeers P{};
+  P.n = num_peers; P.rank = rank; P.epoch = epoch;
+  for (int g = 0; g < num_peers; ++g) {
+    if (!corr_peers[g] || !mask_peers[g] || !flag_peers[g]) return RMVD_E_NULL;
+    P.corr[g] = corr_peers[g]; P.mask[g] = mask_peers[g]; P.flags[g] = flag_peers[g];
+  }
+  return psweep_corr_fwd_impl(feat_key, feat_src, intrinsics_key, intrinsics_src, src_to_key, invdepths, inv_stride, N, C, h, w, V, hs, ws,
+                              S, s_begin, s_end, normalize_mode, P.corr[rank], P.mask[rank], out_S, out_s0, nullptr, nullptr, nullptr,
+                              workspace, workspace_bytes, stream, &P);
 }
 
 extern "C" int rmvd_corr_grid_fwd(const float* feat_key, const float* feat_src, const float* grids,

@@ -52,6 +52,15 @@ int repack_key_tiles(const float* key, void* dst, int N, int C, int h, int w, in
 // `counter`: 4 bytes of device memory (the kernel's work-item counter), zeroed by the repack launch
 int repack_grouped_batch(const float* const* srcs, void* const* dsts, const int* hs, const int* ws, int count, int N, int C, int l2norm,
                          unsigned* counter, cudaStream_t st);
-int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, unsigned* counter, cudaStream_t st);
+// Depth-slab mode: the sampling loop stores every output row into the tensors of all ranks (peer-mapped pointers, own rank
+// included) and the kernel ends with a flag handshake between the ranks.
+struct PsweepPeers {
+  int n, rank;
+  float* corr[RMVD_MAX_PEERS]; float* mask[RMVD_MAX_PEERS];
+  unsigned* flags[RMVD_MAX_PEERS];
+  unsigned epoch;
+};
+// counter: 16 bytes of device memory: [0] work-item counter, [2] finished-CTA counter of the slab handshake
+int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, unsigned* counter, const PsweepPeers* peers, cudaStream_t st);
 
 }  // namespace rmvd

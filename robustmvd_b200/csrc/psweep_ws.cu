@@ -62,6 +62,16 @@ constexpr int kRegsControl = 64, kRegsConsumer = 104;   // setmaxnreg moves regi
 constexpr int kConsThreads = kConsWarps * 32;
 constexpr int kStep = kConsWarps / 2;        // planes between two sampling steps of a warp
 
+constexpr int kMaxPeers = RMVD_MAX_PEERS;
+struct PeerArgs {                  // depth-slab mode (n > 0): peer-mapped output tensors and the end-of-kernel handshake
+  int n, rank;
+  float* corr[kMaxPeers];          // [V,N,out_S,h,w] of every rank (symmetric memory), own rank included
+  float* mask[kMaxPeers];
+  unsigned* flags[kMaxPeers];      // every rank's flag array [n] (symmetric memory): slot r = last epoch rank r completed
+  unsigned epoch;                  // this call's epoch (monotone per communicator)
+  unsigned* done_ctas;             // local counter of finished CTAs
+};
+
 struct __align__(16) PlaneTerm { float ed, id, md, zs; };   // e*d, i*d, m*d, 1/d of one plane (planesweep_corr.py:334,343,492)
 // Texels [xa, xa + len) of one source row of the band; xa and len are multiples of 8.  G column of texel x = offp + x.
 struct __align__(16) RowSpan { int xa, lenm1, offp, len; };
@@ -89,8 +99,23 @@ struct WsConst {                   // per-launch constants of the out-of-line pa
   const float* G;
   int P, C, w;
   float inv_scale;
+  int npeers;                      // depth-slab mode: every output row also goes to the peers' tensors (NVLink stores)
+  float* pcorr[kMaxPeers]; float* pmask[kMaxPeers];
 };
 __shared__ WsConst s_k;
+
+// One output sample.  Single GPU: streaming stores.  Depth slabs over several GPUs (partition 1): the same value is
+// stored into the [V,N,S,h,w] tensor of every rank (own rank included) through the peer-mapped pointers, i.e. the all-gather of the
+// slabs happens row by row from inside the sampling loop instead of as a separate collective.
+template <bool kPeers>
+__device__ __forceinline__ void store_out(const WsConst& W, float* __restrict__ corr, float* __restrict__ mask, size_t o, float c, float m) {
+  if (!kPeers) {
+    __stcs(corr + o, c);                               // corr / mask: the caller's register copies of W.corr / W.mask
+    __stcs(mask + o, m);
+  } else {
+    for (int g = 0; g < W.npeers; ++g) { W.pcorr[g][o] = c; W.pmask[g][o] = m; }
+  }
+}
 
 // barrier slots
 constexpr int kBarFull = 0, kBarFree = kBarFull + kStages, kBarAcc = kBarFree + kStages, kBarDrained = kBarAcc + kNBuf,
@@ -215,7 +240,7 @@ __global__ void __launch_bounds__(256) nchw_to_grouped_kernel(const GroupBatch B
   __shared__ float tile[kRpCh][33];
   __shared__ float s_norm[32];
   const int which = blockIdx.z / N, n = blockIdx.z - which * N;
-  if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0) *B.counter = 0u;
+  if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0) { B.counter[0] = 0u; B.counter[2] = 0u; }
   const int hs = B.hs[which], ws = B.ws[which];
   const int wg = (ws + 7) >> 3, tpr = (wg + 3) >> 2;        // groups per row, 32-texel tiles per row
   if ((int)blockIdx.x >= tpr * hs) return;                   // maps of different sizes share the grid of the largest
@@ -926,6 +951,7 @@ __device__ float dot_thread(const ChunkDesc* D, int C, int slot, int y, int x) {
 }
 
 // One sample through the exact chain, evaluated and stored (about one sample in 10^3 of the filtered locate below).
+template <bool kPeers>
 __device__ __noinline__ void sample_slow(const ChunkDesc* D, int p, int pl, int slot) {
   const WsConst& K = s_k;
   const int hs = D->hs, ws = D->ws, R = D->R, C = K.C;
@@ -962,8 +988,7 @@ __device__ __noinline__ void sample_slow(const ChunkDesc* D, int p, int pl, int 
     val = (g_nw * L.nw + g_ne * L.ne + g_sw * L.sw + g_se * L.se) * K.inv_scale;
   }
   const size_t o = (size_t)D->out_base + (size_t)(D->out_plane0 + pl) * K.P + p;
-  K.corr[o] = val;
-  K.mask[o] = L.valid ? 1.f : 0.f;
+  store_out<kPeers>(K, K.corr, K.mask, o, val, L.valid ? 1.f : 0.f);
   if (K.dbg_ix0) {
     K.dbg_ix0[o] = L.x0;
     K.dbg_iy0[o] = L.y0;
@@ -1019,6 +1044,7 @@ __device__ __forceinline__ FastOut sample_fast(const RowSpan* __restrict__ rows,
 }
 
 // warp = 32 adjacent tile slots x one plane per step (one 128-byte row of corr and of mask), two planes in flight per thread
+template <bool kPeers>
 __device__ __forceinline__ void sample_chunk(const ChunkDesc* D, const float* G, const Pixel& px, int p, int cw, int lane) {
   if (p < 0) return;
   const WsConst& W = s_k;
@@ -1043,15 +1069,14 @@ __device__ __forceinline__ void sample_chunk(const ChunkDesc* D, const float* G,
   size_t o = (size_t)D->out_base + (size_t)(D->out_plane0 + (cw >> 1)) * W.P + p;
   auto emit = [&](size_t oo, int pl, const FastOut& r) {
     if (r.settled) {
-      __stcs(corr + oo, r.val);
-      __stcs(mask + oo, r.valid ? 1.f : 0.f);
+      store_out<kPeers>(W, corr, mask, oo, r.val, r.valid ? 1.f : 0.f);
       if (dix) {
         dix[oo] = min(max(r.xi, -2), ws);   // sat_index()
         W.dbg_iy0[oo] = min(max(r.yi, -2), hs);
         if (W.dbg_geom) W.dbg_geom[oo] = r.geom ? 1 : 0;
       }
     } else {
-      sample_slow(D, p, pl, slot);
+      sample_slow<kPeers>(D, p, pl, slot);
     }
   };
   const unsigned* dead = D->dead;
@@ -1064,7 +1089,7 @@ __device__ __forceinline__ void sample_chunk(const ChunkDesc* D, const float* G,
     for (int j = 0; j < kSU; ++j) all_dead = all_dead && is_dead(pl + j * kStep);
     if (all_dead) {                                      // warp-uniform
 #pragma unroll
-      for (int j = 0; j < kSU; ++j) { __stcs(corr + o + j * step, 0.f); __stcs(mask + o + j * step, 0.f); }
+      for (int j = 0; j < kSU; ++j) store_out<kPeers>(W, corr, mask, o + j * step, 0.f, 0.f);
       continue;
     }
     FastOut r[kSU];
@@ -1078,6 +1103,7 @@ __device__ __forceinline__ void sample_chunk(const ChunkDesc* D, const float* G,
 
 // Irregular chunk: every sample located with the reference chain of common.cuh and evaluated directly, the warp sharing each
 // valid sample's channel reduction.
+template <bool kPeers>
 __device__ void direct_chunk(const PsweepArgs& A, const ChunkDesc* D, int cw, int lane) {
   const WsConst& W = s_k;
   const int C = W.C, P = W.P, hs = D->hs, ws = D->ws, len = D->len, n = D->n;
@@ -1120,8 +1146,7 @@ __device__ void direct_chunk(const PsweepArgs& A, const ChunkDesc* D, int cw, in
     }
     if (p >= 0) {
       const size_t o = (size_t)D->out_base + (size_t)(D->out_plane0 + pl) * P + p;
-      W.corr[o] = valid ? res * W.inv_scale : 0.f;
-      W.mask[o] = valid ? 1.f : 0.f;
+      store_out<kPeers>(W, W.corr, W.mask, o, valid ? res * W.inv_scale : 0.f, valid ? 1.f : 0.f);
       if (W.dbg_ix0) {
         W.dbg_ix0[o] = x0;
         W.dbg_iy0[o] = y0;
@@ -1131,6 +1156,7 @@ __device__ void direct_chunk(const PsweepArgs& A, const ChunkDesc* D, int cw, in
   }
 }
 
+template <bool kPeers>
 __device__ void consumer(const PsweepArgs& A, ChunkDesc* descs, float* G, unsigned bars, unsigned tmem) {
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int cw = warp - 4, q = warp & 3, part = (warp >> 2) - 1;   // TMEM lane quadrant, which of its four warps
@@ -1224,8 +1250,8 @@ __device__ void consumer(const PsweepArgs& A, ChunkDesc* descs, float* G, unsign
     if (rec) atomicAdd(&g_ws_stats[21], (unsigned long long)(clock64() - b2_t0));
     const long long sm_t0 = clock64();
 #endif
-    if (kind == kGemm) sample_chunk(D, G, px, p, cw, lane);
-    else direct_chunk(A, D, cw, lane);
+    if (kind == kGemm) sample_chunk<kPeers>(D, G, px, p, cw, lane);
+    else direct_chunk<kPeers>(A, D, cw, lane);
     __syncwarp();
 #ifdef RMVD_WS_STATS
     if (rec) atomicAdd(&g_ws_stats[22], (unsigned long long)(clock64() - sm_t0));
@@ -1237,8 +1263,10 @@ __device__ void consumer(const PsweepArgs& A, ChunkDesc* descs, float* G, unsign
 #endif
 }
 
+template <bool kPeers>
 __global__ void __launch_bounds__(kThreads, 1) psweep_ws_kernel(const PsweepArgs A, const __nv_bfloat16* __restrict__ key_split, int tw,
-                                                                int th, int tiles_x, int tiles, int items, unsigned* counter) {
+                                                                int th, int tiles_x, int tiles, int items, unsigned* counter,
+                                                                const __grid_constant__ PeerArgs PA) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ unsigned s_tmem;
   unsigned char* stage = smem_raw + ((1024 - (smem_u32(smem_raw) & 1023)) & 1023);
@@ -1265,6 +1293,8 @@ __global__ void __launch_bounds__(kThreads, 1) psweep_ws_kernel(const PsweepArgs
     s_k.corr = A.corr; s_k.mask = A.mask; s_k.dbg_ix0 = A.dbg_ix0; s_k.dbg_iy0 = A.dbg_iy0; s_k.dbg_geom = A.dbg_geom;
     s_k.G = G; s_k.P = A.h * A.w; s_k.C = A.C; s_k.w = A.w;
     s_k.inv_scale = (A.norm == RMVD_NORM_DIM) ? 1.0f / sqrtf((float)A.C) : 1.0f;    // corr / sqrt(C), :178-179
+    s_k.npeers = PA.n;
+    for (int g = 0; g < kMaxPeers; ++g) { s_k.pcorr[g] = PA.corr[g]; s_k.pmask[g] = PA.mask[g]; }
   }
   asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
   __syncthreads();
@@ -1284,12 +1314,33 @@ __global__ void __launch_bounds__(kThreads, 1) psweep_ws_kernel(const PsweepArgs
     }
   } else {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" ::"n"(kRegsConsumer));
-    consumer(A, descs, G, bars, tmem);
+    consumer<kPeers>(A, descs, G, bars, tmem);
   }
 
+  if (kPeers) __threadfence_system();                // this thread's peer stores are ordered before the handshake below
   asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
   __syncthreads();
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem), "r"(kTmemCols));
+  if (kPeers && t == 0) {
+    // End-of-kernel handshake of the depth-slab mode: the last CTA of this rank publishes the call's epoch in every rank's flag
+    // array and waits until all ranks have published theirs, so that when this kernel completes, every rank's rows have landed
+    // in this rank's tensors (no separate barrier or collective launch).
+    const unsigned prev = atomicAdd(PA.done_ctas, 1u);
+    if (prev == gridDim.x - 1) {
+      *PA.done_ctas = 0u;                              // next launch (stream order)
+      __threadfence_system();
+      for (int g = 0; g < PA.n; ++g) asm volatile("st.release.sys.global.u32 [%0], %1;\n" ::"l"(PA.flags[g] + PA.rank), "r"(PA.epoch) : "memory");
+      for (int g = 0; g < PA.n; ++g) {
+        unsigned have = 0, polls = 0;
+        for (;;) {
+          asm volatile("ld.acquire.sys.global.u32 %0, [%1];\n" : "=r"(have) : "l"(PA.flags[PA.rank] + g) : "memory");
+          if ((int)(have - PA.epoch) >= 0) break;
+          __nanosleep(200);
+          if (++polls > (1u << 24)) __trap();         // a peer never arrived (several seconds): fail loudly rather than hang
+        }
+      }
+    }
+  }
 }
 
 static size_t smem_bytes() {
@@ -1380,14 +1431,15 @@ int repack_grouped_batch(const float* const* srcs, void* const* dsts, const int*
   return (int)cudaGetLastError();
 }
 
-int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, unsigned* counter, cudaStream_t st) {
+int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, unsigned* counter, const PsweepPeers* peers, cudaStream_t st) {
   static int num_sms = 0;
   static bool attr_set = false;
   if (!attr_set) {
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(ws::psweep_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws::smem_bytes());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(ws::psweep_ws_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws::smem_bytes());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(ws::psweep_ws_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws::smem_bytes());
     if (e != cudaSuccess) return (int)e;
     attr_set = true;
   }
@@ -1399,14 +1451,24 @@ int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, uns
   if (items_ll > 0x7fff0000LL) return (int)cudaErrorInvalidValue;
   const int items = (int)items_ll;
   const unsigned grid = (unsigned)(items < num_sms ? items : num_sms);
+  ws::PeerArgs PA{};
+  if (peers && peers->n > 0) {
+    if (peers->n > ws::kMaxPeers || peers->rank < 0 || peers->rank >= peers->n || A.dbg_ix0) return (int)cudaErrorInvalidValue;
+    PA.n = peers->n; PA.rank = peers->rank; PA.epoch = peers->epoch; PA.done_ctas = counter + 2;
+    for (int g = 0; g < peers->n; ++g) { PA.corr[g] = peers->corr[g]; PA.mask[g] = peers->mask[g]; PA.flags[g] = peers->flags[g]; }
+  }
 #ifdef RMVD_WS_STATS
   {
     unsigned long long z[32] = {0};
     cudaMemcpyToSymbolAsync(ws::g_ws_stats, z, sizeof(z), 0, cudaMemcpyHostToDevice, st);
   }
 #endif
-  ws::psweep_ws_kernel<<<grid, ws::kThreads, ws::smem_bytes(), st>>>(A, reinterpret_cast<const __nv_bfloat16*>(key_split), tw, th, tiles_x, tiles,
-                                                                     items, counter);
+  if (PA.n > 0)
+    ws::psweep_ws_kernel<true><<<grid, ws::kThreads, ws::smem_bytes(), st>>>(A, reinterpret_cast<const __nv_bfloat16*>(key_split), tw, th, tiles_x,
+                                                                             tiles, items, counter, PA);
+  else
+    ws::psweep_ws_kernel<false><<<grid, ws::kThreads, ws::smem_bytes(), st>>>(A, reinterpret_cast<const __nv_bfloat16*>(key_split), tw, th, tiles_x,
+                                                                              tiles, items, counter, PA);
 #ifdef RMVD_WS_STATS
   {
     unsigned long long h[32];

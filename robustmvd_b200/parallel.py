@@ -75,6 +75,116 @@ def planesweep_correlation_slabs(block, group=None, gather=True, **kwargs):
     return corrs, masks, inv
 
 
+class SlabGather:
+    """Depth slabs with the gather fused into the plane-sweep kernel (partition 1).
+
+    Every rank holds symmetric ``[2, V, N, S, h, w]`` output buffers (``torch.distributed._symmetric_memory``: peer-mapped over
+    NVLink / NVSwitch).  A call computes this rank's planes ``slab_range(S, G, rank)`` and its sampling loop stores each corr / mask
+    row into the buffers of ALL ranks; the kernel ends with a flag handshake between the ranks (``rmvd_psweep_corr_fwd_peers``), so
+    one launch sequence per rank replaces "slab kernel + stack / movedim / contiguous + NCCL all-gather + cat".  Two buffer sets
+    alternate between consecutive calls: a rank that runs ahead writes set ``(k + 1) % 2`` while a slower rank still reads set
+    ``k % 2``, and cannot start call ``k + 2`` before the slower rank has finished call ``k + 1`` (the handshake).
+
+    Returns ``(corrs, masks, sampling_invdepths)`` with full ``[N,S,h,w]`` volumes per view, views of the current buffer set: valid
+    until the call after next.  Falls back to ``planesweep_correlation_slabs`` (NCCL / gloo all-gather) when symmetric memory is
+    not available (``mode == "all_gather"``), e.g. in the CPU tests of the host logic.
+    """
+
+    def __init__(self, block, V, N, S, h, w, device, group=None):
+        self.block, self.group = block, group
+        self.G, self.rank = _world(group)
+        self.S = S
+        self.epoch = 0
+        self.mode = "all_gather"
+        self.bufs = None
+        if torch.device(device).type == "cuda" and self.G > 1 and self.G <= 8:
+            try:
+                import torch.distributed._symmetric_memory as symm
+                grp = group if group is not None else dist.group.WORLD
+                self.bufs, self.hdls = [], []
+                for _ in range(2):
+                    t = symm.empty((2, V, N, S, h, w), dtype=torch.float32, device=device)
+                    self.bufs.append(t)
+                    self.hdls.append(symm.rendezvous(t, grp))
+                self.flags = symm.empty((64,), dtype=torch.int32, device=device)
+                self.flags.zero_()
+                self.fh = symm.rendezvous(self.flags, grp)
+                torch.cuda.synchronize(device)
+                self.fh.barrier(channel=0)           # every rank's flags are zero before anyone's first epoch arrives
+                torch.cuda.synchronize(device)
+                self.mode = "peer_stores"
+            except Exception as e:  # noqa: BLE001
+                self.bufs = None
+                self.why = repr(e)
+
+    def __call__(self, **kwargs):
+        if self.mode != "peer_stores":
+            return planesweep_correlation_slabs(self.block, self.group, **kwargs)
+        self.epoch += 1
+        k = self.epoch % 2
+        buf, hdl = self.bufs[k], self.hdls[k]
+        half = buf[0].numel() * 4                   # bytes of the corr half of a buffer; the mask half follows it
+        peers = dict(rank=self.rank, epoch=self.epoch, corr=[int(p) for p in hdl.buffer_ptrs],
+                     mask=[int(p) + half for p in hdl.buffer_ptrs], flags=[int(p) for p in self.fh.buffer_ptrs])
+        lo, hi = slab_range(self.S, self.G, self.rank)
+        _, _, inv = self.block._forward_impl(plane_range=(lo, hi), peers=peers, **kwargs)
+        return list(buf[0].unbind(0)), list(buf[1].unbind(0)), inv
+
+
+class SlabRegress:
+    """``mvs_regress`` with D sharded over the ranks as ONE kernel per rank (``rmvd_softargmax_slab_fused``): partials into every
+    rank's buffer by peer stores, in-kernel handshake, merge, confidence from peer loads -- no NCCL call.  ``self.cost`` is this
+    rank's symmetric slab buffer ``[B, Dl_max, h, w]``: an upstream producer may write its slab there directly; ``__call__`` copies
+    a given ``cost_slab`` into it first.  Falls back to ``mvs_regress_slabs`` when symmetric memory is unavailable."""
+
+    def __init__(self, B, D, h, w, device, group=None):
+        self.group = group
+        self.G, self.rank = _world(group)
+        self.B, self.D, self.h, self.w = B, D, h, w
+        self.lo, self.hi = slab_range(D, self.G, self.rank)
+        self.epoch = 0
+        self.mode = "all_gather"
+        if torch.device(device).type == "cuda" and 1 < self.G <= 8:
+            try:
+                import torch.distributed._symmetric_memory as symm
+                grp = group if group is not None else dist.group.WORLD
+                dmax = -(-D // self.G)
+                self.cost = symm.empty((B, dmax, h, w), dtype=torch.float32, device=device)
+                self.parts = symm.empty((self.G, 4, B, h, w), dtype=torch.float32, device=device)
+                self.flags = symm.empty((64,), dtype=torch.int32, device=device)
+                self.flags.zero_()
+                self.hc, self.hp, self.hf = (symm.rendezvous(t, grp) for t in (self.cost, self.parts, self.flags))
+                self.counters = torch.zeros(2, dtype=torch.int32, device=device)
+                torch.cuda.synchronize(device)
+                self.hf.barrier(channel=0)
+                torch.cuda.synchronize(device)
+                self.mode = "fused_kernel"
+            except Exception as e:  # noqa: BLE001
+                self.why = repr(e)
+
+    def __call__(self, cost_slab, depth_values):
+        """cost_slab ``[B, hi - lo, h, w]`` (or None: already in ``self.cost``), depth_values ``[B, D]`` (all planes)."""
+        if self.mode != "fused_kernel":
+            return mvs_regress_slabs(cost_slab, depth_values[:, self.lo:self.hi].contiguous(), self.lo, self.D, self.group)
+        from . import _lib
+        lib = _lib.load()
+        dev = self.cost.device
+        if cost_slab is not None:
+            self.cost[:, : self.hi - self.lo].copy_(cost_slab)
+        self.epoch += 1
+        depth = torch.empty((self.B, self.h, self.w), dtype=torch.float32, device=dev)
+        conf = torch.empty_like(depth)
+        eidx = torch.empty_like(depth)
+        didx = torch.empty((self.B, self.h, self.w), dtype=torch.int64, device=dev)
+        dv = depth_values.detach().to(torch.float32).contiguous()
+        st = lib.rmvd_softargmax_slab_fused(
+            _lib.raw_ptr_array(self.hc.buffer_ptrs), _lib.ptr(dv), self.B, self.D, self.h, self.w, self.G, self.rank,
+            _lib.raw_ptr_array(self.hp.buffer_ptrs), _lib.raw_ptr_array(self.hf.buffer_ptrs), self.epoch, _lib.ptr(self.counters),
+            _lib.ptr(depth), _lib.ptr(conf), _lib.ptr(didx), _lib.ptr(eidx), _lib.stream_ptr())
+        _lib.check(st, "rmvd_softargmax_slab_fused")
+        return dict(depth=depth, confidence=conf, depth_index=didx, expected_index=eidx)
+
+
 def mvs_variance_slabs(feats, proj_mats, depth_values, group=None, gather=False, variance_fn=None):
     """MVSNet variance volume with D partitioned: returns this rank's ``[B,C,Dl,h,w]`` slab and its ``(lo, hi)``,
     or the gathered full volume when ``gather=True``."""

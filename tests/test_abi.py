@@ -32,7 +32,7 @@ def test_header_and_binding_agree():
 def test_every_declared_symbol_is_exported(lib):
     for name in declared_functions():
         assert hasattr(lib, name), name
-    assert lib.rmvd_abi_version() == 1
+    assert lib.rmvd_abi_version() == _lib.ABI_VERSION == int(re.search(r"#define RMVD_ABI_VERSION (\d+)", open(HEADER).read()).group(1))
 
 
 def test_only_sm100a_code_is_embedded():

@@ -1,9 +1,9 @@
 """Load the UNMODIFIED reference hot-path files from /root/reference in isolation.
 
-Container-only tooling (``/root/reference`` does not exist on the GPU box): used by
-``tools/make_golden.py`` to freeze golden vectors under ``tests/golden/`` and by
-``tools/validate_oracle.py`` to pin ``oracle/`` against the reference code itself.
-Nothing in ``tests/``, ``bench.py`` or the product imports this module at run time.
+Used by ``tools/make_golden.py`` to freeze golden vectors under ``tests/golden/``, by ``tools/validate_oracle.py`` to pin
+``oracle/`` against the reference code itself (both in the build container, where ``/root/reference`` exists), and by the
+CPU baseline legs of ``bench.py`` (``cpu_baseline`` / ``--impl reference``), which on the GPU box find the same two files
+under ``oracle/_ref/`` (``oracle/make_ref.py``).  Nothing in ``tests/`` or the product imports this module.
 
 Route A of SURVEY.md section 8(c): stub ``rmvd.utils.to_torch`` and
 ``kornia.utils.create_meshgrid``, then ``importlib`` the two files as they lie.
@@ -15,7 +15,16 @@ import types
 import numpy as np
 import torch
 
-REF_ROOT = "/root/reference"
+import os
+
+# The reference tree where it lies (build container), else the two hot-path files that oracle/make_ref.py copied, unmodified, into
+# the git-ignored oracle/_ref/ (they travel to the GPU box with the snapshot; only bench.py's CPU baseline legs load them there).
+_LOCAL = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref")
+REF_ROOT = "/root/reference" if os.path.isdir("/root/reference/rmvd") else _LOCAL
+
+
+def available():
+    return os.path.exists(os.path.join(REF_ROOT, "rmvd", "models", "blocks", "planesweep_corr.py"))
 
 
 def _to_torch(x, device=None):
