@@ -45,12 +45,18 @@ constexpr int kPx = 64;                      // key pixels per tile (A' has 2 * 
 constexpr int kNT = 128;                     // band texels per pass = N of one MMA = columns of one accumulator
 constexpr int kNBuf = 3;                     // accumulators: a whole chunk (<= 3 passes) can sit in TMEM
 constexpr int kKC = 32;                      // channels per stage
-constexpr int kStages = 6;                   // ring of B' stages
+#ifndef WS_STAGES
+#define WS_STAGES 4
+#endif
+#ifndef WS_RMAX
+#define WS_RMAX 512
+#endif
+constexpr int kStages = WS_STAGES;           // ring of B' stages
 constexpr int kStageBytes = kNT * 128;       // 16 KB: 128 texels x [hi 32 ch | lo 32 ch] bf16
 constexpr int kMaxC = 256;                   // A' in TMEM: C / 2 columns
 constexpr int kTmemA = kNBuf * kNT;          // TMEM columns: D = [0, 384), A' = [384, 384 + C / 2)
 constexpr int kTmemCols = 512;
-constexpr int kRMax = kNBuf * kNT;           // band capacity of one chunk (G columns)
+constexpr int kRMax = WS_RMAX;               // band capacity of one chunk (G columns), <= kNBuf * kNT
 constexpr int kGPitch = kRMax + 2;           // 2 (mod 32): conflict-free sampling reads and drain stores (see psweep_tc.cu)
 static_assert(kGPitch % 32 == 2, "G pitch must be 2 mod 32");
 constexpr int kMaxRows = 64;                 // source rows a band may span
@@ -77,6 +83,7 @@ struct __align__(16) PlaneTerm { float ed, id, md, zs; };   // e*d, i*d, m*d, 1/
 struct __align__(16) RowSpan { int xa, lenm1, offp, len; };
 
 enum { kStop = 0, kGemm = 1, kDirect = 2 };
+enum { kModePlain = 0, kModePeers = 1, kModeDebug = 2 };   // kernel variants: outputs only / + peer stores (depth slabs) / + debug outputs
 
 struct __align__(16) ChunkDesc {
   RowSpan rows[kMaxRows];
@@ -107,13 +114,15 @@ __shared__ WsConst s_k;
 // One output sample.  Single GPU: streaming stores.  Depth slabs over several GPUs (partition 1): the same value is
 // stored into the [V,N,S,h,w] tensor of every rank (own rank included) through the peer-mapped pointers, i.e. the all-gather of the
 // slabs happens row by row from inside the sampling loop instead of as a separate collective.
-template <bool kPeers>
-__device__ __forceinline__ void store_out(const WsConst& W, float* __restrict__ corr, float* __restrict__ mask, size_t o, float c, float m) {
-  if (!kPeers) {
-    __stcs(corr + o, c);                               // corr / mask: the caller's register copies of W.corr / W.mask
+// corr / mask: the caller's register copies of W.corr / W.mask, already advanced by `base` elements; o: offset from there
+template <int kMode, typename Off>
+__device__ __forceinline__ void store_out(const WsConst& W, float* __restrict__ corr, float* __restrict__ mask, size_t base, Off o, float c,
+                                          float m) {
+  if (kMode != kModePeers) {
+    __stcs(corr + o, c);
     __stcs(mask + o, m);
   } else {
-    for (int g = 0; g < W.npeers; ++g) { W.pcorr[g][o] = c; W.pmask[g][o] = m; }
+    for (int g = 0; g < W.npeers; ++g) { W.pcorr[g][base + o] = c; W.pmask[g][base + o] = m; }
   }
 }
 
@@ -951,7 +960,7 @@ __device__ float dot_thread(const ChunkDesc* D, int C, int slot, int y, int x) {
 }
 
 // One sample through the exact chain, evaluated and stored (about one sample in 10^3 of the filtered locate below).
-template <bool kPeers>
+template <int kMode>
 __device__ __noinline__ void sample_slow(const ChunkDesc* D, int p, int pl, int slot) {
   const WsConst& K = s_k;
   const int hs = D->hs, ws = D->ws, R = D->R, C = K.C;
@@ -988,8 +997,8 @@ __device__ __noinline__ void sample_slow(const ChunkDesc* D, int p, int pl, int 
     val = (g_nw * L.nw + g_ne * L.ne + g_sw * L.sw + g_se * L.se) * K.inv_scale;
   }
   const size_t o = (size_t)D->out_base + (size_t)(D->out_plane0 + pl) * K.P + p;
-  store_out<kPeers>(K, K.corr, K.mask, o, val, L.valid ? 1.f : 0.f);
-  if (K.dbg_ix0) {
+  store_out<kMode>(K, K.corr, K.mask, (size_t)0, o, val, L.valid ? 1.f : 0.f);
+  if (kMode == kModeDebug) {
     K.dbg_ix0[o] = L.x0;
     K.dbg_iy0[o] = L.y0;
     if (K.dbg_geom) K.dbg_geom[o] = L.geom ? 1 : 0;
@@ -1006,8 +1015,8 @@ __device__ __noinline__ void sample_slow(const ChunkDesc* D, int p, int pl, int 
 struct FastConst {
   float u_h, v_h, k_h;
   float sg, zp;           // visibility in the source as one compare: zs * sg > zp (planesweep_corr.py:500-504)
-  float eps_x, eps_y;     // trust margin of an interior floor
-  float epb_x, epb_y;     // trust margin where a corner column / row is outside the map (covers the 0.9999 threshold)
+  float tin_x, tin_y;     // 0.5 - trust margin of an interior floor: trusted iff |frac - 0.5| < this
+  float tout_x, tout_y;   // the same where a corner column / row is outside the map (margin covers the 0.9999 threshold)
   int ymin, Hm1;
   unsigned wsm1, hsm1;
 };
@@ -1025,8 +1034,8 @@ __device__ __forceinline__ FastOut sample_fast(const RowSpan* __restrict__ rows,
   const float fx = ix - floorf(ix), fy = iy - floorf(iy);        // exact
   o.xi = __float2int_rd(ix); o.yi = __float2int_rd(iy);          // saturating; nan -> 0
   const bool int_x = (unsigned)o.xi < K.wsm1, int_y = (unsigned)o.yi < K.hsm1;
-  const bool trust_x = fminf(fx, 1.0f - fx) > (int_x ? K.eps_x : K.epb_x);   // false for nan
-  const bool trust_y = fminf(fy, 1.0f - fy) > (int_y ? K.eps_y : K.epb_y);
+  const bool trust_x = fabsf(fx - 0.5f) < (int_x ? K.tin_x : K.tout_x);      // frac further than the margin from 0 and 1; false for nan
+  const bool trust_y = fabsf(fy - 0.5f) < (int_y ? K.tin_y : K.tout_y);
   o.valid = o.geom && int_x && int_y;
   const int h0 = o.yi - K.ymin;
   const bool rows_ok = (unsigned)h0 < (unsigned)K.Hm1;
@@ -1044,7 +1053,7 @@ __device__ __forceinline__ FastOut sample_fast(const RowSpan* __restrict__ rows,
 }
 
 // warp = 32 adjacent tile slots x one plane per step (one 128-byte row of corr and of mask), two planes in flight per thread
-template <bool kPeers>
+template <int kMode>
 __device__ __forceinline__ void sample_chunk(const ChunkDesc* D, const float* G, const Pixel& px, int p, int cw, int lane) {
   if (p < 0) return;
   const WsConst& W = s_k;
@@ -1055,33 +1064,37 @@ __device__ __forceinline__ void sample_chunk(const ChunkDesc* D, const float* G,
   K.u_h = px.u_h; K.v_h = px.v_h; K.k_h = px.k_h;
   K.sg = (px.mode == 2) ? -1.0f : 1.0f;
   K.zp = (px.mode == 1) ? px.z_pole : (px.mode == 2) ? -px.z_pole : (px.mode == 3) ? -INFINITY : INFINITY;
-  K.eps_x = kU * (16.0f * (float)ws + 64.0f); K.eps_y = kU * (16.0f * (float)hs + 64.0f);
-  K.epb_x = K.eps_x + 1.2e-4f; K.epb_y = K.eps_y + 1.2e-4f;
+  {
+    const float eps_x = kU * (16.0f * (float)ws + 64.0f), eps_y = kU * (16.0f * (float)hs + 64.0f);
+    K.tin_x = 0.5f - eps_x; K.tin_y = 0.5f - eps_y;
+    K.tout_x = K.tin_x - 1.2e-4f; K.tout_y = K.tin_y - 1.2e-4f;
+  }
   K.ymin = D->ymin; K.Hm1 = max(D->H - 1, 0);
   K.wsm1 = (unsigned)(ws - 1); K.hsm1 = (unsigned)(hs - 1);
   const int slot = (cw & 1) * 32 + lane;
   const float* g = G + slot * kGPitch;
   const RowSpan* rows = D->rows;
   const PlaneTerm* planes = D->planes;
-  float* const corr = W.corr; float* const mask = W.mask;
-  int32_t* const dix = W.dbg_ix0;
-  const size_t step = (size_t)kStep * W.P;
-  size_t o = (size_t)D->out_base + (size_t)(D->out_plane0 + (cw >> 1)) * W.P + p;
-  auto emit = [&](size_t oo, int pl, const FastOut& r) {
+  // outputs of this chunk: 64-bit bases (plane 0 of the chunk, this thread's pixel) + 32-bit element offsets
+  const size_t base = (size_t)D->out_base + (size_t)D->out_plane0 * W.P + p;
+  float* const corr = W.corr + base; float* const mask = W.mask + base;
+  const unsigned P = (unsigned)W.P, step = (unsigned)kStep * P;
+  auto emit = [&](unsigned oo, int pl, const FastOut& r) {
     if (r.settled) {
-      store_out<kPeers>(W, corr, mask, oo, r.val, r.valid ? 1.f : 0.f);
-      if (dix) {
-        dix[oo] = min(max(r.xi, -2), ws);   // sat_index()
-        W.dbg_iy0[oo] = min(max(r.yi, -2), hs);
-        if (W.dbg_geom) W.dbg_geom[oo] = r.geom ? 1 : 0;
+      store_out<kMode>(W, corr, mask, base, oo, r.val, r.valid ? 1.f : 0.f);
+      if (kMode == kModeDebug) {
+        W.dbg_ix0[base + oo] = min(max(r.xi, -2), ws);   // sat_index()
+        W.dbg_iy0[base + oo] = min(max(r.yi, -2), hs);
+        if (W.dbg_geom) W.dbg_geom[base + oo] = r.geom ? 1 : 0;
       }
     } else {
-      sample_slow<kPeers>(D, p, pl, slot);
+      sample_slow<kMode>(D, p, pl, slot);
     }
   };
   const unsigned* dead = D->dead;
   auto is_dead = [&](int q) { return (dead[q >> 5] >> (q & 31)) & 1u; };
   int pl = cw >> 1;
+  unsigned o = (unsigned)pl * P;
   constexpr int kSU = 2;                                 // samples in flight per thread
   for (; pl + (kSU - 1) * kStep < len; pl += kSU * kStep, o += kSU * step) {
     bool all_dead = true;
@@ -1089,7 +1102,7 @@ __device__ __forceinline__ void sample_chunk(const ChunkDesc* D, const float* G,
     for (int j = 0; j < kSU; ++j) all_dead = all_dead && is_dead(pl + j * kStep);
     if (all_dead) {                                      // warp-uniform
 #pragma unroll
-      for (int j = 0; j < kSU; ++j) store_out<kPeers>(W, corr, mask, o + j * step, 0.f, 0.f);
+      for (int j = 0; j < kSU; ++j) store_out<kMode>(W, corr, mask, base, o + j * step, 0.f, 0.f);
       continue;
     }
     FastOut r[kSU];
@@ -1103,7 +1116,7 @@ __device__ __forceinline__ void sample_chunk(const ChunkDesc* D, const float* G,
 
 // Irregular chunk: every sample located with the reference chain of common.cuh and evaluated directly, the warp sharing each
 // valid sample's channel reduction.
-template <bool kPeers>
+template <int kMode>
 __device__ void direct_chunk(const PsweepArgs& A, const ChunkDesc* D, int cw, int lane) {
   const WsConst& W = s_k;
   const int C = W.C, P = W.P, hs = D->hs, ws = D->ws, len = D->len, n = D->n;
@@ -1146,8 +1159,8 @@ __device__ void direct_chunk(const PsweepArgs& A, const ChunkDesc* D, int cw, in
     }
     if (p >= 0) {
       const size_t o = (size_t)D->out_base + (size_t)(D->out_plane0 + pl) * P + p;
-      store_out<kPeers>(W, W.corr, W.mask, o, valid ? res * W.inv_scale : 0.f, valid ? 1.f : 0.f);
-      if (W.dbg_ix0) {
+      store_out<kMode>(W, W.corr, W.mask, (size_t)0, o, valid ? res * W.inv_scale : 0.f, valid ? 1.f : 0.f);
+      if (kMode == kModeDebug) {
         W.dbg_ix0[o] = x0;
         W.dbg_iy0[o] = y0;
         if (W.dbg_geom) W.dbg_geom[o] = geom ? 1 : 0;
@@ -1156,7 +1169,7 @@ __device__ void direct_chunk(const PsweepArgs& A, const ChunkDesc* D, int cw, in
   }
 }
 
-template <bool kPeers>
+template <int kMode>
 __device__ void consumer(const PsweepArgs& A, ChunkDesc* descs, float* G, unsigned bars, unsigned tmem) {
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int cw = warp - 4, q = warp & 3, part = (warp >> 2) - 1;   // TMEM lane quadrant, which of its four warps
@@ -1250,8 +1263,8 @@ __device__ void consumer(const PsweepArgs& A, ChunkDesc* descs, float* G, unsign
     if (rec) atomicAdd(&g_ws_stats[21], (unsigned long long)(clock64() - b2_t0));
     const long long sm_t0 = clock64();
 #endif
-    if (kind == kGemm) sample_chunk<kPeers>(D, G, px, p, cw, lane);
-    else direct_chunk<kPeers>(A, D, cw, lane);
+    if (kind == kGemm) sample_chunk<kMode>(D, G, px, p, cw, lane);
+    else direct_chunk<kMode>(A, D, cw, lane);
     __syncwarp();
 #ifdef RMVD_WS_STATS
     if (rec) atomicAdd(&g_ws_stats[22], (unsigned long long)(clock64() - sm_t0));
@@ -1263,7 +1276,7 @@ __device__ void consumer(const PsweepArgs& A, ChunkDesc* descs, float* G, unsign
 #endif
 }
 
-template <bool kPeers>
+template <int kMode>
 __global__ void __launch_bounds__(kThreads, 1) psweep_ws_kernel(const PsweepArgs A, const __nv_bfloat16* __restrict__ key_split, int tw,
                                                                 int th, int tiles_x, int tiles, int items, unsigned* counter,
                                                                 const __grid_constant__ PeerArgs PA) {
@@ -1314,14 +1327,14 @@ __global__ void __launch_bounds__(kThreads, 1) psweep_ws_kernel(const PsweepArgs
     }
   } else {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" ::"n"(kRegsConsumer));
-    consumer<kPeers>(A, descs, G, bars, tmem);
+    consumer<kMode>(A, descs, G, bars, tmem);
   }
 
-  if (kPeers) __threadfence_system();                // this thread's peer stores are ordered before the handshake below
+  if (kMode == kModePeers) __threadfence_system();                // this thread's peer stores are ordered before the handshake below
   asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
   __syncthreads();
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem), "r"(kTmemCols));
-  if (kPeers && t == 0) {
+  if (kMode == kModePeers && t == 0) {
     // End-of-kernel handshake of the depth-slab mode: the last CTA of this rank publishes the call's epoch in every rank's flag
     // array and waits until all ranks have published theirs, so that when this kernel completes, every rank's rows have landed
     // in this rank's tensors (no separate barrier or collective launch).
@@ -1438,8 +1451,9 @@ int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, uns
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(ws::psweep_ws_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws::smem_bytes());
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(ws::psweep_ws_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws::smem_bytes());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(ws::psweep_ws_kernel<ws::kModePlain>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws::smem_bytes());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(ws::psweep_ws_kernel<ws::kModePeers>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws::smem_bytes());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(ws::psweep_ws_kernel<ws::kModeDebug>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws::smem_bytes());
     if (e != cudaSuccess) return (int)e;
     attr_set = true;
   }
@@ -1463,12 +1477,13 @@ int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, uns
     cudaMemcpyToSymbolAsync(ws::g_ws_stats, z, sizeof(z), 0, cudaMemcpyHostToDevice, st);
   }
 #endif
+  const auto ks = reinterpret_cast<const __nv_bfloat16*>(key_split);
   if (PA.n > 0)
-    ws::psweep_ws_kernel<true><<<grid, ws::kThreads, ws::smem_bytes(), st>>>(A, reinterpret_cast<const __nv_bfloat16*>(key_split), tw, th, tiles_x,
-                                                                             tiles, items, counter, PA);
+    ws::psweep_ws_kernel<ws::kModePeers><<<grid, ws::kThreads, ws::smem_bytes(), st>>>(A, ks, tw, th, tiles_x, tiles, items, counter, PA);
+  else if (A.dbg_ix0)
+    ws::psweep_ws_kernel<ws::kModeDebug><<<grid, ws::kThreads, ws::smem_bytes(), st>>>(A, ks, tw, th, tiles_x, tiles, items, counter, PA);
   else
-    ws::psweep_ws_kernel<false><<<grid, ws::kThreads, ws::smem_bytes(), st>>>(A, reinterpret_cast<const __nv_bfloat16*>(key_split), tw, th, tiles_x,
-                                                                              tiles, items, counter, PA);
+    ws::psweep_ws_kernel<ws::kModePlain><<<grid, ws::kThreads, ws::smem_bytes(), st>>>(A, ks, tw, th, tiles_x, tiles, items, counter, PA);
 #ifdef RMVD_WS_STATS
   {
     unsigned long long h[32];

@@ -113,3 +113,39 @@ def test_robust_mvd_parameter_gradients_match_reference(cuda_lib, case_name, mon
     name = "encoder.conv3.0.weight"
     moved = np.abs(broken[name].reshape(-1)[::cases.MODEL_GRAD_STRIDE] - g[name]).max() / float(g[name + "|absmax"])
     assert moved > 2e-2, moved
+
+
+def test_robust_mvd_on_reference_sample_data(cuda_lib):
+    """BASELINE.json configs[0]: ``robust_mvd`` on the reference's own ``sample_data`` (720x1280 key view + 6 source views with their
+    real calibration) against the UNMODIFIED reference model run on CPU (tools/make_sample_data_golden.py, identical seeded weights).
+    Masks of all six views bit for bit (sha256 of the packed volume), correlation volumes within 1e-3 of max|ref| (the features
+    come from cuDNN here and from CPU convolutions there), regressed depth within 1e-3 relative where the inverse depth is well
+    conditioned."""
+    import hashlib
+    import io
+    from PIL import Image
+    g = np.load(os.path.join(GOLDEN, "sample_data.npz"))
+    V = int(g["n_views"])
+    images = [np.array(Image.open(io.BytesIO(g[f"png_{v}"].tobytes())), dtype=np.float32).transpose(2, 0, 1) for v in range(V + 1)]
+    sample = dict(images=images, intrinsics=[k for k in g["intrinsics"]], poses=[p for p in g["poses"]], keyview_idx=0)
+    torch.manual_seed(cases.MODEL_SEED)
+    model = rb.create_model("robust_mvd", pretrained=False, num_gpus=1)
+    pred, aux = model.run(**sample)
+    assert pred["depth"].shape == g["pred_depth"].shape
+    masks, corrs = model.corr_block.masks, model.corr_block.corrs
+    assert len(masks) == V and tuple(corrs[0].shape) == tuple(g["feat_shape"])
+    for v in range(V):
+        m = masks[v].cpu().numpy()
+        sha = np.frombuffer(hashlib.sha256(np.packbits(m.astype(np.uint8)).tobytes()).digest(), dtype=np.uint8)
+        if not np.array_equal(sha, g[f"mask_sha_{v}"]):
+            rows = np.argwhere(m.sum(axis=(0, 3)).astype(np.int32) != g[f"mask_rowsum_{v}"])
+            raise AssertionError(f"mask of view {v}: count {int(m.sum())} vs {int(g[f'mask_count_{v}'])}, first differing (plane,row) {rows[:4].tolist()}")
+        c = corrs[v].cpu().numpy().reshape(-1)[::251]
+        err = np.abs(c - g[f"corr_sub_{v}"]).max() / float(g[f"corr_absmax_{v}"])
+        assert err <= 1e-3, f"corr of view {v}: {err}"
+    ginv = g["aux_invdepth"]
+    assert np.abs(aux["invdepth"] - ginv).max() <= 1e-3 * np.abs(ginv).max()
+    live = ginv > 1e-2 * ginv.max()
+    rel = np.abs(pred["depth"] - g["pred_depth"])[live] / g["pred_depth"][live]
+    n_out = int((rel > 1e-3).sum())
+    assert n_out <= 0.005 * rel.size and np.median(rel) < 1e-4, f"{n_out} of {rel.size} well-conditioned pixels beyond 1e-3 (median {np.median(rel):.2e})"
