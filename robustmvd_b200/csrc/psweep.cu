@@ -402,7 +402,7 @@ static int psweep_corr_fwd_impl(const float* feat_key, const float* const* feat_
   bool tc = allow_tc, wsk = allow_ws;
   {
     PsweepArgs T{};
-    T.C = C;
+    T.C = C; T.h = h; T.w = w;
     for (int k = 0; k < 4; ++k) T.ist[k] = inv_stride[k];
     tc = tc && psweep_tc_eligible(T, 0);
     wsk = wsk && psweep_ws_eligible(T, 0) && (long long)N * (V < kMaxViews ? V : kMaxViews) <= 65535;

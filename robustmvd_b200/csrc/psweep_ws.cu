@@ -114,13 +114,22 @@ __shared__ WsConst s_k;
 // One output sample.  Single GPU: streaming stores.  Depth slabs over several GPUs (partition 1): the same value is
 // stored into the [V,N,S,h,w] tensor of every rank (own rank included) through the peer-mapped pointers, i.e. the all-gather of the
 // slabs happens row by row from inside the sampling loop instead of as a separate collective.
+// streaming store of base[off]: one 32 x 32 + 64-bit multiply-add forms the address (the compiler's own 64-bit offset arithmetic
+// costs four instructions per store in the sampling loop)
+__device__ __forceinline__ void stcs_at(float* base, unsigned off, float v) {
+  unsigned long long a;
+  asm("mad.wide.u32 %0, %1, 4, %2;" : "=l"(a) : "r"(off), "l"(base));
+  asm volatile("st.global.cs.f32 [%0], %1;" ::"l"(a), "f"(v) : "memory");
+}
+__device__ __forceinline__ void stcs_at(float* base, size_t off, float v) { __stcs(base + off, v); }
+
 // corr / mask: the caller's register copies of W.corr / W.mask, already advanced by `base` elements; o: offset from there
 template <int kMode, typename Off>
 __device__ __forceinline__ void store_out(const WsConst& W, float* __restrict__ corr, float* __restrict__ mask, size_t base, Off o, float c,
                                           float m) {
   if (kMode != kModePeers) {
-    __stcs(corr + o, c);
-    __stcs(mask + o, m);
+    stcs_at(corr, o, c);
+    stcs_at(mask, o, m);
   } else {
     for (int g = 0; g < W.npeers; ++g) { W.pcorr[g][base + o] = c; W.pmask[g][base + o] = m; }
   }
@@ -1095,7 +1104,10 @@ __device__ __forceinline__ void sample_chunk(const ChunkDesc* D, const float* G,
   auto is_dead = [&](int q) { return (dead[q >> 5] >> (q & 31)) & 1u; };
   int pl = cw >> 1;
   unsigned o = (unsigned)pl * P;
-  constexpr int kSU = 2;                                 // samples in flight per thread
+#ifndef WS_SU
+#define WS_SU 2
+#endif
+  constexpr int kSU = WS_SU;                             // samples in flight per thread
   for (; pl + (kSU - 1) * kStep < len; pl += kSU * kStep, o += kSU * step) {
     bool all_dead = true;
 #pragma unroll
@@ -1415,6 +1427,7 @@ int repack_key_tiles(const float* key, void* dst, int N, int C, int h, int w, in
 
 bool psweep_ws_eligible(const PsweepArgs& A, int nviews) {
   if (A.C % 32 != 0 || A.C > ws::kMaxC || A.ist[2] != 0 || A.ist[3] != 0) return false;
+  if ((long long)A.h * A.w > (1 << 23)) return false;          // 32-bit element offsets inside a chunk of <= 256 planes
   for (int v = 0; v < nviews; ++v)
     if (A.hs[v] >= 32768 || A.ws[v] >= 32768) return false;
   return true;
