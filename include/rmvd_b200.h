@@ -276,7 +276,7 @@ int rmvd_view_fusion_fwd(const float* const* logits, const float* const* corrs, 
 
 /*
  * Test hook: the sampling chain of the tcgen05 kernel shares one refined reciprocal between its divisions
- * (csrc/psweep_tc.cu: rcp_refined / div_shared, the fast path of div.rn.f32 itself).  q_shared[i] = that sequence,
+ * (csrc/common.cuh: rcp_refined / div_shared, the fast path of div.rn.f32 itself).  q_shared[i] = that sequence,
  * q_rn[i] = __fdiv_rn(a[i], b[i]); the two must agree bit for bit for 2^-60 <= |b| <= 2^60, |a| <= 2^60.
  */
 int rmvd_debug_div_check(const float* a, const float* b, int n, float* q_shared, float* q_rn, void* stream);

@@ -5,7 +5,7 @@ import subprocess
 
 CSRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc")
 LIB = os.path.join(CSRC, "librmvd_b200.so")
-SOURCES = ("psweep.cu", "psweep_band.cu", "psweep_tc.cu", "psweep_ws.cu", "psweep_bwd.cu", "mvs.cu", "fusion.cu", "vis.cu")
+SOURCES = ("psweep.cu", "psweep_band.cu", "psweep_ws.cu", "psweep_bwd.cu", "mvs.cu", "fusion.cu", "vis.cu")
 HEADERS = ("common.cuh", "psweep.cuh", os.path.join("..", "..", "include", "rmvd_b200.h"))
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "-shared"]

@@ -391,20 +391,19 @@ static int psweep_corr_fwd_impl(const float* feat_key, const float* const* feat_
   if (s_begin == s_end && !peers) return RMVD_OK;     // (an empty slab of the peer mode still takes part in the handshake)
   cudaStream_t st = (cudaStream_t)stream;
 
-  // kernel choice: tcgen05 kernel (C % 32 == 0, per-plane hypotheses) > banded fp32 kernel (C % 32 == 0, source map
-  // <= 65536 texels) > general direct kernel.  RMVD_PSWEEP_KERNEL=tc|band|direct restricts the choice (A/B runs only).
+  // kernel choice: persistent tcgen05 kernel (psweep_ws.cu: C % 32 == 0, C <= 256, per-plane hypotheses) > banded fp32
+  // kernel (C % 32 == 0, source map <= 65536 texels) > general direct kernel.  RMVD_PSWEEP_KERNEL=ws|band|direct restricts
+  // the choice (A/B runs only).
   static const char* const force = getenv("RMVD_PSWEEP_KERNEL");   // read once per process
   const bool allow_ws = !force || strcmp(force, "ws") == 0;
-  const bool allow_tc = (force && strcmp(force, "tc") == 0);
   const bool allow_band = !force || strcmp(force, "band") == 0;
   bool band = (C % 32 == 0) && allow_band;
   for (int v = 0; v < V; ++v) band = band && ((long long)hs[v] * ws[v] <= 65536);
-  bool tc = allow_tc, wsk = allow_ws;
+  bool wsk = allow_ws;
   {
     PsweepArgs T{};
     T.C = C; T.h = h; T.w = w;
     for (int k = 0; k < 4; ++k) T.ist[k] = inv_stride[k];
-    tc = tc && psweep_tc_eligible(T, 0);
     wsk = wsk && psweep_ws_eligible(T, 0) && (long long)N * (V < kMaxViews ? V : kMaxViews) <= 65535;
   }
   if (peers && (!wsk || V > kMaxViews)) return RMVD_E_MODE;
@@ -417,8 +416,6 @@ static int psweep_corr_fwd_impl(const float* feat_key, const float* const* feat_
   if (wsk) {
     int rc = repack_key_tiles(feat_key, key_nhwc, N, C, h, w, l2, st);
     if (rc) return rc;
-  } else if (tc) {
-    // repacked together with the first group of source maps below (one launch)
   } else if (band) {
     int rc = repack(feat_key, key_nhwc, N, C, h * w, l2, st);
     if (rc) return rc;
@@ -432,17 +429,13 @@ static int psweep_corr_fwd_impl(const float* feat_key, const float* const* feat_
     for (int k = 0; k < 4; ++k) A.ist[k] = inv_stride[k];
     const float* rp_src[1 + kMaxViews];
     void* rp_dst[1 + kMaxViews];
-    int rp_P[1 + kMaxViews];
     int rp_n = 0;
-    if (tc && v0 == 0) { rp_src[0] = feat_key; rp_dst[0] = key_nhwc; rp_P[0] = h * w; rp_n = 1; }
     for (int j = 0; j < nv; ++j) {
       const int v = v0 + j;
       float* dst = (float*)wsp;
       wsp += (psweep_ws_src_bytes(N, C, hs[v], ws[v]) + 255) / 256 * 256;
       if (wsk) {
-        rp_src[rp_n] = feat_src[v]; rp_dst[rp_n] = dst; rp_P[rp_n] = hs[v] * ws[v]; ++rp_n;
-      } else if (tc) {
-        rp_src[rp_n] = feat_src[v]; rp_dst[rp_n] = dst; rp_P[rp_n] = hs[v] * ws[v]; ++rp_n;
+        rp_src[rp_n] = feat_src[v]; rp_dst[rp_n] = dst; ++rp_n;
       } else {
         int rc = repack(feat_src[v], dst, N, C, hs[v] * ws[v], l2, st);
         if (rc) return rc;
@@ -456,15 +449,11 @@ static int psweep_corr_fwd_impl(const float* feat_key, const float* const* feat_
     if (wsk) {
       int rc = repack_grouped_batch(rp_src, rp_dst, hs + v0, ws + v0, rp_n, N, C, l2, counter, st);
       if (rc) return rc;
-    } else if (tc) {
-      int rc = repack_split_batch(rp_src, rp_dst, rp_P, rp_n, N, C, l2, st);
-      if (rc) return rc;
     }
     A.N = N; A.C = C; A.h = h; A.w = w; A.S = S; A.s_begin = s_begin; A.s_end = s_end;
     A.norm = normalize_mode; A.out_S = out_S; A.out_s0 = out_s0; A.v0 = v0;
     A.corr = corr; A.mask = mask; A.dbg_ix0 = dbg_ix0; A.dbg_iy0 = dbg_iy0; A.dbg_geom = dbg_geom;
     int rc = wsk ? launch_psweep_ws(A, key_nhwc, nv, counter, peers, st)
-                : tc ? launch_psweep_tc(A, key_nhwc, nv, st)
                 : band ? launch_psweep_band(A, key_nhwc, nv, st) : dispatch_corr<false>(A, nv, st);
     if (rc) return rc;
   }

@@ -1,5 +1,5 @@
 // Argument block shared by the plane-sweep correlation kernels (psweep.cu: general direct kernel,
-// psweep_band.cu: banded-GEMM kernel).
+// psweep_band.cu: banded fp32 kernel, psweep_ws.cu: persistent tcgen05 kernel).
 #pragma once
 #include "common.cuh"
 
@@ -27,20 +27,10 @@ struct PsweepArgs {
   int32_t* dbg_ix0;
   int32_t* dbg_iy0;
   uint8_t* dbg_geom;
-  unsigned long long* stats;         // optional debug counters (RMVD_PSWEEP_STATS=1), see psweep_tc.cu
 };
 
 // psweep_band.cu: launches the banded kernel when the shape qualifies; returns -1000 when it does not.
 int launch_psweep_band(const PsweepArgs& A, const float* key_nhwc, int nviews, cudaStream_t st);
-
-// psweep_tc.cu: tcgen05 kernel.  Operands are channels-last bf16 hi / lo planes written by repack_split() into the same
-// workspace slots (4 bytes per feature element) the fp32 channels-last copies of the band kernel use.
-bool psweep_tc_eligible(const PsweepArgs& A, int nviews);
-int repack_split(const float* src, void* dst, int N, int C, int P, int l2norm, cudaStream_t st);
-// the same for up to 1 + kMaxViews maps of one call (key + sources) in one launch
-int repack_split_batch(const float* const* srcs, void* const* dsts, const int* Ps, int count, int N, int C, int l2norm,
-                       cudaStream_t st);
-int launch_psweep_tc(const PsweepArgs& A, const void* key_split, int nviews, cudaStream_t st);
 
 // psweep_ws.cu: persistent warp-specialised tcgen05 kernel (one CTA per SM).  The key map is repacked tile by tile
 // (repack_key_tiles: psweep_ws_key_bytes), the source maps into the grouped split layout of repack_grouped_batch() (rows

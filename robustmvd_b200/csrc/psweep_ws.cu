@@ -1,8 +1,8 @@
 // Plane-sweep correlation, persistent warp-specialised form (sm_100a): one CTA per SM owns all 512 TMEM columns and
-// loops over work items (tile of 64 key pixels, sample, source view).  Same contraction as psweep_tc.cu --
+// loops over work items (tile of 64 key pixels, sample, source view).  The contraction:
 // corr = bilinear(G), G = key . band^T over the source texels under the tile's epipolar band
-// (planesweep_corr.py:174-186 restricted to where it is sampled), bf16 hi/lo split operands on tcgen05 -- but the serial
-// phases of a tile no longer wait for one another:
+// (planesweep_corr.py:174-186 restricted to where it is sampled), bf16 hi/lo split operands on tcgen05.  The serial
+// phases of a tile do not wait for one another:
 //
 //   warp 0      planner    per item: calibration (planesweep_corr.py:228-300), tile slots; per chunk of planes: the band
 //                          (one 8-aligned [xa, xa + len) span per source row), the per-plane terms and dead-plane bits,
@@ -57,7 +57,10 @@ constexpr int kMaxC = 256;                   // A' in TMEM: C / 2 columns
 constexpr int kTmemA = kNBuf * kNT;          // TMEM columns: D = [0, 384), A' = [384, 384 + C / 2)
 constexpr int kTmemCols = 512;
 constexpr int kRMax = WS_RMAX;               // band capacity of one chunk (G columns), <= kNBuf * kNT
-constexpr int kGPitch = kRMax + 2;           // 2 (mod 32): conflict-free sampling reads and drain stores (see psweep_tc.cu)
+// G row pitch = 2 (mod 32).  Sampling: lane = pixel = G row, and adjacent pixels read adjacent columns, so a warp's addresses
+// step by pitch + 1 = 3 (mod 32): 32 distinct banks (an odd pitch gives a step of 2 and two wavefronts per read).  Drain:
+// sixteen rows at one column step by 2 -- the lower half-warp covers the even banks, the upper half (next column) the odd.
+constexpr int kGPitch = kRMax + 2;
 static_assert(kGPitch % 32 == 2, "G pitch must be 2 mod 32");
 constexpr int kMaxRows = 64;                 // source rows a band may span
 constexpr int kMaxPlanes = 256;              // planes per chunk
@@ -1014,13 +1017,18 @@ __device__ __noinline__ void sample_slow(const ChunkDesc* D, int p, int pl, int 
   }
 }
 
-// Filtered locate (see psweep_tc.cu for the error analysis): only the INTEGER corner and the 0/1 mask have to be the
-// reference's bit for bit.  ix' = fma(nu, rcp(den), -0.5) is within u (3 ws + 6.5) of U - 0.5 and the reference's chain within
-// u (5.5 ws + 10.5) (u = 2^-24): whenever ix' is further than eps = u (16 ws + 64) from an integer, floor(ix') IS the
-// reference's floor.  Interior samples are valid iff the geometric mask holds; samples with a corner column / row outside
-// the map need the in-range weight below 0.9999 by more than eps (mask 0); everything else takes sample_slow().  The
-// reciprocal is MUFU's (relative error <= 2^-23 = 2u, i.e. <= 2u (ws + 2) on ix'): the margin u (10.5 ws + 53.5) left by the
-// reference's own bound covers it several times (tools/filter_check.py perturbs the reciprocal by +-2 ulp).
+// Filtered locate.  Only the INTEGER corner (floor of the un-normalised coordinate) and the 0/1 mask have to be the
+// reference's bit for bit; the bilinear weights only to 1e-4.  With U = nu / den the reference's chain
+// (us = nu/den; xg = 2 us/ws - 1; ix = fma(xg + 1, ws/2, -0.5), five roundings) stays within u (5.5 ws + 10.5) of
+// U - 0.5 (u = 2^-24, |U| <= ws + 2), and ix' = fma(nu, rcp(den), -0.5) with an exactly rounded reciprocal within
+// u (3 ws + 6.5): whenever ix' is further than eps = u (16 ws + 64) from an integer, floor(ix') IS the reference's floor.
+// The reciprocal here is MUFU's (relative error <= 2^-23 = 2u, i.e. <= 2u (ws + 2) more on ix'): the margin
+// u (10.5 ws + 53.5) left by the two bounds covers it several times (tools/filter_check.py perturbs the reciprocal by
+// +-2 ulp).  A sample is settled by the cheap chain when both floors are trusted (or the coordinate is beyond
+// [-3, size + 1], where the saturated index is decided) and it is either interior (all four corners inside the map: the
+// in-range weight sum is 1 +- 6u >= 0.9999, mask = geometric mask) or has a corner column / row outside the map with the
+// in-range weight below 0.9999 by more than eps (mask = 0).  Everything else -- about one sample in 10^3 -- takes
+// sample_slow(), the exact chain.  tests/test_gpu_planesweep.py compares indices, geometric masks and masks bit for bit.
 struct FastConst {
   float u_h, v_h, k_h;
   float sg, zp;           // visibility in the source as one compare: zs * sg > zp (planesweep_corr.py:500-504)
@@ -1517,4 +1525,20 @@ int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, uns
   return (int)cudaGetLastError();
 }
 
+// q_shared[i] = a[i] / b[i] through rcp_refined() + div_shared() (the divisions of the exact coordinate chain), q_rn[i] = __fdiv_rn
+__global__ void div_check_kernel(const float* __restrict__ a, const float* __restrict__ b, int n, float* __restrict__ q_shared,
+                                 float* __restrict__ q_rn) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  q_shared[i] = div_shared(a[i], b[i], rcp_refined(b[i]));
+  q_rn[i] = __fdiv_rn(a[i], b[i]);
+}
+
 }  // namespace rmvd
+
+extern "C" int rmvd_debug_div_check(const float* a, const float* b, int n, float* q_shared, float* q_rn, void* stream) {
+  if (!a || !b || !q_shared || !q_rn) return RMVD_E_NULL;
+  if (n <= 0) return RMVD_E_SHAPE;
+  rmvd::div_check_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(a, b, n, q_shared, q_rn);
+  return (int)cudaGetLastError();
+}

@@ -186,7 +186,7 @@ def test_warp_function_zeros_and_border(cuda_lib):
 
 
 def test_shared_reciprocal_division_is_exact(cuda_lib):
-    """The tcgen05 kernel's coordinate chain divides through a shared refined reciprocal (psweep_tc.cu: rcp_refined /
+    """The exact coordinate chain divides through a shared refined reciprocal (common.cuh: rcp_refined /
     div_shared); within the guarded operand range it must equal the correctly rounded quotient bit for bit."""
     from robustmvd_b200 import _lib
     rng = np.random.default_rng(123)

@@ -1,4 +1,4 @@
-"""CPU model of the filtered locate of csrc/psweep_tc.cu (tc_sample_fast): for every sample the cheap chain settles,
+"""CPU model of the filtered locate of csrc/psweep_ws.cu (sample_fast): for every sample the cheap chain settles,
 its integer corner and its mask must equal the oracle's exact chain.  The reciprocal is modelled as the correctly
 rounded 1/den perturbed by up to +-2 ulp (rcp.approx.ftz.f32 is specified to 1 ulp) before the Newton step.
 

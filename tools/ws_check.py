@@ -2,7 +2,7 @@
 against the numpy oracle and the relative corr error, without stopping at the first failure; then the timing of the
 16-frame cfg2 call (the bench workload) and of single frames.
 
-    python tools/ws_check.py [--quick] [--time-only] [--kernel ws|tc]
+    python tools/ws_check.py [--quick] [--time-only] [--kernel ws|band|direct]
 
 The kernel is chosen by RMVD_PSWEEP_KERNEL (read once per process by the library): --kernel sets it before the first call.
 """
