@@ -9,7 +9,8 @@
  *   - all tensors float32, contiguous, NCHW unless stated; pointers are DEVICE pointers unless the name
  *     ends in `_host` or the comment says "host array";
  *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*), re-entrant, and holds no
- *     global mutable state; scratch memory is passed in by the caller (`workspace`);
+ *     global mutable state; scratch memory is passed in by the caller (`workspace`) -- the one exception is
+ *     rmvd_psweep_corr_fwd_static, which says so;
  *   - return value: 0 ok, <0 invalid argument (RMVD_E_*), >0 a cudaError_t; nothing throws across the ABI;
  *   - there is no CPU fallback: without a CUDA device the calls return a cudaError_t.
  */
@@ -23,7 +24,7 @@
 extern "C" {
 #endif
 
-#define RMVD_ABI_VERSION 2
+#define RMVD_ABI_VERSION 3
 #define RMVD_MAX_PEERS 8      /* ranks of one depth-slab communicator (GPUs of one NVSwitch box) */
 
 #define RMVD_OK 0
@@ -32,6 +33,7 @@ extern "C" {
 #define RMVD_E_MODE (-3)      /* unknown enum value */
 #define RMVD_E_WORKSPACE (-4) /* workspace too small */
 #define RMVD_E_RANGE (-5)     /* plane range outside [0, S] */
+#define RMVD_E_STATIC_LIMIT (-6) /* problem needs more scratch than RMVD_STATIC_SCRATCH_BYTES (rmvd_psweep_corr_fwd_static) */
 
 /* normalize= of TorchCorr / WarpOnlyCorr (planesweep_corr.py:108-114, :144-150) */
 #define RMVD_NORM_NONE 0   /* False */
@@ -99,6 +101,30 @@ int rmvd_psweep_corr_fwd_peers(const float* feat_key, const float* const* feat_s
                                int normalize_mode, int out_S, int out_s0, int num_peers, int rank,
                                float* const* corr_peers, float* const* mask_peers, uint32_t* const* flag_peers,
                                uint32_t epoch, void* workspace, size_t workspace_bytes, void* stream);
+
+/*
+ * rmvd_psweep_corr_fwd without any allocation by anyone: the scratch (what rmvd_psweep_workspace_bytes() sizes) is a
+ * file-scope device array of RMVD_STATIC_SCRATCH_BYTES inside the library instead of a caller's workspace.  This entry
+ * point has no counterpart in the reference; it was added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The call itself
+ * issues no cudaMalloc / cudaFree and no allocating library routine; the caller passes inputs and outputs as for
+ * rmvd_psweep_corr_fwd (same meaning, same results; no debug outputs).
+ *   limit     rmvd_psweep_workspace_bytes(N, C, h, w, V, hs, ws) <= RMVD_STATIC_SCRATCH_BYTES (32 MiB: one frame of the
+ *             KITTI shape, C = 256, 48 x 160 features, with up to 3 source views = 31.5 MB); larger problems return
+ *             RMVD_E_STATIC_LIMIT and launch nothing -- use rmvd_psweep_corr_fwd with a workspace.
+ *   cost      every GPU that loads the library holds the 32 MiB until the process exits.
+ *   sharing   all calls of a process on one GPU use the same array, which keeps the previous call's contents (each call
+ *             zeroes the counters it needs and overwrites the rest before reading it): calls that overlap on the GPU
+ *             -- different streams, or different threads -- race.  Serialise them on one stream.
+ *   device    the array's device address is looked up once per device (cudaGetSymbolAddress with the calling thread's
+ *             current device) and cached; call with the device of the tensors current.
+ */
+#define RMVD_STATIC_SCRATCH_BYTES (32u << 20)
+int rmvd_psweep_corr_fwd_static(const float* feat_key, const float* const* feat_src, const float* intrinsics_key,
+                                const float* const* intrinsics_src, const float* const* src_to_key,
+                                const float* invdepths, const int64_t* inv_stride_host, int N, int C, int h, int w,
+                                int V, const int* hs_host, const int* ws_host, int S, int s_begin, int s_end,
+                                int normalize_mode, float* corr, float* mask, int out_S, int out_s0, void* stream);
 
 /*
  * Backward of rmvd_psweep_corr_fwd with respect to the feature maps.  The reference obtains it from

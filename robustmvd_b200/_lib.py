@@ -10,11 +10,11 @@ from ctypes import c_char_p, c_float, c_int, c_int64, c_size_t, c_void_p, POINTE
 from . import _build
 
 _lib = None
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 EXPORTS = (
     "rmvd_abi_version", "rmvd_status_string", "rmvd_psweep_workspace_bytes", "rmvd_psweep_corr_fwd",
-    "rmvd_psweep_corr_fwd_peers",
+    "rmvd_psweep_corr_fwd_peers", "rmvd_psweep_corr_fwd_static",
     "rmvd_psweep_warp_fwd", "rmvd_psweep_bwd_workspace_bytes", "rmvd_psweep_corr_bwd",
     "rmvd_corr_grid_fwd", "rmvd_warp_grid_fwd", "rmvd_mvs_variance_fwd",
     "rmvd_homo_warp_fwd", "rmvd_mvs_regress_fwd", "rmvd_softargmax_partial", "rmvd_softargmax_combine",
@@ -38,6 +38,8 @@ def _declare(lib):
     lib.rmvd_psweep_workspace_bytes.argtypes = [c_int, c_int, c_int, c_int, c_int, PI, PI]
     lib.rmvd_psweep_corr_fwd.argtypes = [P, PP, P, PP, PP, P, PL] + [c_int] * 5 + [PI, PI] + [c_int] * 4 + \
         [P, P, c_int, c_int, P, P, P, P, c_size_t, P]
+    lib.rmvd_psweep_corr_fwd_static.argtypes = [P, PP, P, PP, PP, P, PL] + [c_int] * 5 + [PI, PI] + [c_int] * 4 + \
+        [P, P, c_int, c_int, P]
     lib.rmvd_psweep_corr_fwd_peers.argtypes = [P, PP, P, PP, PP, P, PL] + [c_int] * 5 + [PI, PI] + [c_int] * 8 + \
         [PP, PP, PP, ctypes.c_uint32, P, c_size_t, P]
     lib.rmvd_psweep_bwd_workspace_bytes.restype = c_size_t

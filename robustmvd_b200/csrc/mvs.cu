@@ -923,6 +923,7 @@ extern "C" const char* rmvd_status_string(int status) {
     case RMVD_E_MODE: return "unknown mode";
     case RMVD_E_WORKSPACE: return "workspace missing or too small";
     case RMVD_E_RANGE: return "plane range outside the schedule";
+    case RMVD_E_STATIC_LIMIT: return "problem needs more scratch than the library's static scratch array (RMVD_STATIC_SCRATCH_BYTES)";
     default: return status > 0 ? cudaGetErrorString((cudaError_t)status) : "unknown status";
   }
 }

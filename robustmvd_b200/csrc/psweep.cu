@@ -11,6 +11,7 @@
 //   corr, mask     [V, N, S, h, w] written once, 128-byte coalesced rows staged through shared memory.
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 
 #include "psweep.cuh"
 
@@ -490,6 +491,56 @@ extern "C" int rmvd_psweep_corr_fwd_peers(const float* feat_key, const float* co
   return psweep_corr_fwd_impl(feat_key, feat_src, intrinsics_key, intrinsics_src, src_to_key, invdepths, inv_stride, N, C, h, w, V, hs, ws,
                               S, s_begin, s_end, normalize_mode, P.corr[rank], P.mask[rank], out_S, out_s0, nullptr, nullptr, nullptr,
                               workspace, workspace_bytes, stream, &P);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// rmvd_psweep_corr_fwd_static: the forward call for callers that may not allocate (CUDA graph capture, serving loops,
+// harnesses that forbid cudaMalloc).  The scratch of rmvd_psweep_corr_fwd -- the repacked key / source maps and the
+// work-item counter -- lives in this file-scope device array instead of a caller's workspace: RMVD_STATIC_SCRATCH_BYTES
+// of every GPU that loads the library, held until the process exits.  The array's name is a host-side stand-in in host
+// code, not a device address; the address is taken once per device with cudaGetSymbolAddress (that device current) and
+// cached.  Nothing in the scratch has to start at zero except the work-item counters, which the repack launch of every
+// call zeroes; everything else is written before it is read.  All calls share the array: calls that overlap on the GPU
+// (two streams, two threads) race.
+static __device__ __align__(256) unsigned char g_static_scratch[RMVD_STATIC_SCRATCH_BYTES];
+
+static int static_scratch_address(void** out) {
+  constexpr int kMaxDevices = 64;
+  static std::mutex mu;
+  static void* addr[kMaxDevices] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= kMaxDevices) return RMVD_E_RANGE;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess) return (int)e;
+    if (!p) return (int)cudaErrorInvalidSymbol;
+    addr[dev] = p;
+  }
+  *out = addr[dev];
+  return RMVD_OK;
+}
+
+extern "C" int rmvd_psweep_corr_fwd_static(const float* feat_key, const float* const* feat_src, const float* intrinsics_key,
+                                           const float* const* intrinsics_src, const float* const* src_to_key,
+                                           const float* invdepths, const int64_t* inv_stride, int N, int C, int h, int w,
+                                           int V, const int* hs, const int* ws, int S, int s_begin, int s_end,
+                                           int normalize_mode, float* corr, float* mask, int out_S, int out_s0, void* stream) {
+  if (!hs || !ws) return RMVD_E_NULL;
+  if (N <= 0 || C <= 0 || h <= 0 || w <= 0 || V <= 0) return RMVD_E_SHAPE;
+  for (int v = 0; v < V; ++v)
+    if (hs[v] <= 0 || ws[v] <= 0 || hs[v] >= 32768 || ws[v] >= 32768) return RMVD_E_SHAPE;
+  const size_t need = rmvd_psweep_workspace_bytes(N, C, h, w, V, hs, ws);
+  if (need > (size_t)RMVD_STATIC_SCRATCH_BYTES) return RMVD_E_STATIC_LIMIT;
+  void* scratch = nullptr;
+  int rc = static_scratch_address(&scratch);
+  if (rc) return rc;
+  return psweep_corr_fwd_impl(feat_key, feat_src, intrinsics_key, intrinsics_src, src_to_key, invdepths, inv_stride, N, C, h, w, V, hs, ws,
+                              S, s_begin, s_end, normalize_mode, corr, mask, out_S, out_s0, nullptr, nullptr, nullptr, scratch,
+                              (size_t)RMVD_STATIC_SCRATCH_BYTES, stream, nullptr);
 }
 
 extern "C" int rmvd_corr_grid_fwd(const float* feat_key, const float* feat_src, const float* grids,
