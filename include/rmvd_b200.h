@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define RMVD_ABI_VERSION 3
+#define RMVD_ABI_VERSION 4
 #define RMVD_MAX_PEERS 8      /* ranks of one depth-slab communicator (GPUs of one NVSwitch box) */
 
 #define RMVD_OK 0
@@ -184,6 +184,18 @@ int rmvd_warp_grid_fwd(const float* x, const float* grid, int K, int C, int hs, 
 int rmvd_mvs_variance_fwd(const float* feats, const float* proj, const float* depths, int B, int Vt, int C,
                           int h, int w, int D, int d_begin, int d_end, float* variance, int out_D, int out_d0,
                           void* stream);
+
+/*
+ * The same volume (mvsnet.py:123-136 + blocks/utils.py:222-268) through the channels-last staged kernel (csrc/mvs_var.cu):
+ * the source views are first repacked into `workspace` ([B,Vt-1,h*w,C] float32), a staged texel is one 128-byte line and a
+ * corner 8 x LDS.128.  Takes C % 32 == 0 and Vt >= 2; every other shape is forwarded to rmvd_mvs_variance_fwd (no
+ * workspace needed: rmvd_mvs_variance_workspace_bytes returns 0 for it).  workspace: 16-byte aligned device memory of at
+ * least rmvd_mvs_variance_workspace_bytes(B, Vt, C, h, w) bytes, scratch (contents undefined afterwards).
+ */
+size_t rmvd_mvs_variance_workspace_bytes(int B, int Vt, int C, int h, int w);
+int rmvd_mvs_variance_fwd_ws(const float* feats, const float* proj, const float* depths, int B, int Vt, int C, int h,
+                             int w, int D, int d_begin, int d_end, float* variance, int out_D, int out_d0,
+                             void* workspace, size_t workspace_bytes, void* stream);
 
 /*
  * homo_warp (blocks/utils.py:222-268), materialising: src_feat [B,C,H,W], src_proj/ref_proj_inv [B,4,4],

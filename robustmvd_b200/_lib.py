@@ -10,13 +10,14 @@ from ctypes import c_char_p, c_float, c_int, c_int64, c_size_t, c_void_p, POINTE
 from . import _build
 
 _lib = None
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 EXPORTS = (
     "rmvd_abi_version", "rmvd_status_string", "rmvd_psweep_workspace_bytes", "rmvd_psweep_corr_fwd",
     "rmvd_psweep_corr_fwd_peers", "rmvd_psweep_corr_fwd_static",
     "rmvd_psweep_warp_fwd", "rmvd_psweep_bwd_workspace_bytes", "rmvd_psweep_corr_bwd",
-    "rmvd_corr_grid_fwd", "rmvd_warp_grid_fwd", "rmvd_mvs_variance_fwd",
+    "rmvd_corr_grid_fwd", "rmvd_warp_grid_fwd", "rmvd_mvs_variance_fwd", "rmvd_mvs_variance_fwd_ws",
+    "rmvd_mvs_variance_workspace_bytes",
     "rmvd_homo_warp_fwd", "rmvd_mvs_regress_fwd", "rmvd_softargmax_partial", "rmvd_softargmax_combine",
     "rmvd_softargmax_confidence", "rmvd_softargmax_slab_fused", "rmvd_soft_argmin_fwd", "rmvd_view_fusion_fwd", "rmvd_homography_groupcorr_fwd", "rmvd_homography_warp_fwd", "rmvd_vis_cost_volume_fwd", "rmvd_cvp_proj_cost_fwd", "rmvd_cvp_projections", "rmvd_debug_div_check",
 )
@@ -50,6 +51,9 @@ def _declare(lib):
     lib.rmvd_corr_grid_fwd.argtypes = [P, P, P, P] + [c_int] * 8 + [P, P, P, c_size_t, P]
     lib.rmvd_warp_grid_fwd.argtypes = [P, P] + [c_int] * 7 + [P, P, P]
     lib.rmvd_mvs_variance_fwd.argtypes = [P, P, P] + [c_int] * 8 + [P, c_int, c_int, P]
+    lib.rmvd_mvs_variance_workspace_bytes.restype = c_size_t
+    lib.rmvd_mvs_variance_workspace_bytes.argtypes = [c_int] * 5
+    lib.rmvd_mvs_variance_fwd_ws.argtypes = [P, P, P] + [c_int] * 8 + [P, c_int, c_int, P, c_size_t, P]
     lib.rmvd_homo_warp_fwd.argtypes = [P, P, P, P] + [c_int] * 5 + [P, P, P, P]
     lib.rmvd_mvs_regress_fwd.argtypes = [P, P] + [c_int] * 4 + [P, P, P, P, P, P]
     lib.rmvd_softargmax_partial.argtypes = [P, P] + [c_int] * 5 + [P, P]
@@ -66,7 +70,7 @@ def _declare(lib):
     lib.rmvd_debug_div_check.argtypes = [P, P, c_int, P, P, P]
     for name in EXPORTS:
         if name not in ("rmvd_abi_version", "rmvd_status_string", "rmvd_psweep_workspace_bytes",
-                        "rmvd_psweep_bwd_workspace_bytes"):
+                        "rmvd_psweep_bwd_workspace_bytes", "rmvd_mvs_variance_workspace_bytes"):
             getattr(lib, name).restype = c_int
 
 

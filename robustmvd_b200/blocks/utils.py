@@ -40,9 +40,12 @@ def mvs_variance_volume(feats, proj_mats, depth_values, plane_range=None):
     D = depth_values.shape[1]
     d0, d1 = (0, D) if plane_range is None else plane_range
     out = torch.empty((B, C, d1 - d0, h, w), dtype=torch.float32, device=feats.device)
-    st = _lib.load().rmvd_mvs_variance_fwd(_lib.ptr(feats), _lib.ptr(proj_mats), _lib.ptr(depth_values), B, V, C, h, w,
-                                           D, d0, d1, _lib.ptr(out), d1 - d0, 0, _lib.stream_ptr())
-    _lib.check(st, "rmvd_mvs_variance_fwd")
+    lib = _lib.load()
+    need = lib.rmvd_mvs_variance_workspace_bytes(B, V, C, h, w)     # channels-last copy of the source views (0: shape takes the NCHW kernel)
+    ws = torch.empty(max(need, 16), dtype=torch.uint8, device=feats.device)
+    st = lib.rmvd_mvs_variance_fwd_ws(_lib.ptr(feats), _lib.ptr(proj_mats), _lib.ptr(depth_values), B, V, C, h, w, D, d0, d1,
+                                      _lib.ptr(out), d1 - d0, 0, _lib.ptr(ws), need, _lib.stream_ptr())
+    _lib.check(st, "rmvd_mvs_variance_fwd_ws")
     return out
 
 

@@ -156,3 +156,79 @@ def test_variance_rotated_views(cuda_lib, w):
     var = npy(bu.mvs_variance_volume(cu(inp["feats"]), cu(inp["proj"]), cu(inp["depth"])))
     ov = oracle.mvs_variance(inp["feats"], inp["proj"], inp["depth"])
     assert np.abs(var - ov).max() <= 1e-4 * np.abs(ov).max()
+
+
+CL_CASES = {
+    # name: (h, w, C, views, planes, batch, fx, seed)
+    "c32_odd_sizes": (21, 37, 32, 3, 9, 1, 30.0, 81),          # partially filled 16 x 4 tiles on both edges, ragged plane group
+    "c64_two_channel_groups": (24, 40, 64, 4, 10, 1, 32.0, 82),
+    "c32_batch2_single_source": (18, 34, 32, 2, 7, 2, 28.0, 83),
+    "c32_many_views": (16, 32, 32, 9, 5, 1, 25.0, 84),
+    "c32_one_plane": (12, 20, 32, 3, 1, 1, 20.0, 85),
+}
+
+
+@pytest.mark.parametrize("name", list(CL_CASES))
+def test_variance_channels_last_kernel(cuda_lib, name):
+    """Shapes that take the channels-last staged kernel (csrc/mvs_var.cu, C % 32 == 0) against the oracle: ragged tiles, several
+    channel groups, batches, one source view, more views than the pipeline has buffers, a single plane."""
+    from robustmvd_b200.blocks import utils as bu
+    h, w, C, V, D, n, fx, seed = CL_CASES[name]
+    inp = syn.mvs_inputs(h, w, C, V, D, n=n, seed=seed, fx=fx)
+    var = npy(bu.mvs_variance_volume(cu(inp["feats"]), cu(inp["proj"]), cu(inp["depth"])))
+    ov = oracle.mvs_variance(inp["feats"], inp["proj"], inp["depth"])
+    assert var.shape == ov.shape
+    assert np.abs(var - ov).max() <= 1e-4 * np.abs(ov).max()
+    if D > 2:
+        part = npy(bu.mvs_variance_volume(cu(inp["feats"]), cu(inp["proj"]), cu(inp["depth"]), plane_range=(1, D - 1)))
+        assert np.array_equal(part, var[:, :, 1:D - 1])
+
+
+def test_variance_views_outside_and_zoomed(cuda_lib):
+    """A source view that sees nothing of the key frustum (every sample outside: zeros, mvsnet.py:128 adds them), one zoomed
+    2x (neighbouring key pixels two texels apart) and one zoomed out (neighbouring pixels share texels); and a non-finite
+    depth plane (nan coordinates sample nothing)."""
+    from robustmvd_b200.blocks import utils as bu
+    h, w = 20, 36
+    inp = syn.mvs_inputs(h, w, 32, 4, 8, seed=91, fx=30.0)
+    K = np.array([[30.0, 0, w / 2.0, 0], [0, 30.0, h / 2.0, 0], [0, 0, 1, 0], [0, 0, 0, 1]], np.float64)
+    for v, (scale, shift) in ((1, (1.0, 500.0)), (2, (2.0, 0.02)), (3, (0.4, -0.03))):
+        Kv = K.copy()
+        Kv[0, 0] *= scale
+        Kv[1, 1] *= scale
+        pose = np.eye(4)
+        pose[:3, 3] = (shift, 0.01, 0.0)
+        P = pose.astype(np.float32)
+        P[:3, :4] = (Kv[:3, :3].astype(np.float32) @ P[:3, :4]).astype(np.float32)
+        inp["proj"][:, v] = P
+    var = npy(bu.mvs_variance_volume(cu(inp["feats"]), cu(inp["proj"]), cu(inp["depth"])))
+    ov = oracle.mvs_variance(inp["feats"], inp["proj"], inp["depth"])
+    assert np.abs(var - ov).max() <= 1e-4 * np.abs(ov).max()
+    depth = inp["depth"].copy()
+    depth[:, 3] = np.nan
+    var = npy(bu.mvs_variance_volume(cu(inp["feats"]), cu(inp["proj"]), cu(depth)))
+    ov = oracle.mvs_variance(inp["feats"], inp["proj"], depth)
+    assert np.abs(var - ov).max() <= 1e-4 * np.abs(ov).max()
+
+
+def test_variance_kernels_agree_and_workspace_is_checked(cuda_lib):
+    """rmvd_mvs_variance_fwd (NCHW-staged kernel) and rmvd_mvs_variance_fwd_ws (channels-last staged kernel) on the same
+    inputs; a missing or short workspace is refused."""
+    from robustmvd_b200 import _lib
+    lib = cuda_lib
+    inp = syn.mvs_inputs(28, 44, 32, 4, 12, seed=95, fx=40.0)
+    feats, proj, depth = cu(inp["feats"]), cu(inp["proj"]), cu(inp["depth"])
+    B, V, C, h, w = feats.shape
+    D = depth.shape[1]
+    a = torch.empty((B, C, D, h, w), dtype=torch.float32, device="cuda")
+    b = torch.empty_like(a)
+    need = lib.rmvd_mvs_variance_workspace_bytes(B, V, C, h, w)
+    assert need == 4 * B * (V - 1) * C * h * w
+    assert lib.rmvd_mvs_variance_workspace_bytes(B, V, 24, h, w) == 0 and lib.rmvd_mvs_variance_workspace_bytes(B, 1, C, h, w) == 0
+    ws = torch.empty(need, dtype=torch.uint8, device="cuda")
+    args = (_lib.ptr(feats), _lib.ptr(proj), _lib.ptr(depth), B, V, C, h, w, D, 0, D)
+    _lib.check(lib.rmvd_mvs_variance_fwd(*args, _lib.ptr(a), D, 0, _lib.stream_ptr()), "rmvd_mvs_variance_fwd")
+    _lib.check(lib.rmvd_mvs_variance_fwd_ws(*args, _lib.ptr(b), D, 0, _lib.ptr(ws), need, _lib.stream_ptr()), "rmvd_mvs_variance_fwd_ws")
+    assert float((a - b).abs().max()) <= 2e-5 * float(a.abs().max())
+    assert lib.rmvd_mvs_variance_fwd_ws(*args, _lib.ptr(b), D, 0, None, need, _lib.stream_ptr()) == -1          # RMVD_E_NULL
+    assert lib.rmvd_mvs_variance_fwd_ws(*args, _lib.ptr(b), D, 0, _lib.ptr(ws), need - 1, _lib.stream_ptr()) == -4  # RMVD_E_WORKSPACE
