@@ -93,14 +93,29 @@ int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* feat_src, co
  * between two sets of output tensors so that a rank that runs ahead never overwrites rows a slower rank is still reading.
  * All ranks must issue the call (same shapes, own slab); num_peers <= RMVD_MAX_PEERS; the debug outputs are not available.
  * Requires the persistent tcgen05 kernel (C % 32 == 0, C <= 256, per-plane hypotheses): RMVD_E_MODE otherwise.
+ * partition: RMVD_PARTITION_PLANES -- rank computes the planes [s_begin, s_end) of every tile (the depth slabs of SURVEY.md 8e);
+ *            RMVD_PARTITION_TILES  -- every rank passes the same plane range (normally all S planes) and computes every
+ *            num_peers-th (tile, sample, view) work item of it: the same tensors result on every rank, but the per-tile costs that
+ *            do not depend on the plane count (key tile, calibration, band planning, the band's rows) are divided between the
+ *            ranks too, which the plane split cannot do.
  */
+#define RMVD_PARTITION_PLANES 0
+#define RMVD_PARTITION_TILES 1
 int rmvd_psweep_corr_fwd_peers(const float* feat_key, const float* const* feat_src, const float* intrinsics_key,
                                const float* const* intrinsics_src, const float* const* src_to_key,
                                const float* invdepths, const int64_t* inv_stride_host, int N, int C, int h, int w,
                                int V, const int* hs_host, const int* ws_host, int S, int s_begin, int s_end,
                                int normalize_mode, int out_S, int out_s0, int num_peers, int rank,
                                float* const* corr_peers, float* const* mask_peers, uint32_t* const* flag_peers,
-                               uint32_t epoch, void* workspace, size_t workspace_bytes, void* stream);
+                               uint32_t epoch, int partition, void* workspace, size_t workspace_bytes, void* stream);
+
+/*
+ * Transport of the depth-slab gather by the copy engines (no counterpart in the reference, see rmvd_psweep_corr_fwd_peers): `rows`
+ * runs of row_bytes bytes, pitch_bytes apart in both buffers, from this rank's tensor to the same place in a peer-mapped tensor
+ * (one cudaMemcpy2DAsync).  Used by parallel.SlabGather(transport="copy"): the slab of view group k travels while the kernel of
+ * group k + 1 runs.
+ */
+int rmvd_copy_rows(void* dst, const void* src, size_t pitch_bytes, size_t row_bytes, int rows, void* stream);
 
 /*
  * rmvd_psweep_corr_fwd without any allocation by anyone: the scratch (what rmvd_psweep_workspace_bytes() sizes) is a

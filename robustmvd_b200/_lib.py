@@ -14,7 +14,7 @@ ABI_VERSION = 4
 
 EXPORTS = (
     "rmvd_abi_version", "rmvd_status_string", "rmvd_psweep_workspace_bytes", "rmvd_psweep_corr_fwd",
-    "rmvd_psweep_corr_fwd_peers", "rmvd_psweep_corr_fwd_static",
+    "rmvd_psweep_corr_fwd_peers", "rmvd_psweep_corr_fwd_static", "rmvd_copy_rows",
     "rmvd_psweep_warp_fwd", "rmvd_psweep_bwd_workspace_bytes", "rmvd_psweep_corr_bwd",
     "rmvd_corr_grid_fwd", "rmvd_warp_grid_fwd", "rmvd_mvs_variance_fwd", "rmvd_mvs_variance_fwd_ws",
     "rmvd_mvs_variance_workspace_bytes",
@@ -42,7 +42,8 @@ def _declare(lib):
     lib.rmvd_psweep_corr_fwd_static.argtypes = [P, PP, P, PP, PP, P, PL] + [c_int] * 5 + [PI, PI] + [c_int] * 4 + \
         [P, P, c_int, c_int, P]
     lib.rmvd_psweep_corr_fwd_peers.argtypes = [P, PP, P, PP, PP, P, PL] + [c_int] * 5 + [PI, PI] + [c_int] * 8 + \
-        [PP, PP, PP, ctypes.c_uint32, P, c_size_t, P]
+        [PP, PP, PP, ctypes.c_uint32, c_int, P, c_size_t, P]
+    lib.rmvd_copy_rows.argtypes = [P, P, c_size_t, c_size_t, c_int, P]
     lib.rmvd_psweep_bwd_workspace_bytes.restype = c_size_t
     lib.rmvd_psweep_bwd_workspace_bytes.argtypes = [c_int, c_int, c_int, c_int, c_int, PI, PI]
     lib.rmvd_psweep_corr_bwd.argtypes = [P, PP, P, PP, PP, P, PL] + [c_int] * 5 + [PI, PI] + [c_int] * 4 + \

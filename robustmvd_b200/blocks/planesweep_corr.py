@@ -229,7 +229,8 @@ class PlanesweepCorrelation(nn.Module):
     ``plane_range=(s_begin, s_end)`` (extension, default all planes) restricts the call to a depth slab; outputs
     then hold only those planes.  ``debug=True`` additionally keeps ``self.debug`` with the integer
     sampling indices and the geometric mask of every view.  ``out=(corr, mask)`` (extension): caller-provided contiguous
-    float32 device tensors ``[V, N, planes, h, w]`` that receive the correlation outputs instead of fresh allocations.
+    float32 device tensors ``[V, N, planes, h, w]`` that receive the correlation outputs instead of fresh allocations
+    (``planes`` = the slab's length, or S: the slab is then written at its own plane offset of the full-height tensors).
     """
 
     @torch.no_grad()
@@ -384,17 +385,20 @@ class PlanesweepCorrelation(nn.Module):
                 _lib.ptr(inv_c), ist, N, C, h, w, V, _lib.int_array(hs), _lib.int_array(ws), S, s0, s1,
                 _corr_norm_mode(self.normalize) if norm_mode is None else norm_mode, S, s0, G, peers["rank"],
                 _lib.raw_ptr_array(peers["corr"]), _lib.raw_ptr_array(peers["mask"]), _lib.raw_ptr_array(peers["flags"]),
-                peers["epoch"], _lib.ptr(wsp), wsp.numel(), _lib.stream_ptr())
+                peers["epoch"], int(peers.get("partition", 0)), _lib.ptr(wsp), wsp.numel(), _lib.stream_ptr())
             _lib.check(st, "rmvd_psweep_corr_fwd_peers")
             return None, None, inv
         if not self.warp_only:
+            out_S, out_s0 = Sl, 0
             if out is None:
                 corr = torch.empty((V, N, Sl, h, w), dtype=torch.float32, device=dev)
                 mask = torch.empty_like(corr)
             else:
                 corr, mask = out
+                if corr.shape[2] == S and Sl != S:      # full-height tensors: the slab lands at its own plane offset
+                    out_S, out_s0 = S, s0
                 for o in (corr, mask):
-                    assert o.shape == (V, N, Sl, h, w) and o.dtype == torch.float32 and o.is_contiguous() and o.device == dev
+                    assert o.shape == (V, N, out_S, h, w) and o.dtype == torch.float32 and o.is_contiguous() and o.device == dev
             dbg = [None, None, None]
             if debug:
                 dbg = [torch.empty((V, N, Sl, h, w), dtype=torch.int32, device=dev) for _ in range(2)]
@@ -404,7 +408,7 @@ class PlanesweepCorrelation(nn.Module):
             st = lib.rmvd_psweep_corr_fwd(
                 _lib.ptr(feat_key), _lib.ptr_array(srcs), _lib.ptr(Kk), _lib.ptr_array(Ks), _lib.ptr_array(Ts),
                 _lib.ptr(inv_c), ist, N, C, h, w, V, _lib.int_array(hs), _lib.int_array(ws), S, s0, s1,
-                _corr_norm_mode(self.normalize) if norm_mode is None else norm_mode, _lib.ptr(corr), _lib.ptr(mask), Sl, 0,
+                _corr_norm_mode(self.normalize) if norm_mode is None else norm_mode, _lib.ptr(corr), _lib.ptr(mask), out_S, out_s0,
                 _lib.ptr(dbg[0]),
                 _lib.ptr(dbg[1]), _lib.ptr(dbg[2]), _lib.ptr(wsp), wsp.numel(), _lib.stream_ptr())
             _lib.check(st, "rmvd_psweep_corr_fwd")

@@ -479,11 +479,12 @@ extern "C" int rmvd_psweep_corr_fwd_peers(const float* feat_key, const float* co
                                           int V, const int* hs, const int* ws, int S, int s_begin, int s_end,
                                           int normalize_mode, int out_S, int out_s0, int num_peers, int rank,
                                           float* const* corr_peers, float* const* mask_peers, uint32_t* const* flag_peers,
-                                          uint32_t epoch, void* workspace, size_t workspace_bytes, void* stream) {
+                                          uint32_t epoch, int partition, void* workspace, size_t workspace_bytes, void* stream) {
   if (!corr_peers || !mask_peers || !flag_peers) return RMVD_E_NULL;
   if (num_peers < 1 || num_peers > RMVD_MAX_PEERS || rank < 0 || rank >= num_peers) return RMVD_E_RANGE;
+  if (partition != RMVD_PARTITION_PLANES && partition != RMVD_PARTITION_TILES) return RMVD_E_MODE;
   PsweepPeers P{};
-  P.n = num_peers; P.rank = rank; P.epoch = epoch;
+  P.n = num_peers; P.rank = rank; P.epoch = epoch; P.by_tiles = (partition == RMVD_PARTITION_TILES);
   for (int g = 0; g < num_peers; ++g) {
     if (!corr_peers[g] || !mask_peers[g] || !flag_peers[g]) return RMVD_E_NULL;
     P.corr[g] = corr_peers[g]; P.mask[g] = mask_peers[g]; P.flags[g] = flag_peers[g];
@@ -491,6 +492,16 @@ extern "C" int rmvd_psweep_corr_fwd_peers(const float* feat_key, const float* co
   return psweep_corr_fwd_impl(feat_key, feat_src, intrinsics_key, intrinsics_src, src_to_key, invdepths, inv_stride, N, C, h, w, V, hs, ws,
                               S, s_begin, s_end, normalize_mode, P.corr[rank], P.mask[rank], out_S, out_s0, nullptr, nullptr, nullptr,
                               workspace, workspace_bytes, stream, &P);
+}
+
+// Copy-engine transport of the depth-slab gather: `rows` runs of `row_bytes` bytes, `pitch_bytes` apart in both buffers (a rank's
+// planes [lo, hi) of several [S,h,w] volumes), device to (peer) device.  One cudaMemcpy2DAsync: the copy engines move it at NVLink
+// speed without occupying an SM, so it overlaps the persistent plane-sweep kernel of the next view group (parallel.SlabGather).
+extern "C" int rmvd_copy_rows(void* dst, const void* src, size_t pitch_bytes, size_t row_bytes, int rows, void* stream) {
+  if (!dst || !src) return RMVD_E_NULL;
+  if (rows < 0 || row_bytes > pitch_bytes) return RMVD_E_SHAPE;
+  if (rows == 0 || row_bytes == 0) return RMVD_OK;
+  return (int)cudaMemcpy2DAsync(dst, pitch_bytes, src, pitch_bytes, row_bytes, (size_t)rows, cudaMemcpyDeviceToDevice, (cudaStream_t)stream);
 }
 
 // ---------------------------------------------------------------------------------------------------------

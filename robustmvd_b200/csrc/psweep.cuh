@@ -49,6 +49,7 @@ struct PsweepPeers {
   float* corr[RMVD_MAX_PEERS]; float* mask[RMVD_MAX_PEERS];
   unsigned* flags[RMVD_MAX_PEERS];
   unsigned epoch;
+  int by_tiles;                    // 0: the ranks split the planes (the caller's [s_begin, s_end)); 1: they split the work items (tiles), all planes each
 };
 // counter: 16 bytes of device memory: [0] work-item counter, [2] finished-CTA counter of the slab handshake
 int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, unsigned* counter, const PsweepPeers* peers, cudaStream_t st);

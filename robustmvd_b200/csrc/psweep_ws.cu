@@ -79,6 +79,7 @@ struct PeerArgs {                  // depth-slab mode (n > 0): peer-mapped outpu
   unsigned* flags[kMaxPeers];      // every rank's flag array [n] (symmetric memory): slot r = last epoch rank r completed
   unsigned epoch;                  // this call's epoch (monotone per communicator)
   unsigned* done_ctas;             // local counter of finished CTAs
+  int item_stride, item_offset;    // this launch works on items j * item_stride + item_offset (tile partition between the ranks); 1, 0 otherwise
 };
 
 struct __align__(16) PlaneTerm { float ed, id, md, zs; };   // e*d, i*d, m*d, 1/d of one plane (planesweep_corr.py:334,343,492)
@@ -604,7 +605,7 @@ __device__ bool load_schedule(const PsweepArgs& A, int n, float* sched) {
 }
 
 __device__ void planner(const PsweepArgs& A, const __nv_bfloat16* key_split, ChunkDesc* descs, unsigned bars, int tw, int th, int tiles_x,
-                        int tiles, int items, unsigned* counter, float* sched, PlanJob* job) {
+                        int tiles, int items, unsigned* counter, float* sched, PlanJob* job, int item_stride, int item_offset) {
   const int lane = threadIdx.x & 31;
   const int P = A.h * A.w, C = A.C;
   const unsigned bar_cready = bars + 8 * kBarCReady, bar_cfree = bars + 8 * kBarCFree, bar_jready = bars + 8 * kBarJobReady,
@@ -621,8 +622,11 @@ __device__ void planner(const PsweepArgs& A, const __nv_bfloat16* key_split, Chu
   bool sched_mono = false;
   // Work items are handed out in index order through a global counter (the first gridDim.x statically): tiles differ in cost
   // by a factor of three, and neighbouring CTAs keep working on neighbouring tiles (shared source rows in L2).
-  int item = blockIdx.x;
-  while (item < items) {
+  // `items` counts this launch's items; launch-local index j stands for item j * item_stride + item_offset (the ranks of a
+  // tile-partitioned depth-slab group take every item_stride-th item each)
+  int jitem = blockIdx.x;
+  while (jitem < items) {
+    const int item = jitem * item_stride + item_offset;
     unsigned nxt = 0;
     if (lane == 0) nxt = atomicAdd(counter, 1u);      // fetched now, needed after this item's chunks
     const ItemGeo g = item_geo(A, item, tiles, tiles_x);
@@ -708,7 +712,7 @@ __device__ void planner(const PsweepArgs& A, const __nv_bfloat16* key_split, Chu
       if (rem2 > 0) { const int k2 = (rem2 + len - 1) / len; len_hint = (rem2 + k2 - 1) / k2; }
     }
     prev_chunks = nchunks;
-    item = (int)__shfl_sync(kFullMask, nxt, 0) + (int)gridDim.x;
+    jitem = (int)__shfl_sync(kFullMask, nxt, 0) + (int)gridDim.x;
   }
 #ifdef RMVD_WS_STATS
   if (lane == 0) atomicAdd(&g_ws_stats[4], (unsigned long long)(clock64() - pl_t0));
@@ -1337,7 +1341,7 @@ __global__ void __launch_bounds__(kThreads, 1) psweep_ws_kernel(const PsweepArgs
   if (warp < 4) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;\n" ::"n"(kRegsControl));
     if (warp == 0) {
-      planner(A, key_split, descs, bars, tw, th, tiles_x, tiles, items, counter, sched, job);
+      planner(A, key_split, descs, bars, tw, th, tiles_x, tiles, items, counter, sched, job, PA.n > 0 ? PA.item_stride : 1, PA.n > 0 ? PA.item_offset : 0);
     } else if (warp == 1) {
       producer(descs, bars, smem_u32(stage), A.C);
     } else if (warp == 2) {
@@ -1484,14 +1488,19 @@ int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, uns
   const int tiles = tiles_x * tiles_y;
   const long long items_ll = (long long)tiles * A.N * nviews;
   if (items_ll > 0x7fff0000LL) return (int)cudaErrorInvalidValue;
-  const int items = (int)items_ll;
-  const unsigned grid = (unsigned)(items < num_sms ? items : num_sms);
+  int items = (int)items_ll;
   ws::PeerArgs PA{};
+  PA.item_stride = 1;
   if (peers && peers->n > 0) {
     if (peers->n > ws::kMaxPeers || peers->rank < 0 || peers->rank >= peers->n || A.dbg_ix0) return (int)cudaErrorInvalidValue;
     PA.n = peers->n; PA.rank = peers->rank; PA.epoch = peers->epoch; PA.done_ctas = counter + 2;
+    if (peers->by_tiles) {           // this rank's share of the items: rank, rank + n, rank + 2 n, ...
+      PA.item_stride = peers->n; PA.item_offset = peers->rank;
+      items = (items - peers->rank + peers->n - 1) / peers->n;
+    }
     for (int g = 0; g < peers->n; ++g) { PA.corr[g] = peers->corr[g]; PA.mask[g] = peers->mask[g]; PA.flags[g] = peers->flags[g]; }
   }
+  const unsigned grid = (unsigned)(items < num_sms ? (items > 0 ? items : 1) : num_sms);   // a rank without items still runs the handshake
 #ifdef RMVD_WS_STATS
   {
     unsigned long long z[32] = {0};

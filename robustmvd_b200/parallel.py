@@ -85,15 +85,23 @@ class SlabGather:
     alternate between consecutive calls: a rank that runs ahead writes set ``(k + 1) % 2`` while a slower rank still reads set
     ``k % 2``, and cannot start call ``k + 2`` before the slower rank has finished call ``k + 1`` (the handshake).
 
+    ``partition="tiles"``: the ranks split the (tile, sample, view) work items instead of the planes -- same result on every rank, and
+    the per-tile costs that do not shrink with the plane count (key tile, band planning, band rows) are divided too; at one frame
+    this is the partition that is faster than one GPU.
+
     Returns ``(corrs, masks, sampling_invdepths)`` with full ``[N,S,h,w]`` volumes per view, views of the current buffer set: valid
     until the call after next.  Falls back to ``planesweep_correlation_slabs`` (NCCL / gloo all-gather) when symmetric memory is
     not available (``mode == "all_gather"``), e.g. in the CPU tests of the host logic.
     """
 
-    def __init__(self, block, V, N, S, h, w, device, group=None):
+    def __init__(self, block, V, N, S, h, w, device, group=None, partition="planes", transport="stores", view_groups=None):
+        assert partition in ("planes", "tiles") and transport in ("stores", "copy")
         self.block, self.group = block, group
         self.G, self.rank = _world(group)
         self.S = S
+        self.partition = partition
+        self.transport = transport
+        self.view_groups = view_groups
         self.epoch = 0
         self.mode = "all_gather"
         self.bufs = None
@@ -112,12 +120,70 @@ class SlabGather:
                 torch.cuda.synchronize(device)
                 self.fh.barrier(channel=0)           # every rank's flags are zero before anyone's first epoch arrives
                 torch.cuda.synchronize(device)
-                self.mode = "peer_stores"
+                self.mode = "peer_stores" if transport == "stores" else "copy_engine"
+                if transport == "copy":
+                    self.side = torch.cuda.Stream(device=device)
+                    shape = (2, V, N, S, h, w)
+                    self.peer_bufs = [[hd.get_buffer(p, shape, torch.float32) for p in range(self.G)] for hd in self.hdls]
             except Exception as e:  # noqa: BLE001
                 self.bufs = None
                 self.why = repr(e)
 
+    def _call_copy(self, **kwargs):
+        """Depth slabs with the copy engines as the transport: the views are cut into groups, the slab of group k is computed by the
+        single-GPU kernel straight into this rank's symmetric buffer (at its plane offset) and then pushed to every peer's buffer by
+        one 2-D copy per peer on a side stream while the kernel of group k + 1 runs; a stream-ordered barrier between the ranks
+        closes the call.  The persistent kernel holds every SM, the copy engines hold none: the two overlap, which SM-issued peer
+        stores from the sampling loop do not (they stall the consumer warps, profiles/r02t)."""
+        from . import _lib
+        self.epoch += 1
+        k = self.epoch % 2
+        buf = self.bufs[k]
+        lo, hi = slab_range(self.S, self.G, self.rank)
+        srcs = list(kwargs.pop("feat_sources"))
+        Ts = list(kwargs.pop("source_to_key_transforms"))
+        Ks = kwargs.pop("intrinsics_sources", None)
+        V = len(srcs)
+        ng = self.view_groups or min(V, 4)
+        bounds = [round(i * V / ng) for i in range(ng + 1)]
+        main = torch.cuda.current_stream()
+        lib = _lib.load()
+        N, h, w = buf.shape[2], buf.shape[4], buf.shape[5]
+        plane = h * w * 4
+        pitch, row = self.S * plane, (hi - lo) * plane
+        inv = None
+        self.side.wait_stream(main)                  # the previous readers of this buffer set are ahead of us in stream order
+        for gi in range(ng):
+            v0, v1 = bounds[gi], bounds[gi + 1]
+            if v1 == v0:
+                continue
+            if hi > lo:
+                _, _, inv = self.block._forward_impl(
+                    feat_sources=srcs[v0:v1], source_to_key_transforms=Ts[v0:v1], intrinsics_sources=None if Ks is None else Ks[v0:v1],
+                    plane_range=(lo, hi), out=(buf[0, v0:v1], buf[1, v0:v1]), **kwargs)
+            ev = torch.cuda.Event()
+            ev.record(main)
+            self.side.wait_event(ev)
+            if hi > lo:
+                for c in range(2):                   # corr, mask: rows = (view, sample) volumes of the group
+                    off = ((c * V + v0) * N) * pitch + lo * plane
+                    for p in range(self.G):
+                        if p != self.rank:
+                            st = lib.rmvd_copy_rows(self.peer_bufs[k][p].data_ptr() + off, buf.data_ptr() + off, pitch, row, (v1 - v0) * N,
+                                                    self.side.cuda_stream)
+                            _lib.check(st, "rmvd_copy_rows")
+        with torch.cuda.stream(self.side):
+            self.hdls[k].barrier(channel=1)          # every rank's copies into every buffer are complete
+        main.wait_stream(self.side)
+        if inv is None:
+            inv = self.block.get_sampling_invdepths(kwargs.get("num_sampling_points"), kwargs.get("min_depth"), kwargs.get("max_depth"),
+                                                    kwargs.get("sampling_invdepths"), kwargs.get("sampling_type", "linear_invdepth"),
+                                                    device=buf.device)
+        return list(buf[0].unbind(0)), list(buf[1].unbind(0)), inv
+
     def __call__(self, **kwargs):
+        if self.mode == "copy_engine":
+            return self._call_copy(**kwargs)
         if self.mode != "peer_stores":
             return planesweep_correlation_slabs(self.block, self.group, **kwargs)
         self.epoch += 1
@@ -127,6 +193,9 @@ class SlabGather:
         peers = dict(rank=self.rank, epoch=self.epoch, corr=[int(p) for p in hdl.buffer_ptrs],
                      mask=[int(p) + half for p in hdl.buffer_ptrs], flags=[int(p) for p in self.fh.buffer_ptrs])
         lo, hi = slab_range(self.S, self.G, self.rank)
+        if self.partition == "tiles":               # every rank sweeps all planes of every G-th tile (RMVD_PARTITION_TILES)
+            lo, hi = 0, self.S
+            peers["partition"] = 1
         _, _, inv = self.block._forward_impl(plane_range=(lo, hi), peers=peers, **kwargs)
         return list(buf[0].unbind(0)), list(buf[1].unbind(0)), inv
 

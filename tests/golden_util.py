@@ -48,7 +48,8 @@ def check_planesweep_against_golden(g, corrs, masks, inv, ix0s=None, iy0s=None, 
 def check_mvs_variance_against_golden(g, var, tol=1e-4):
     if bool(g["large"]):
         ref = g["var_sub"]
-        assert np.abs(var.reshape(-1)[::SUB] - ref).max() <= tol * float(g["var_absmax"])
+        sub = int(g["sub"]) if "sub" in g.files else SUB      # full-size fixtures keep a coarser subsample
+        assert np.abs(var.reshape(-1)[::sub] - ref).max() <= tol * float(g["var_absmax"])
     else:
         ref = g["var"]
         assert np.abs(var - ref).max() <= tol * float(np.abs(ref).max())

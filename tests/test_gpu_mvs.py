@@ -232,3 +232,19 @@ def test_variance_kernels_agree_and_workspace_is_checked(cuda_lib):
     assert float((a - b).abs().max()) <= 2e-5 * float(a.abs().max())
     assert lib.rmvd_mvs_variance_fwd_ws(*args, _lib.ptr(b), D, 0, None, need, _lib.stream_ptr()) == -1          # RMVD_E_NULL
     assert lib.rmvd_mvs_variance_fwd_ws(*args, _lib.ptr(b), D, 0, _lib.ptr(ws), need - 1, _lib.stream_ptr()) == -4  # RMVD_E_WORKSPACE
+
+
+def test_cfg3_full_size_against_reference_golden(cuda_lib):
+    """BASELINE.json configs[2] at full size (DTU 224x304 features, C=32, 5 views, 192 planes) against the golden frozen from the
+    unmodified reference (tools/make_fullsize_golden.py): a stride-997 subsample of the 418 M-element variance volume within 1e-4 of
+    max|ref|, regressed depth within 1e-3, the integer depth index exact away from ties."""
+    from robustmvd_b200.blocks import utils as bu
+    case = cases.fullsize_mvs_case()
+    g = load_golden("mvs", case["name"])
+    var = bu.mvs_variance_volume(cu(case["feats"]), cu(case["proj"]), cu(case["depth"]))
+    sub = int(g["sub"])
+    got = npy(var.reshape(-1)[::sub])
+    assert np.abs(got - g["var_sub"]).max() <= 1e-4 * float(g["var_absmax"])
+    del var
+    r = bu.mvs_regress(cu(case["cost"]), cu(case["depth"]))
+    check_regress_against_golden(g, npy(r["depth"]), npy(r["confidence"]), npy(r["depth_index"]), npy(r["expected_index"]))

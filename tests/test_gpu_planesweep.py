@@ -257,3 +257,16 @@ def test_host_pipeline_stream_of_batches(cuda_lib):
                               source_to_key_transforms=x["Ts"], **kw)
         for v in range(V):
             assert torch.equal(x["out"][0, v], corrs[v].cpu()) and torch.equal(x["out"][1, v], masks[v].cpu())
+
+
+def test_cfg4_full_size_against_reference_golden(cuda_lib):
+    """BASELINE.json configs[3] at full size (ETH3D 96x144 features, C=256, 256 planes, 2 source views) against the golden frozen
+    from the unmodified reference (tools/make_fullsize_golden.py): masks, geometric masks and corner indices bit for bit, the
+    correlation on a stride-31 subsample within 1e-4 of max|ref|."""
+    case = cases.fullsize_planesweep_case()
+    g = load_golden("ps", case["name"])
+    corrs, masks, inv, dbg = _run_cuda(case)
+    check_planesweep_against_golden(g, corrs, masks, inv, dbg["ix0"], dbg["iy0"], dbg["geom"], tol=TOL)
+    corrs2, masks2, _, _ = _run_cuda(case, debug=False)           # the production kernel variant (no debug outputs)
+    for v in range(len(corrs)):
+        assert np.array_equal(masks2[v], masks[v]) and np.array_equal(corrs2[v], corrs[v])

@@ -123,3 +123,38 @@ def test_cvp_oracle_matches_reference(c):
                                        c["depth_planes"])
     assert np.abs(oc - g["cost"]).max() <= 2e-5 * np.abs(g["cost"]).max()
     assert np.abs(ow - g["warped"]).max() <= 2e-5 * np.abs(g["warped"]).max()
+
+
+def test_fullsize_cfg4_oracle_matches_golden():
+    """BASELINE.json configs[3] at full size (ETH3D 96x144 features, C=256, 256 planes, 2 views): the oracle against the golden of the
+    unmodified reference (tools/make_fullsize_golden.py) -- masks, geometric masks and corner indices bit for bit."""
+    case = cases.fullsize_planesweep_case()
+    g = load_golden("ps", case["name"])
+    corrs, masks, inv, dbg = oracle.planesweep_correlation(
+        case["feat_key"], case["intrinsics_key"], case["feat_sources"], case["transforms"], case["intrinsics_sources"],
+        return_debug=True, **case["kwargs"])
+    check_planesweep_against_golden(g, corrs, masks, inv, [d["ix0"] for d in dbg], [d["iy0"] for d in dbg],
+                                    [d["geom_mask"] for d in dbg], tol=1e-5)
+
+
+def test_fullsize_cfg3_oracle_matches_golden():
+    """BASELINE.json configs[2] at full size (DTU 224x304 features, C=32, 5 views, 192 planes): three 8-plane slabs of the oracle's
+    variance volume against the strided subsample of the reference's full volume, and the regression at full size."""
+    case = cases.fullsize_mvs_case()
+    g = load_golden("mvs", case["name"])
+    B, V, C, h, w = case["feats"].shape
+    D = case["depth"].shape[1]
+    sub, ref = int(g["sub"]), g["var_sub"]
+    idx = np.arange(ref.size, dtype=np.int64) * sub                      # flat index into [B,C,D,h,w]
+    d_of = (idx // (h * w)) % D
+    checked = 0
+    for d0 in (0, 96, 184):
+        var = oracle.mvs_variance(case["feats"], case["proj"], case["depth"][:, d0:d0 + 8])      # [B,C,8,h,w]
+        sel = (d_of >= d0) & (d_of < d0 + 8)
+        c_of, p_of = idx[sel] // (D * h * w), idx[sel] % (h * w)
+        got = var.reshape(C, 8, h * w)[c_of, d_of[sel] - d0, p_of]
+        assert np.abs(got - ref[sel]).max() <= 1e-5 * float(g["var_absmax"])
+        checked += int(sel.sum())
+    assert checked > 40000
+    d, c, i, e = oracle.mvs_regress(case["cost"], case["depth"])
+    check_regress_against_golden(g, d, c, i, e, rtol=1e-5)

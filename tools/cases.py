@@ -125,6 +125,18 @@ def grad_corrs(case, S):
     return [rng.standard_normal((n, S, h, w)).astype(np.float32) for _ in case["feat_sources"]]
 
 
+def fullsize_planesweep_case():
+    """BASELINE.json configs[3] at full size: ETH3D 768x1152 -> 96x144 features, C=256, 256 planes, 2 source views."""
+    c = syn.CFG4
+    return _ps("cfg4_eth3d_full", c["h"], c["w"], c["C"], syn.kitti_like_views(c["V"]), S=c["S"], seed=4004)
+
+
+def fullsize_mvs_case():
+    """BASELINE.json configs[2] at full size: DTU 896x1216 -> 224x304 features, C=32, 5 views, 192 planes."""
+    c = syn.CFG3
+    return dict(name="cfg3_dtu_full", **syn.mvs_inputs(c["h"], c["w"], c["C"], c["V"], c["D"]))
+
+
 def mvs_cases(include_large=True):
     cases = []
     cases.append(dict(name="mvs_small", **syn.mvs_inputs(12, 16, 8, 3, 8, seed=40, fx=20.0, min_depth=0.5, max_depth=1.5)))
