@@ -171,20 +171,36 @@ int rmvd_psweep_warp_fwd(const float* feat_src, const float* intrinsics_key, con
                          int normalize_mode, float* warped, float* mask, int out_S, int out_s0, void* stream);
 
 /*
+ * The state the reference block keeps after forward(): sampling points of one source view (planesweep_corr.py:489-512) --
+ * us, vs (source pixel coordinates, non-finite values replaced as :336-338), zs = 1 / invdepth, geom_mask (uint8, :499-506), all
+ * [N,S,h,w] -- and its epipolar coefficients (:228-300): coeff_pix [N,3,h,w] = (u_infs_h, v_infs_h, k_infs_h), coeff_m [N,3] =
+ * (m_u_h, m_v_h, m_k_h).  Either group may be NULL.  The fused correlation never materialises these; the Python block computes
+ * them lazily when `block.sampling_points[i].us` / `block.coeffs[i]` is read.
+ */
+int rmvd_sampling_points_fwd(const float* intrinsics_key, const float* intrinsics_src, const float* src_to_key,
+                             const float* invdepths, const int64_t* inv_stride_host, int N, int h, int w, int hs, int ws,
+                             int S, float* us, float* vs, float* zs, uint8_t* geom_mask, float* coeff_pix, float* coeff_m,
+                             void* stream);
+
+/*
  * TorchCorr.forward on caller-supplied sampling grids (planesweep_corr.py:152-195): grids [N,S,2,h,w] in
  * source pixels, geom_mask optional uint8 [N,S,h,w].  Outputs corr, mask float32 [N,S,h,w].
+ * padding_border: TorchCorr's constructor argument (:144-148): 0 = "zeros" (the block's use), 1 = "border" (coordinates clipped
+ * into the source map as ATen does, sampling mask all ones: mask = geom_mask).
  */
 int rmvd_corr_grid_fwd(const float* feat_key, const float* feat_src, const float* grids,
                        const uint8_t* geom_mask, int N, int C, int h, int w, int hs, int ws, int S,
-                       int normalize_mode, float* corr, float* mask, void* workspace, size_t workspace_bytes,
-                       void* stream);
+                       int normalize_mode, int padding_border, float* corr, float* mask, void* workspace,
+                       size_t workspace_bytes, void* stream);
 
 /*
- * warp() grid branch (planesweep_corr.py:49-104): x [K,C,hs,ws], grid [K,2,ho,wo] in source pixels,
- * padding_border: 0 = "zeros", 1 = "border".  out [K,C,ho,wo], mask [K,1,ho,wo].
+ * warp() grid branch (planesweep_corr.py:49-104): x [K / x_repeat,C,hs,ws], grid [K,2,ho,wo] in source pixels,
+ * padding_border: 0 = "zeros", 1 = "border".  out [K,C,ho,wo], mask [K,1,ho,wo].  x_repeat = 1: warp(); x_repeat = S with
+ * K = N * S: warp_multi() (:13-46) in one launch, grids k = n * S + s all sample image n (the reference's repeat of x, :33, is
+ * not materialised).
  */
 int rmvd_warp_grid_fwd(const float* x, const float* grid, int K, int C, int hs, int ws, int ho, int wo,
-                       int padding_border, float* out, float* mask, void* stream);
+                       int padding_border, int x_repeat, float* out, float* mask, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------
  * MVSNet family
@@ -274,6 +290,18 @@ int rmvd_softargmax_slab_fused(const float* const* cost_peers, const float* dept
  */
 int rmvd_soft_argmin_fwd(const float* volume, int B, int D, int h, int w, float window, float* prob,
                          float* expected_index, float* prob_map, float* entropy, void* stream);
+
+/*
+ * Plain reductions over D without a softmax: depth_regression (blocks/utils.py:271-274, `sum_d p[b,d,y,x] * values`) with
+ * values per plane [B,D] (mode RMVD_REDUCE_PLANE_VALUES, mvsnet.py:141) or per pixel [B,D,h,w] (RMVD_REDUCE_PIXEL_VALUES,
+ * cvp_mvsnet.py:168), and entropy (blocks/utils.py:67-68, `sum_d -v * log(clamp(v, 1e-9, 1))`, RMVD_REDUCE_ENTROPY, values unused).
+ * volume [B,D,h,w] -> out [B,h,w].
+ */
+#define RMVD_REDUCE_PLANE_VALUES 0
+#define RMVD_REDUCE_PIXEL_VALUES 1
+#define RMVD_REDUCE_ENTROPY 2
+int rmvd_volume_reduce_fwd(const float* volume, const float* values, int B, int D, int h, int w, int mode, float* out,
+                           void* stream);
 
 /*
  * CVP-MVSNet proj_cost (cvp_mvsnet_components.py:375-457): variance cost volume over PER-PIXEL depth

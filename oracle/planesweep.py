@@ -159,7 +159,7 @@ def grid_unnormalize(coord, size):
     return _fma32(t, F32(size) / _TWO, F32(-0.5))
 
 
-def bilinear_setup(us, vs, hs, ws):
+def bilinear_setup(us, vs, hs, ws, padding_mode="zeros"):
     """Sampling indices and weights of ``warp`` (planesweep_corr.py:85-93) + ATen bilinear grid_sample.
 
     Returns dict with integer corner ``ix0, iy0`` (int32, saturated to ``[-2, size]``), the four weights
@@ -171,6 +171,11 @@ def bilinear_setup(us, vs, hs, ws):
         yg = (_TWO * _f32(vs)) / F32(hs) - _ONE  # :88
         ix = grid_unnormalize(xg, ws)
         iy = grid_unnormalize(yg, hs)
+        if padding_mode == "border":
+            # ATen clip_coordinates (GridSampler.h): std::min(size - 1, std::max(coord, 0)); with the CPU's std::min / std::max a
+            # nan coordinate comes out as size - 1
+            ix = np.where(np.isnan(ix), F32(ws - 1), np.minimum(F32(ws - 1), np.maximum(ix, F32(0)))).astype(np.float32)
+            iy = np.where(np.isnan(iy), F32(hs - 1), np.minimum(F32(hs - 1), np.maximum(iy, F32(0)))).astype(np.float32)
         x0 = np.floor(ix)
         y0 = np.floor(iy)
         wx1 = ix - x0  # "w"
@@ -189,6 +194,8 @@ def bilinear_setup(us, vs, hs, ws):
     z = F32(0)
     msum = ((np.where(in_nw, nw, z) + np.where(in_ne, ne, z)) + np.where(in_sw, sw, z)) + np.where(in_se, se, z)
     samp_mask = (~(msum < F32(0.9999))) & (msum > 0)  # :101-102 (nan cannot occur: us/vs are finite)
+    if padding_mode == "border":
+        samp_mask = np.ones_like(samp_mask)           # :95-96: border padding -> the mask is all ones
     ix0 = np.clip(x0, -2, ws).astype(np.int32)
     iy0 = np.clip(y0, -2, hs).astype(np.int32)
     return dict(ix0=ix0, iy0=iy0, nw=nw, ne=ne, sw=sw, se=se, in_nw=in_nw, in_ne=in_ne, in_sw=in_sw,
@@ -204,8 +211,8 @@ def _l2_normalize(x, axis):
 # --------------------------------------------------------------------------------------
 # a7: TorchCorr
 # --------------------------------------------------------------------------------------
-def torch_corr(feat_ref, feat_src, us, vs, mask=None, normalize="dim", return_debug=False):
-    """planesweep_corr.py:152-195 (``TorchCorr.forward``, zeros padding), the reference's own algorithm:
+def torch_corr(feat_ref, feat_src, us, vs, mask=None, normalize="dim", return_debug=False, padding_mode="zeros"):
+    """planesweep_corr.py:152-195 (``TorchCorr.forward``, zeros or border padding), the reference's own algorithm:
     all-pairs correlation matrix, then bilinear sampling of that matrix at the S epipolar points.
 
     feat_ref ``[N,C,h,w]``, feat_src ``[N,C,hs,ws]``, us/vs ``[N,S,h,w]`` (= grids[:, :, 0/1]),
@@ -221,7 +228,7 @@ def torch_corr(feat_ref, feat_src, us, vs, mask=None, normalize="dim", return_de
     if normalize and normalize != "dim":  # :170-172
         fr = _l2_normalize(fr, 1)
         fs = _l2_normalize(fs, 1)
-    b = bilinear_setup(us, vs, hs, ws)
+    b = bilinear_setup(us, vs, hs, ws, padding_mode)
     corr = np.empty((N, S, h, w), np.float32)
     P = h * w
     for n in range(N):

@@ -16,10 +16,10 @@ EXPORTS = (
     "rmvd_abi_version", "rmvd_status_string", "rmvd_psweep_workspace_bytes", "rmvd_psweep_corr_fwd",
     "rmvd_psweep_corr_fwd_peers", "rmvd_psweep_corr_fwd_static", "rmvd_copy_rows",
     "rmvd_psweep_warp_fwd", "rmvd_psweep_bwd_workspace_bytes", "rmvd_psweep_corr_bwd",
-    "rmvd_corr_grid_fwd", "rmvd_warp_grid_fwd", "rmvd_mvs_variance_fwd", "rmvd_mvs_variance_fwd_ws",
+    "rmvd_corr_grid_fwd", "rmvd_warp_grid_fwd", "rmvd_sampling_points_fwd", "rmvd_mvs_variance_fwd", "rmvd_mvs_variance_fwd_ws",
     "rmvd_mvs_variance_workspace_bytes",
     "rmvd_homo_warp_fwd", "rmvd_mvs_regress_fwd", "rmvd_softargmax_partial", "rmvd_softargmax_combine",
-    "rmvd_softargmax_confidence", "rmvd_softargmax_slab_fused", "rmvd_soft_argmin_fwd", "rmvd_view_fusion_fwd", "rmvd_homography_groupcorr_fwd", "rmvd_homography_warp_fwd", "rmvd_vis_cost_volume_fwd", "rmvd_cvp_proj_cost_fwd", "rmvd_cvp_projections", "rmvd_debug_div_check",
+    "rmvd_softargmax_confidence", "rmvd_softargmax_slab_fused", "rmvd_soft_argmin_fwd", "rmvd_volume_reduce_fwd", "rmvd_view_fusion_fwd", "rmvd_homography_groupcorr_fwd", "rmvd_homography_warp_fwd", "rmvd_vis_cost_volume_fwd", "rmvd_cvp_proj_cost_fwd", "rmvd_cvp_projections", "rmvd_debug_div_check",
 )
 
 
@@ -49,8 +49,9 @@ def _declare(lib):
     lib.rmvd_psweep_corr_bwd.argtypes = [P, PP, P, PP, PP, P, PL] + [c_int] * 5 + [PI, PI] + [c_int] * 4 + \
         [P, c_int, c_int, P, PP, P, c_size_t, P]
     lib.rmvd_psweep_warp_fwd.argtypes = [P, P, P, P, P, PL] + [c_int] * 10 + [P, P, c_int, c_int, P]
-    lib.rmvd_corr_grid_fwd.argtypes = [P, P, P, P] + [c_int] * 8 + [P, P, P, c_size_t, P]
-    lib.rmvd_warp_grid_fwd.argtypes = [P, P] + [c_int] * 7 + [P, P, P]
+    lib.rmvd_sampling_points_fwd.argtypes = [P, P, P, P, PL] + [c_int] * 6 + [P] * 7
+    lib.rmvd_corr_grid_fwd.argtypes = [P, P, P, P] + [c_int] * 9 + [P, P, P, c_size_t, P]
+    lib.rmvd_warp_grid_fwd.argtypes = [P, P] + [c_int] * 8 + [P, P, P]
     lib.rmvd_mvs_variance_fwd.argtypes = [P, P, P] + [c_int] * 8 + [P, c_int, c_int, P]
     lib.rmvd_mvs_variance_workspace_bytes.restype = c_size_t
     lib.rmvd_mvs_variance_workspace_bytes.argtypes = [c_int] * 5
@@ -62,6 +63,7 @@ def _declare(lib):
     lib.rmvd_softargmax_confidence.argtypes = [P, P] + [c_int] * 6 + [P, P]
     lib.rmvd_softargmax_slab_fused.argtypes = [PP, P] + [c_int] * 6 + [PP, PP, ctypes.c_uint32, P, P, P, P, P, P]
     lib.rmvd_soft_argmin_fwd.argtypes = [P] + [c_int] * 4 + [c_float, P, P, P, P, P]
+    lib.rmvd_volume_reduce_fwd.argtypes = [P, P] + [c_int] * 5 + [P, P]
     lib.rmvd_view_fusion_fwd.argtypes = [PP, PP, PP] + [c_int] * 5 + [P, P, P, P]
     lib.rmvd_homography_groupcorr_fwd.argtypes = [P, P, P, PL] + [c_int] * 6 + [P, P]
     lib.rmvd_homography_warp_fwd.argtypes = [P, P, PL] + [c_int] * 5 + [P, P]

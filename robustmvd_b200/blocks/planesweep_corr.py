@@ -103,46 +103,51 @@ def _inv_strides(inv, N):
     return st
 
 
+def _pixel_centres(h_ref, w_ref, device):
+    yy, xx = torch.meshgrid(torch.arange(h_ref, device=device), torch.arange(w_ref, device=device), indexing="ij")
+    return torch.stack((xx + 0.5, yy + 0.5), 0).float()          # 2, h_ref, w_ref  (:68-77)
+
+
+def _warp_launch(x, grid, K, x_repeat, padding_mode):
+    """``x [K / x_repeat, C, hs, ws]``, ``grid [K, 2, ho, wo]`` -> ``out [K, C, ho, wo]``, ``mask [K, 1, ho, wo]``."""
+    C, hs, ws = x.shape[1:]
+    ho, wo = grid.shape[-2:]
+    out = torch.empty((K, C, ho, wo), dtype=torch.float32, device=x.device)
+    mask = torch.empty((K, 1, ho, wo), dtype=torch.float32, device=x.device)
+    lib = _lib.load()
+    step = max(x_repeat, 65535 // x_repeat * x_repeat)        # gridDim.y carries K: chunk very large K on image boundaries
+    for k0 in range(0, K, step):
+        k1 = min(K, k0 + step)
+        st = lib.rmvd_warp_grid_fwd(_lib.ptr(x[k0 // x_repeat:]), _lib.ptr(grid[k0:k1]), k1 - k0, C, hs, ws, ho, wo,
+                                    1 if padding_mode == "border" else 0, x_repeat, _lib.ptr(out[k0:k1]),
+                                    _lib.ptr(mask[k0:k1]), _lib.stream_ptr())
+        _lib.check(st, "rmvd_warp_grid_fwd")
+    return out, mask
+
+
 def warp(x, offset=None, grid=None, padding_mode="border"):
     """planesweep_corr.py:49-104.  ``x [N,C,H,W]``; ``grid [N,2,h_out,w_out]`` in source pixels (or ``offset``
     relative to pixel centres).  Returns ``(output [N,C,h_out,w_out], mask [N,1,h_out,w_out])``."""
     assert (offset is None and grid is not None) or (grid is None and offset is not None)
     assert padding_mode in ("border", "zeros")
     if offset is not None:
-        h_ref, w_ref = offset.shape[-2:]
-        yy, xx = torch.meshgrid(torch.arange(h_ref, device=x.device), torch.arange(w_ref, device=x.device),
-                                indexing="ij")
-        grid = torch.stack((xx + 0.5, yy + 0.5), 0).float().unsqueeze(0).repeat(x.shape[0], 1, 1, 1) + offset
+        grid = _pixel_centres(offset.shape[-2], offset.shape[-1], x.device).unsqueeze(0) + offset
     x = _f32c(x)
-    grid = _f32c(grid)
-    K, C, hs, ws = x.shape
-    ho, wo = grid.shape[-2:]
-    out = torch.empty((K, C, ho, wo), dtype=torch.float32, device=x.device)
-    mask = torch.empty((K, 1, ho, wo), dtype=torch.float32, device=x.device)
-    lib = _lib.load()
-    # gridDim.y carries K: chunk very large K (TorchCorr-style K = N*h*w use)
-    for k0 in range(0, K, 65535):
-        k1 = min(K, k0 + 65535)
-        st = lib.rmvd_warp_grid_fwd(_lib.ptr(x[k0:k1]), _lib.ptr(grid[k0:k1]), k1 - k0, C, hs, ws, ho, wo,
-                                    1 if padding_mode == "border" else 0, _lib.ptr(out[k0:k1]),
-                                    _lib.ptr(mask[k0:k1]), _lib.stream_ptr())
-        _lib.check(st, "rmvd_warp_grid_fwd")
-    return out, mask
+    return _warp_launch(x, _f32c(grid), x.shape[0], 1, padding_mode)
 
 
 def warp_multi(x, offsets=None, grids=None, padding_mode="border"):
-    """planesweep_corr.py:13-46: ``x [N,C,hs,ws]``, ``grids [N,S,2,h,w]`` -> ``[N,S,C,h,w]``, ``[N,S,h,w]``.
-    The S-fold repeat of the source (:33) is not materialised: each plane samples the same source map."""
+    """planesweep_corr.py:13-46: ``x [N,C,hs,ws]``, ``grids [N,S,2,h,w]`` -> ``[N,S,C,h,w]``, ``[N,S,h,w]`` in ONE launch:
+    the S-fold repeat of the source (:33) is not materialised, grid ``n * S + s`` samples image ``n``."""
     assert (offsets is None and grids is not None) or (grids is None and offsets is not None)
+    assert padding_mode in ("border", "zeros")
     loc = offsets if offsets is not None else grids
     N, S, _, H, W = loc.shape
-    outs, masks = [], []
-    for s in range(S):
-        o, m = warp(x, offset=None if offsets is None else loc[:, s], grid=None if grids is None else loc[:, s],
-                    padding_mode=padding_mode)
-        outs.append(o)
-        masks.append(m[:, 0])
-    return torch.stack(outs, 1), torch.stack(masks, 1)
+    if offsets is not None:
+        loc = _pixel_centres(H, W, x.device).view(1, 1, 2, H, W) + offsets
+    x = _f32c(x)
+    out, mask = _warp_launch(x, _f32c(loc).view(N * S, 2, H, W), N * S, S, padding_mode)
+    return out.view(N, S, x.shape[1], H, W), mask.view(N, S, H, W)
 
 
 class WarpOnlyCorr(nn.Module):
@@ -165,7 +170,7 @@ class WarpOnlyCorr(nn.Module):
 
 
 class TorchCorr(nn.Module):
-    """planesweep_corr.py:143-195 on caller-supplied grids: ``rmvd_corr_grid_fwd`` (zeros padding)."""
+    """planesweep_corr.py:143-195 on caller-supplied grids: ``rmvd_corr_grid_fwd`` (zeros or border padding)."""
 
     def __init__(self, normalize=False, padding_mode="zeros"):
         super().__init__()
@@ -173,7 +178,7 @@ class TorchCorr(nn.Module):
         self.padding_mode = padding_mode
         if isinstance(self.normalize, str):
             assert self.normalize in ["dim", "before"]
-        assert padding_mode == "zeros", "the fused correlation kernel implements zeros padding (the block's only use)"
+        assert padding_mode in ("zeros", "border")
 
     def forward(self, feat_ref, feat_src, grids=None, mask=None):
         feat_ref, feat_src, grids = _f32c(feat_ref), _f32c(feat_src), _f32c(grids)
@@ -188,8 +193,8 @@ class TorchCorr(nn.Module):
         nb = lib.rmvd_psweep_workspace_bytes(N, C, h, w, 1, _lib.int_array([hs]), _lib.int_array([ws]))
         wsp = _workspace(nb, dev)
         st = lib.rmvd_corr_grid_fwd(_lib.ptr(feat_ref), _lib.ptr(feat_src), _lib.ptr(grids), _lib.ptr(m8), N, C, h, w,
-                                    hs, ws, S, _corr_norm_mode(self.normalize), _lib.ptr(corr), _lib.ptr(cmask),
-                                    _lib.ptr(wsp), wsp.numel(), _lib.stream_ptr())
+                                    hs, ws, S, _corr_norm_mode(self.normalize), 1 if self.padding_mode == "border" else 0,
+                                    _lib.ptr(corr), _lib.ptr(cmask), _lib.ptr(wsp), wsp.numel(), _lib.stream_ptr())
         _lib.check(st, "rmvd_corr_grid_fwd")
         return corr, cmask
 
@@ -223,6 +228,116 @@ class _CorrFunction(torch.autograd.Function):
         return (None, None, None, gkey, *gsrcs)
 
 
+class _LazyView:
+    """Per-source-view state of the reference block (planesweep_corr.py:389-394), materialised on first access by
+    ``rmvd_sampling_points_fwd``: the fused correlation never writes sampling points or coefficients."""
+
+    def __init__(self, calib):
+        self._calib = calib          # (Kk, Ks_v, T_v, inv_c, N, h, w, hs, ws, S)
+        self._pts = None
+        self._co = None
+
+    def _run(self, points):
+        Kk, Ks, T, inv_c, N, h, w, hs, ws, S = self._calib
+        dev = Kk.device
+        ist = _lib.i64_array(_inv_strides(inv_c, N))
+        us = vs = zs = mask = pix = mvec = None
+        if points:
+            us = torch.empty((N, S, h, w), dtype=torch.float32, device=dev)
+            vs, zs = torch.empty_like(us), torch.empty_like(us)
+            mask = torch.empty((N, S, h, w), dtype=torch.uint8, device=dev)
+        else:
+            pix = torch.empty((N, 3, h, w), dtype=torch.float32, device=dev)
+            mvec = torch.empty((N, 3), dtype=torch.float32, device=dev)
+        st = _lib.load().rmvd_sampling_points_fwd(_lib.ptr(Kk), _lib.ptr(Ks), _lib.ptr(T), _lib.ptr(inv_c), ist, N, h, w, hs, ws, S,
+                                                  _lib.ptr(us), _lib.ptr(vs), _lib.ptr(zs), _lib.ptr(mask), _lib.ptr(pix), _lib.ptr(mvec),
+                                                  _lib.stream_ptr())
+        _lib.check(st, "rmvd_sampling_points_fwd")
+        if points:
+            self._pts = (us, vs, zs, mask.bool())
+        else:
+            self._co = (pix, mvec)
+
+    def points(self):
+        if self._pts is None:
+            self._run(True)
+        return self._pts
+
+    def coeffs(self):
+        if self._co is None:
+            self._run(False)
+        return self._co
+
+
+class EpipolarSamplingPoints:
+    """planesweep_corr.py:352-368: ``us``, ``vs``, ``zs`` float32 and ``mask`` bool, all ``[N,S,h,w]`` (lazily computed)."""
+
+    def __init__(self, lazy):
+        self._lazy = lazy
+        _, _, _, _, _, h, w, _, _, S = lazy._calib
+        self.height, self.width, self._num = h, w, S
+
+    us = property(lambda self: self._lazy.points()[0])
+    vs = property(lambda self: self._lazy.points()[1])
+    zs = property(lambda self: self._lazy.points()[2])
+    mask = property(lambda self: self._lazy.points()[3])
+
+    @property
+    def num(self):
+        return self._num
+
+    def get_uvs(self):
+        return torch.stack((self.us, self.vs), 2)  # (N, S, 2, H, W)
+
+
+class EpipolarCoeffs:
+    """planesweep_corr.py:198-331 (the attributes and derived properties; ``from_calib`` runs inside the kernels)."""
+
+    def __init__(self, lazy):
+        self._lazy = lazy
+        _, _, _, _, _, h, w, _, _, _ = lazy._calib
+        self.height, self.width, self.eps = h, w, 1e-9
+        self._u_infs = self._v_infs = self._z_poles = self._epipole = None
+
+    u_infs_h = property(lambda self: self._lazy.coeffs()[0][:, 0:1])
+    v_infs_h = property(lambda self: self._lazy.coeffs()[0][:, 1:2])
+    k_infs_h = property(lambda self: self._lazy.coeffs()[0][:, 2:3])
+    m_u_h = property(lambda self: self._lazy.coeffs()[1][:, 0].reshape(-1, 1, 1, 1))
+    m_v_h = property(lambda self: self._lazy.coeffs()[1][:, 1].reshape(-1, 1, 1, 1))
+    m_k_h = property(lambda self: self._lazy.coeffs()[1][:, 2].reshape(-1, 1, 1, 1))
+
+    @staticmethod
+    def _finite(x):                                   # :303-304, :311-312
+        x = x.clone()
+        bad = torch.isinf(x)
+        x[bad] = 1e9 * torch.sign(x)[bad]
+        return x
+
+    @property
+    def u_infs(self):
+        if self._u_infs is None:
+            self._u_infs = self._finite(self.u_infs_h / self.k_infs_h)
+        return self._u_infs
+
+    @property
+    def v_infs(self):
+        if self._v_infs is None:
+            self._v_infs = self._finite(self.v_infs_h / self.k_infs_h)
+        return self._v_infs
+
+    @property
+    def epipole(self):
+        if self._epipole is None:
+            self._epipole = (self.m_u_h / self.m_k_h, self.m_v_h / self.m_k_h)
+        return self._epipole
+
+    @property
+    def z_poles(self):
+        if self._z_poles is None:
+            self._z_poles = -(self.m_k_h / self.k_infs_h)
+        return self._z_poles
+
+
 class PlanesweepCorrelation(nn.Module):
     """planesweep_corr.py:371-521.  ``forward`` returns ``(corrs, masks, sampling_invdepths)`` like the reference.
 
@@ -243,11 +358,15 @@ class PlanesweepCorrelation(nn.Module):
         self.corrs = []
         self.masks = []
         self.debug = None
+        self.coeffs = []               # per source view, like the reference's attributes of the same names (:389-391),
+        self.sampling_points = []      # computed on first read of an attribute (rmvd_sampling_points_fwd)
 
     def reset(self):
         self.corrs = []
         self.masks = []
         self.debug = None
+        self.coeffs = []
+        self.sampling_points = []
 
     @torch.no_grad()
     def get_sampling_invdepths(self, num_sampling_points=None, min_depth=None, max_depth=None,
@@ -372,6 +491,9 @@ class PlanesweepCorrelation(nn.Module):
         ws = [f.shape[3] for f in srcs]
         ist = _lib.i64_array(_inv_strides(inv_c, N))
         lib = _lib.load()
+        lazy = [_LazyView((Kk, Ks[v], Ts[v], inv_c, N, h, w, hs[v], ws[v], S)) for v in range(V)]
+        self.coeffs = [EpipolarCoeffs(z) for z in lazy]
+        self.sampling_points = [EpipolarSamplingPoints(z) for z in lazy]
         if V == 0:
             return self.corrs, self.masks, inv
         if peers is not None:

@@ -14,8 +14,16 @@ def _f32c(t):
     return t.detach().to(torch.float32).contiguous()
 
 
+def _forward_only(name, *tensors):
+    """These wrappers have no autograd node (the reference differentiates through torch ops): refuse, loudly, to return a tensor
+    without a graph to a caller that needs gradients (the correlation block and LearnedFusion do have differentiable paths)."""
+    if torch.is_grad_enabled() and any(isinstance(t, torch.Tensor) and t.requires_grad for t in tensors):
+        raise _lib.RmvdError(f"{name}: forward only -- an input requires grad; call it under torch.no_grad() or detach the inputs")
+
+
 def homo_warp(src_feat, src_proj, ref_proj_inv, depth_values, return_indices=False):
     """utils.py:222-268: ``src_feat [B,C,H,W]``, projections ``[B,4,4]``, ``depth_values [B,D]`` -> ``[B,C,D,H,W]``."""
+    _forward_only("homo_warp", src_feat, src_proj, ref_proj_inv, depth_values)
     src_feat, src_proj, ref_proj_inv, depth_values = map(_f32c, (src_feat, src_proj, ref_proj_inv, depth_values))
     B, C, H, W = src_feat.shape
     D = depth_values.shape[1]
@@ -35,6 +43,7 @@ def homo_warp(src_feat, src_proj, ref_proj_inv, depth_values, return_indices=Fal
 def mvs_variance_volume(feats, proj_mats, depth_values, plane_range=None):
     """mvsnet.py:123-136 fused with homo_warp: ``feats [B,V,C,h,w]`` (view 0 = key), ``proj_mats [B,V,4,4]`` (view 0
     already inverted), ``depth_values [B,D]`` -> variance ``[B,C,D,h,w]`` (or the ``plane_range`` slab of D)."""
+    _forward_only("mvs_variance_volume", feats, proj_mats, depth_values)
     feats, proj_mats, depth_values = map(_f32c, (feats, proj_mats, depth_values))
     B, V, C, h, w = feats.shape
     D = depth_values.shape[1]
@@ -52,6 +61,7 @@ def mvs_variance_volume(feats, proj_mats, depth_values, plane_range=None):
 def mvs_regress(cost_reg, depth_values, return_prob=False):
     """mvsnet.py:140-160 in one pass: ``cost_reg [B,D,h,w]`` (pre-softmax), ``depth_values [B,D]`` ->
     dict(depth, confidence, depth_index (int64), expected_index[, prob])."""
+    _forward_only("mvs_regress", cost_reg, depth_values)
     cost_reg, depth_values = _f32c(cost_reg), _f32c(depth_values)
     B, D, h, w = cost_reg.shape
     dev = cost_reg.device
@@ -70,17 +80,31 @@ def mvs_regress(cost_reg, depth_values, return_prob=False):
     return out
 
 
+def _volume_reduce(volume, values, mode):
+    volume = _f32c(volume)
+    B, D, h, w = volume.shape
+    out = torch.empty((B, h, w), dtype=torch.float32, device=volume.device)
+    st = _lib.load().rmvd_volume_reduce_fwd(_lib.ptr(volume), _lib.ptr(values), B, D, h, w, mode, _lib.ptr(out), _lib.stream_ptr())
+    _lib.check(st, "rmvd_volume_reduce_fwd")
+    return out
+
+
 def depth_regression(p, depth_values):
-    """utils.py:271-274: ``sum_d p[:,d] * depth_values[:,d]`` for an already normalised ``p [B,D,h,w]``.
-    Runs the regression kernel on ``log p`` (softmax(log p) = p for a normalised p)."""
-    p = _f32c(p)
+    """utils.py:271-274: ``sum_d p[:,d] * depth_values[:,d]`` for ``p [B,D,h,w]`` (normalised or not: no softmax is applied) and
+    ``depth_values [B,D]`` (mvsnet.py:141), ``[D]`` or per-pixel ``[B,D,h,w]`` (cvp_mvsnet.py:168)."""
+    _forward_only("depth_regression", p, depth_values)
     if depth_values.ndim == 1:
         depth_values = depth_values[None].expand(p.shape[0], -1)
-    return mvs_regress(torch.log(p.clamp_min(1e-38)), depth_values)["depth"]
+    if depth_values.ndim == 4:
+        assert tuple(depth_values.shape) == tuple(p.shape)
+        return _volume_reduce(p, _f32c(depth_values), 1)
+    assert depth_values.ndim == 2 and depth_values.shape[1] == p.shape[1]
+    return _volume_reduce(p, _f32c(depth_values.expand(p.shape[0], -1)), 0)
 
 
 def soft_argmin(volume, dim, keepdim=False, window=None):
     """utils.py:51-64 along ``dim`` = 1 of ``[B,D,h,w]``."""
+    _forward_only("soft_argmin", volume)
     assert dim == 1 and volume.ndim == 4, "the kernel reduces dim 1 of a [B,D,h,w] volume"
     volume = _f32c(volume)
     B, D, h, w = volume.shape
@@ -97,15 +121,10 @@ def soft_argmin(volume, dim, keepdim=False, window=None):
 
 
 def entropy(volume, dim, keepdim=False):
-    """utils.py:67-68 for a probability volume ``[B,D,h,w]`` along dim 1 (softmax(log p) = p)."""
+    """utils.py:67-68: ``sum_d -v * log(clamp(v, 1e-9, 1))`` along dim 1 of ``[B,D,h,w]`` (no normalisation, as in the reference)."""
     assert dim == 1 and volume.ndim == 4
-    volume = _f32c(volume)
-    B, D, h, w = volume.shape
-    eidx = torch.empty((B, h, w), dtype=torch.float32, device=volume.device)
-    ent = torch.empty_like(eidx)
-    st = _lib.load().rmvd_soft_argmin_fwd(_lib.ptr(torch.log(volume.clamp_min(1e-38))), B, D, h, w, -1.0, None,
-                                          _lib.ptr(eidx), None, _lib.ptr(ent), _lib.stream_ptr())
-    _lib.check(st, "rmvd_soft_argmin_fwd")
+    _forward_only("entropy", volume)
+    ent = _volume_reduce(volume, None, 2)
     return ent.unsqueeze(1) if keepdim else ent
 
 

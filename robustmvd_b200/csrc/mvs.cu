@@ -674,6 +674,33 @@ __global__ void __launch_bounds__(256) soft_argmin_kernel(const float* __restric
   if (entropy) entropy[o] = ent;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Plain reductions over D of a [B,D,h,w] volume, no softmax: depth_regression (blocks/utils.py:271-274: sum_d p * depth, depth
+// values per plane [B,D] or per pixel [B,D,h,w] as cvp_mvsnet.py:168 passes them) and entropy (:67-68:
+// sum_d -v * log(clamp(v, 1e-9, 1))).  Thread = pixel, lanes = adjacent pixels (128-byte rows), 4 planes in flight.
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) volume_reduce_kernel(const float* __restrict__ vol, const float* __restrict__ values, int D, int P,
+                                                            int mode, float* __restrict__ out) {
+  const int b = blockIdx.y;
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= P) return;
+  const float* v = vol + (size_t)b * D * P + p;
+  float acc = 0.f;
+  if (mode == 2) {                                   // entropy
+    for (int d = 0; d < D; ++d) {
+      const float x = __ldg(v + (size_t)d * P);
+      acc = fadd(acc, fmul(-x, logf(fminf(fmaxf(x, 1e-9f), 1.0f))));
+    }
+  } else if (mode == 1) {                            // per-pixel values [B,D,h,w]
+    const float* q = values + (size_t)b * D * P + p;
+    for (int d = 0; d < D; ++d) acc = fadd(acc, fmul(__ldg(v + (size_t)d * P), __ldg(q + (size_t)d * P)));
+  } else {                                           // per-plane values [B,D]
+    const float* q = values + (size_t)b * D;
+    for (int d = 0; d < D; ++d) acc = fadd(acc, fmul(__ldg(v + (size_t)d * P), __ldg(q + d)));
+  }
+  out[(size_t)b * P + p] = acc;
+}
+
 }  // namespace rmvd
 
 using namespace rmvd;
@@ -913,5 +940,16 @@ extern "C" int rmvd_cvp_proj_cost_fwd(const float* feats, const float* proj, con
   dim3 grid((unsigned)((tot + 255) / 256), (C + kCh - 1) / kCh, B);
   mvs_variance_kernel<kCh, true><<<grid, 256, 0, (cudaStream_t)stream>>>(feats, proj, depth_hypos, B, Vt, C, h, w, D, 0, D,
                                                                             cost, D, 0);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int rmvd_volume_reduce_fwd(const float* volume, const float* values, int B, int D, int h, int w, int mode, float* out,
+                                      void* stream) {
+  if (!volume || !out || (mode != RMVD_REDUCE_ENTROPY && !values)) return RMVD_E_NULL;
+  if (B <= 0 || D <= 0 || h <= 0 || w <= 0 || B > 65535) return RMVD_E_SHAPE;
+  if (mode < 0 || mode > 2) return RMVD_E_MODE;
+  const int P = h * w;
+  dim3 grid((P + 255) / 256, B);
+  volume_reduce_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(volume, values, D, P, mode, out);
   return (int)cudaGetLastError();
 }

@@ -136,9 +136,13 @@ __global__ void __launch_bounds__(kWarps * 32) psweep_corr_kernel(const PsweepAr
           const float d = A.invd[n * A.ist[0] + s * A.ist[1] + yi * A.ist[2] + xi * A.ist[3]];
           epi_sample(E, ep, d, us, vs, geom);
         }
-        const float ix = pix_to_unnorm(us, ws), iy = pix_to_unnorm(vs, hs);
+        float ix = pix_to_unnorm(us, ws), iy = pix_to_unnorm(vs, hs);
+        if (kFromGrid && A.border) {   // ATen clip_coordinates with the CPU's std::min / std::max: nan -> size - 1
+          ix = isnan(ix) ? (float)(ws - 1) : fminf((float)(ws - 1), fmaxf(ix, 0.f));
+          iy = isnan(iy) ? (float)(hs - 1) : fminf((float)(hs - 1), fmaxf(iy, 0.f));
+        }
         const Bilinear b = bilinear_setup(ix, iy, hs, ws);
-        valid = sampling_mask(b.msum) && geom;
+        valid = ((kFromGrid && A.border) || sampling_mask(b.msum)) && geom;
         wnw = b.nw; wne = b.ne; wsw = b.sw; wse = b.se;
         const int x0 = sat_index(b.x0f, ws), y0 = sat_index(b.y0f, hs);
         const int x0c = clampi(x0, 0, ws - 1), x1c = clampi(x0 + 1, 0, ws - 1);
@@ -295,16 +299,16 @@ __global__ void __launch_bounds__(256) psweep_warp_kernel(const WarpArgs A) {
 // warp() grid branch (planesweep_corr.py:49-104) for arbitrary images: thread = one output pixel.
 // ---------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) warp_grid_kernel(const float* __restrict__ x, const float* __restrict__ grid,
-                                                        int C, int hs, int ws, int Po, int border,
+                                                        int C, int hs, int ws, int Po, int border, int x_repeat,
                                                         float* __restrict__ out, float* __restrict__ mask) {
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   const int k = blockIdx.y;
   if (p >= Po) return;
   const float us = grid[((size_t)k * 2) * Po + p], vs = grid[((size_t)k * 2 + 1) * Po + p];
   float ix = pix_to_unnorm(us, ws), iy = pix_to_unnorm(vs, hs);
-  if (border) {  // ATen clip_coordinates: min(size - 1, max(coord, 0))
-    ix = fminf((float)(ws - 1), fmaxf(ix, 0.f));
-    iy = fminf((float)(hs - 1), fmaxf(iy, 0.f));
+  if (border) {  // ATen clip_coordinates: min(size - 1, max(coord, 0)); with the CPU's std::min / std::max a nan becomes size - 1
+    ix = isnan(ix) ? (float)(ws - 1) : fminf((float)(ws - 1), fmaxf(ix, 0.f));
+    iy = isnan(iy) ? (float)(hs - 1) : fminf((float)(hs - 1), fmaxf(iy, 0.f));
   }
   const Bilinear b = bilinear_setup(ix, iy, hs, ws);
   const int x0 = sat_index(b.x0f, ws), y0 = sat_index(b.y0f, hs);
@@ -312,7 +316,7 @@ __global__ void __launch_bounds__(256) warp_grid_kernel(const float* __restrict_
   const int y0c = clampi(y0, 0, hs - 1), y1c = clampi(y0 + 1, 0, hs - 1);
   const int o_nw = y0c * ws + x0c, o_ne = y0c * ws + x1c, o_sw = y1c * ws + x0c, o_se = y1c * ws + x1c;
   const int Ps = hs * ws;
-  const float* xs = x + (size_t)k * C * Ps;
+  const float* xs = x + (size_t)(k / x_repeat) * C * Ps;   // warp_multi: x_repeat consecutive grids sample the same image (:33)
   for (int c = 0; c < C; ++c) {
     const float* sc = xs + (size_t)c * Ps;
     out[((size_t)k * C + c) * Po + p] =
@@ -556,7 +560,7 @@ extern "C" int rmvd_psweep_corr_fwd_static(const float* feat_key, const float* c
 
 extern "C" int rmvd_corr_grid_fwd(const float* feat_key, const float* feat_src, const float* grids,
                                   const uint8_t* geom_mask, int N, int C, int h, int w, int hs, int ws, int S,
-                                  int normalize_mode, float* corr, float* mask, void* workspace,
+                                  int normalize_mode, int padding_border, float* corr, float* mask, void* workspace,
                                   size_t workspace_bytes, void* stream) {
   if (!feat_key || !feat_src || !grids || !corr || !mask) return RMVD_E_NULL;
   if (N <= 0 || C <= 0 || h <= 0 || w <= 0 || S <= 0 || hs <= 0 || ws <= 0 || hs >= 32768 || ws >= 32768)
@@ -572,11 +576,58 @@ extern "C" int rmvd_corr_grid_fwd(const float* feat_key, const float* feat_src, 
   A.src[0] = (const float*)workspace;
   A.grids = grids;
   A.grid_mask = geom_mask;
+  A.border = padding_border;
   A.hs[0] = hs; A.ws[0] = ws;
   A.N = N; A.C = C; A.h = h; A.w = w; A.S = S; A.s_begin = 0; A.s_end = S;
   A.norm = normalize_mode; A.out_S = S; A.out_s0 = 0; A.v0 = 0;
   A.corr = corr; A.mask = mask;
   return dispatch_corr<true>(A, 1, st);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// What the reference block leaves on itself after forward() (planesweep_corr.py:389-394, :436-462, :489-512): the homogeneous
+// epipolar terms of every key pixel and the sampling points us / vs / zs / geometric mask of every (plane, pixel), materialised on
+// request only (the fused correlation never writes them).  Thread = (plane, pixel); every value through the exact chain of common.cuh.
+// ---------------------------------------------------------------------------------------------------------
+namespace rmvd {
+__global__ void __launch_bounds__(256) sampling_points_kernel(const float* __restrict__ Kk, const float* __restrict__ Ks, const float* __restrict__ T,
+                                                              const float* __restrict__ invd, long long i0, long long i1, long long i2, long long i3,
+                                                              int h, int w, int hs, int ws, int S, float* __restrict__ us, float* __restrict__ vs,
+                                                              float* __restrict__ zs, uint8_t* __restrict__ mask, float* __restrict__ pix,
+                                                              float* __restrict__ mvec) {
+  const int n = blockIdx.y, P = h * w;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)S * P) return;
+  const int s = (int)(idx / P), p = (int)(idx - (long long)s * P);
+  const int yi = p / w, xi = p - yi * w;
+  const Epi E = epi_from_calib(Kk + n * 9, Ks + n * 9, T + n * 16, h, w, hs, ws);
+  const EpiPix px = epi_pixel(E, xi, yi);
+  const float d = invd[n * i0 + s * i1 + yi * i2 + xi * i3];
+  float u, v;
+  bool geom;
+  epi_sample(E, px, d, u, v, geom);
+  const size_t o = ((size_t)n * S + s) * P + p;
+  if (us) { us[o] = u; vs[o] = v; zs[o] = fdiv(1.0f, d); mask[o] = geom ? 1 : 0; }
+  if (pix && s == 0) {
+    pix[((size_t)n * 3 + 0) * P + p] = px.u_h; pix[((size_t)n * 3 + 1) * P + p] = px.v_h; pix[((size_t)n * 3 + 2) * P + p] = px.k_h;
+    if (p == 0) { mvec[n * 3 + 0] = E.e; mvec[n * 3 + 1] = E.i; mvec[n * 3 + 2] = E.m; }
+  }
+}
+}  // namespace rmvd
+
+extern "C" int rmvd_sampling_points_fwd(const float* intrinsics_key, const float* intrinsics_src, const float* src_to_key, const float* invdepths,
+                                        const int64_t* inv_stride, int N, int h, int w, int hs, int ws, int S, float* us, float* vs, float* zs,
+                                        uint8_t* geom_mask, float* coeff_pix, float* coeff_m, void* stream) {
+  if (!intrinsics_key || !intrinsics_src || !src_to_key || !invdepths || !inv_stride) return RMVD_E_NULL;
+  if ((us == nullptr) != (vs == nullptr) || (us == nullptr) != (zs == nullptr) || (us == nullptr) != (geom_mask == nullptr)) return RMVD_E_NULL;
+  if ((coeff_pix == nullptr) != (coeff_m == nullptr) || (!us && !coeff_pix)) return RMVD_E_NULL;
+  if (N <= 0 || h <= 0 || w <= 0 || hs <= 0 || ws <= 0 || S <= 0 || N > 65535) return RMVD_E_SHAPE;
+  const long long tot = (long long)(us ? S : 1) * h * w;
+  dim3 grid((unsigned)((tot + 255) / 256), N);
+  rmvd::sampling_points_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(intrinsics_key, intrinsics_src, src_to_key, invdepths, inv_stride[0], inv_stride[1],
+                                                                      inv_stride[2], inv_stride[3], h, w, hs, ws, us ? S : 1, us, vs, zs, geom_mask,
+                                                                      coeff_pix, coeff_m);
+  return (int)cudaGetLastError();
 }
 
 extern "C" int rmvd_psweep_warp_fwd(const float* feat_src, const float* intrinsics_key, const float* intrinsics_src,
@@ -603,13 +654,13 @@ extern "C" int rmvd_psweep_warp_fwd(const float* feat_src, const float* intrinsi
 }
 
 extern "C" int rmvd_warp_grid_fwd(const float* x, const float* grid, int K, int C, int hs, int ws, int ho, int wo,
-                                  int padding_border, float* out, float* mask, void* stream) {
+                                  int padding_border, int x_repeat, float* out, float* mask, void* stream) {
   if (!x || !grid || !out || !mask) return RMVD_E_NULL;
-  if (K <= 0 || C <= 0 || hs <= 0 || ws <= 0 || ho <= 0 || wo <= 0) return RMVD_E_SHAPE;
+  if (K <= 0 || C <= 0 || hs <= 0 || ws <= 0 || ho <= 0 || wo <= 0 || x_repeat <= 0) return RMVD_E_SHAPE;
   if (padding_border != 0 && padding_border != 1) return RMVD_E_MODE;
   if (K > 65535) return RMVD_E_SHAPE;
   const int Po = ho * wo;
   dim3 g((Po + 255) / 256, K);
-  warp_grid_kernel<<<g, 256, 0, (cudaStream_t)stream>>>(x, grid, C, hs, ws, Po, padding_border, out, mask);
+  warp_grid_kernel<<<g, 256, 0, (cudaStream_t)stream>>>(x, grid, C, hs, ws, Po, padding_border, x_repeat, out, mask);
   return (int)cudaGetLastError();
 }

@@ -20,6 +20,7 @@ struct PsweepArgs {
   long long ist[4];                  // element strides of invd for (n,s,y,x)
   const float* grids;                // kFromGrid: [N,S,2,h,w] sampling positions in source pixels
   const uint8_t* grid_mask;          // kFromGrid: optional [N,S,h,w]
+  int border;                        // kFromGrid: grid_sample padding_mode="border" (coordinates clipped into the map, mask = geometric mask only)
   int hs[kMaxViews], ws[kMaxViews];
   int N, C, h, w, S, s_begin, s_end, norm, out_S, out_s0, v0;
   float* corr;                       // [V,N,out_S,h,w]

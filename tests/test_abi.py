@@ -47,11 +47,17 @@ def test_only_sm100a_code_is_embedded():
 
 def test_argument_validation_needs_no_device(lib):
     null = ctypes.c_void_p(None)
+    st = (ctypes.c_int64 * 4)(0, 1, 0, 0)
     assert lib.rmvd_softargmax_combine(null, 2, 1, 4, 4, null, null) == -1          # RMVD_E_NULL
     one = ctypes.c_void_p(1)
     assert lib.rmvd_softargmax_combine(one, 0, 1, 4, 4, one, null) == -2            # RMVD_E_SHAPE
     assert lib.rmvd_mvs_variance_fwd(one, one, one, 1, 3, 8, 4, 4, 8, 2, 9, one, 8, 0, null) == -5  # RMVD_E_RANGE
-    assert lib.rmvd_warp_grid_fwd(one, one, 1, 1, 4, 4, 4, 4, 7, one, one, null) == -3  # RMVD_E_MODE
+    assert lib.rmvd_warp_grid_fwd(one, one, 1, 1, 4, 4, 4, 4, 7, 1, one, one, null) == -3  # RMVD_E_MODE
+    assert lib.rmvd_mvs_variance_fwd_ws(one, one, one, 1, 3, 32, 4, 4, 8, 0, 8, one, 8, 0, null, 0, null) == -1   # RMVD_E_NULL: workspace needed
+    assert lib.rmvd_mvs_variance_workspace_bytes(2, 5, 32, 7, 9) == 4 * 2 * 4 * 32 * 63
+    assert lib.rmvd_volume_reduce_fwd(one, one, 1, 4, 4, 4, 3, one, null) == -3                                   # RMVD_E_MODE
+    assert lib.rmvd_copy_rows(one, one, 16, 32, 1, null) == -2                                                    # row wider than the pitch
+    assert lib.rmvd_sampling_points_fwd(one, one, one, one, st, 1, 4, 4, 4, 4, 4, null, null, null, null, null, null, null) == -1
     assert lib.rmvd_status_string(-4).decode().startswith("workspace")
     arr = (ctypes.c_void_p * 1)(1)
     ints = (ctypes.c_int * 1)(4)

@@ -248,3 +248,26 @@ def test_cfg3_full_size_against_reference_golden(cuda_lib):
     del var
     r = bu.mvs_regress(cu(case["cost"]), cu(case["depth"]))
     check_regress_against_golden(g, npy(r["depth"]), npy(r["confidence"]), npy(r["depth_index"]), npy(r["expected_index"]))
+
+
+def test_depth_regression_and_entropy_follow_the_reference_for_any_input(cuda_lib):
+    """blocks/utils.py:271-274 and :67-68 apply no softmax: an un-normalised volume, per-pixel depth hypotheses
+    (cvp_mvsnet.py:168) and values outside the clamp range of entropy() must come out as torch computes them."""
+    from robustmvd_b200.blocks import utils as bu
+    from robustmvd_b200._lib import RmvdError
+    rng = np.random.default_rng(5)
+    p = (rng.random((2, 9, 7, 13), dtype=np.float32) * 1.7).astype(np.float32)          # not normalised, some values > 1
+    p[0, 3] = 0.0
+    dv = rng.random((2, 9), dtype=np.float32) + 0.5
+    dpix = rng.random((2, 9, 7, 13), dtype=np.float32) + 0.5
+    tp = torch.from_numpy(p)
+    ref = torch.sum(tp * torch.from_numpy(dv).view(2, 9, 1, 1), 1).numpy()
+    assert np.allclose(npy(bu.depth_regression(cu(p), cu(dv))), ref, rtol=1e-6, atol=1e-6)
+    ref4 = torch.sum(tp * torch.from_numpy(dpix), 1).numpy()
+    assert np.allclose(npy(bu.depth_regression(cu(p), cu(dpix))), ref4, rtol=1e-6, atol=1e-6)
+    ent = torch.sum(-tp * tp.clamp(1e-9, 1.0).log(), dim=1, keepdim=True).numpy()
+    assert np.allclose(npy(bu.entropy(cu(p), 1, keepdim=True)), ent, rtol=1e-5, atol=1e-5)
+    with pytest.raises(RmvdError):                                                       # forward only: no silent graph-less result
+        bu.depth_regression(cu(p).requires_grad_(True), cu(dv))
+    with torch.no_grad():
+        bu.depth_regression(cu(p).requires_grad_(True), cu(dv))

@@ -270,3 +270,91 @@ def test_cfg4_full_size_against_reference_golden(cuda_lib):
     corrs2, masks2, _, _ = _run_cuda(case, debug=False)           # the production kernel variant (no debug outputs)
     for v in range(len(corrs)):
         assert np.array_equal(masks2[v], masks[v]) and np.array_equal(corrs2[v], corrs[v])
+
+
+@pytest.mark.parametrize("name", ["roll_pitch_12x20", "src_res_differs", "behind_12x20", "stereo_x_12x20", "explicit_inv_rank4"])
+def test_block_state_like_the_reference(cuda_lib, name):
+    """The reference block leaves ``coeffs`` and ``sampling_points`` on itself (planesweep_corr.py:389-394, :489-512); here they
+    are materialised on first read (``rmvd_sampling_points_fwd``): us / vs / zs and the geometric mask bit for bit against the
+    oracle's chain, the derived coefficient properties against their definitions."""
+    from robustmvd_b200.blocks.planesweep_corr import PlanesweepCorrelation
+    case = [c for c in PS if c["name"] == name][0]
+    t = lambda a: None if a is None else torch.from_numpy(np.asarray(a)).cuda()  # noqa: E731
+    kw = {k: (t(v) if isinstance(v, np.ndarray) else v) for k, v in case["kwargs"].items()}
+    blk = PlanesweepCorrelation()
+    blk(feat_key=t(case["feat_key"]), intrinsics_key=t(case["intrinsics_key"]), feat_sources=[t(f) for f in case["feat_sources"]],
+        source_to_key_transforms=[t(x) for x in case["transforms"]],
+        intrinsics_sources=None if case["intrinsics_sources"] is None else [t(x) for x in case["intrinsics_sources"]], **kw)
+    _, _, _, odbg = oracle.planesweep_correlation(case["feat_key"], case["intrinsics_key"], case["feat_sources"], case["transforms"],
+                                                  case["intrinsics_sources"], return_debug=True, **case["kwargs"])
+    assert len(blk.sampling_points) == len(blk.coeffs) == len(case["feat_sources"])
+    for v, sp in enumerate(blk.sampling_points):
+        shape = sp.us.shape
+        assert np.array_equal(sp.us.cpu().numpy(), np.broadcast_to(odbg[v]["us"], shape))
+        assert np.array_equal(sp.vs.cpu().numpy(), np.broadcast_to(odbg[v]["vs"], shape))
+        assert np.array_equal(sp.zs.cpu().numpy(), np.broadcast_to(odbg[v]["zs"], shape), equal_nan=True)
+        assert sp.mask.dtype == torch.bool and np.array_equal(sp.mask.cpu().numpy(), np.broadcast_to(odbg[v]["geom_mask"], shape))
+        assert sp.get_uvs().shape == (shape[0], shape[1], 2, shape[2], shape[3]) and sp.num == shape[1]
+        co = blk.coeffs[v]
+        N, _, h, w = case["feat_key"].shape
+        assert co.u_infs_h.shape == (N, 1, h, w) and co.m_k_h.shape == (N, 1, 1, 1) and (co.height, co.width) == (h, w)
+        # us = (u_infs_h + m_u_h * d) / (k_infs_h + m_k_h * d) (:333-335) reproduces the sampling points from the coefficients
+        d = 1.0 / sp.zs
+        us2 = (co.u_infs_h + co.m_u_h * d) / (co.k_infs_h + co.m_k_h * d)
+        ok = torch.isfinite(us2) & (sp.us.abs() < 1e8)
+        assert torch.allclose(us2[ok], sp.us[ok], rtol=1e-4, atol=1e-3)
+        assert torch.isfinite(co.u_infs).all() and co.z_poles.shape == (N, 1, h, w) and len(co.epipole) == 2
+
+
+def test_torchcorr_border_padding(cuda_lib):
+    """TorchCorr(padding_mode="border") through rmvd_corr_grid_fwd against the golden of the unmodified reference and the oracle."""
+    import os
+    from robustmvd_b200.blocks.planesweep_corr import TorchCorr
+    c = cases.border_case()
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "border_torchcorr.npz"))
+    cu = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
+    for nm in ("dim", False, True):
+        for wm in (0, 1):
+            corr, mask = TorchCorr(normalize=nm, padding_mode="border")(cu(c["feat_key"]), cu(c["feat_src"]), cu(c["grids"]),
+                                                                       cu(c["geom"]) if wm else None)
+            assert np.array_equal(mask.cpu().numpy().astype(np.uint8), g[f"mask_{nm}_{wm}"])
+            ref = g[f"corr_{nm}_{wm}"]
+            assert np.abs(corr.cpu().numpy() - ref).max() <= TOL * np.abs(ref).max()
+
+
+@pytest.mark.parametrize("padding", ["zeros", "border"])
+def test_warp_multi_and_warponlycorr_one_launch(cuda_lib, padding):
+    """warp_multi (planesweep_corr.py:13-46) and WarpOnlyCorr.forward (:107-140) on caller grids / offsets: one launch for all S
+    planes, against the reference's own formulation restated with torch CPU ops (per-plane warp(): grid scaling :85-88, grid_sample,
+    mask thresholds :95-102)."""
+    import torch.nn.functional as F
+    from robustmvd_b200.blocks.planesweep_corr import warp_multi, WarpOnlyCorr
+    rng = np.random.default_rng(11)
+    N, C, hs, ws, S, h, w = 2, 6, 9, 14, 5, 7, 8
+    x = torch.from_numpy(rng.standard_normal((N, C, hs, ws), dtype=np.float32))
+    grids = torch.from_numpy(np.stack([rng.uniform(-3, ws + 3, (N, S, h, w)), rng.uniform(-3, hs + 3, (N, S, h, w))], 2).astype(np.float32))
+
+    def ref_warp(g2):                                            # g2 [N,2,h,w] in source pixels
+        gg = g2.permute(0, 2, 3, 1)
+        gn = torch.cat([2 * gg[..., :1] / ws - 1, 2 * gg[..., 1:] / hs - 1], -1)
+        out = F.grid_sample(x, gn, padding_mode=padding, align_corners=False)
+        if padding == "border":
+            return out, torch.ones((N, 1, h, w))
+        m = F.grid_sample(torch.ones((N, 1, hs, ws)), gn, padding_mode="zeros", align_corners=False)
+        m[m < 0.9999] = 0
+        m[m > 0] = 1
+        return out, m
+    ro, rm = zip(*[ref_warp(grids[:, s]) for s in range(S)])
+    ro, rm = torch.stack(ro, 1), torch.stack([m[:, 0] for m in rm], 1)
+    out, mask = warp_multi(x.cuda(), grids=grids.cuda(), padding_mode=padding)
+    assert out.shape == (N, S, C, h, w) and mask.shape == (N, S, h, w)
+    assert torch.equal(mask.cpu(), rm) and float((out.cpu() - ro).abs().max()) < 1e-5
+    # offsets relative to the pixel centres (:68-79)
+    yy, xx = torch.meshgrid(torch.arange(h), torch.arange(w), indexing="ij")
+    centres = torch.stack((xx + 0.5, yy + 0.5), 0).float().view(1, 1, 2, h, w)
+    out2, mask2 = warp_multi(x.cuda(), offsets=(grids - centres).cuda(), padding_mode=padding)
+    assert float((out2.cpu() - ro).abs().max()) < 1e-4 and float((mask2.cpu() != rm).float().mean()) < 0.01
+    # WarpOnlyCorr: normalisation after the warp (:133-134), then masking (:136)
+    wo, wm = WarpOnlyCorr(normalize="after", padding_mode=padding)(None, x.cuda(), grids.cuda())
+    expect = ro / (torch.linalg.norm(ro, dim=2, keepdim=True) + 1e-9) * rm.unsqueeze(2)
+    assert float((wo.cpu() - expect).abs().max()) < 1e-5 and torch.equal(wm.cpu(), rm)

@@ -1,4 +1,6 @@
 """CPU: the numpy oracle against the golden vectors frozen from the UNMODIFIED reference (tools/make_golden.py)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -158,3 +160,16 @@ def test_fullsize_cfg3_oracle_matches_golden():
     assert checked > 40000
     d, c, i, e = oracle.mvs_regress(case["cost"], case["depth"])
     check_regress_against_golden(g, d, c, i, e, rtol=1e-5)
+
+
+def test_torchcorr_border_padding_oracle_matches_golden():
+    """TorchCorr(padding_mode="border") (planesweep_corr.py:143-148, :91-96): golden of the unmodified reference."""
+    c = cases.border_case()
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "border_torchcorr.npz"))
+    for nm in ("dim", False, True):
+        for wm in (0, 1):
+            corr, mask = oracle.torch_corr(c["feat_key"], c["feat_src"], c["grids"][:, :, 0], c["grids"][:, :, 1],
+                                           mask=c["geom"] if wm else None, normalize=nm, padding_mode="border")
+            assert np.array_equal(mask.astype(np.uint8), g[f"mask_{nm}_{wm}"])
+            ref = g[f"corr_{nm}_{wm}"]
+            assert np.abs(corr - ref).max() <= 1e-5 * np.abs(ref).max()

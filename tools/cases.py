@@ -125,6 +125,19 @@ def grad_corrs(case, S):
     return [rng.standard_normal((n, S, h, w)).astype(np.float32) for _ in case["feat_sources"]]
 
 
+def border_case():
+    """Caller grids for TorchCorr(padding_mode="border"): samples up to 4 texels outside the 9 x 14 source map on every side, a few
+    exactly on the rim, and a geometric mask."""
+    rng = np.random.default_rng(808)
+    N, C, h, w, hs, ws, S = 2, 16, 6, 10, 9, 14, 7
+    us = rng.uniform(-4, ws + 4, (N, S, h, w)).astype(np.float32)
+    vs = rng.uniform(-4, hs + 4, (N, S, h, w)).astype(np.float32)
+    us[0, 0, 0, :4] = (0.0, 0.5, ws - 0.5, float(ws))
+    vs[0, 0, 0, :4] = (0.0, 0.5, hs - 0.5, float(hs))
+    return dict(feat_key=syn.features((N, C, h, w), 809), feat_src=syn.features((N, C, hs, ws), 810),
+                grids=np.stack([us, vs], 2).astype(np.float32), geom=rng.random((N, S, h, w)) < 0.8)
+
+
 def fullsize_planesweep_case():
     """BASELINE.json configs[3] at full size: ETH3D 768x1152 -> 96x144 features, C=256, 256 planes, 2 source views."""
     c = syn.CFG4
