@@ -385,6 +385,8 @@ class PlanesweepCorrelation(nn.Module):
             if cached is None:
                 cached = self._as_4d(_to_torch(compute_sampling_invdepths(min_depth, max_depth, num_sampling_points,
                                                                          sampling_type)).to(device))
+                if cached.is_cuda:                       # the pageable H2D copy ran on the stream current NOW; later calls clone the
+                    torch.cuda.current_stream(cached.device).synchronize()   # entry from other streams: make it globally complete once
                 if len(_INVDEPTH_CACHE) >= 16:
                     _INVDEPTH_CACHE.clear()
                 _INVDEPTH_CACHE[key] = cached
