@@ -1,4 +1,4 @@
-// MVSNet variance volume, channels-last staged form (sm_100a): homo_warp (blocks/utils.py:222-268) fused with the volume
+// MVSNet variance volume, channels-last staged forms (sm_100a; the warp-specialised kernel at the end of the namespace is the default): homo_warp (blocks/utils.py:222-268) fused with the volume
 // assembly of mvsnet.py:123-136 for C a multiple of 32.  What changed against mvs_variance_tile_kernel (mvs.cu), which spent
 // its issue slots on 128 scalar shared-memory loads per (voxel, view):
 //
@@ -324,6 +324,242 @@ __global__ void __launch_bounds__(kPx * kPL, (kPL <= 4) ? 2 : 1) mvs_variance_cl
 }
 
 
+// ---------------------------------------------------------------------------------------------------------
+// Warp-specialised form of the same kernel: one CTA per SM = 16 consumer warps (tile of 64 key pixels x 8 planes, thread = voxel x 32
+// channels) + ONE producer warp that plans and copies the rectangles of the coming steps into a ring of kWsBufs buffers.  The
+// consumers execute no planning and no copy instructions and meet no CTA barrier: they wait on the ring's `full` mbarrier (32
+// cp.async completions + the producer's release of the rectangle record), gather, and release the buffer through its `empty`
+// mbarrier (one arrival per consumer warp).  The two-barriers / one-barrier kernels above lost 20 % of their warp-time at the step
+// barrier behind whichever warp had planned and copied (profiles/r02r_var_kernel.md).
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kWsPL = 8;                           // planes per step
+constexpr int kWsConsumers = kPx * kWsPL;          // 512 threads
+constexpr int kWsThreads = kWsConsumers + 128;     // + the producer's warpgroup (one working warp; setmaxnreg moves its registers to the consumers)
+constexpr int kWsBufs = 4;                         // staged rectangles in flight
+
+template <bool kPacked>
+__global__ void __launch_bounds__(kWsThreads, 1) mvs_variance_ws_kernel(
+    const float* __restrict__ feats, const float* __restrict__ src_cl, const float* __restrict__ proj, const float* __restrict__ depths,
+    int B, int Vt, int C, int h, int w, int D, int d_begin, int d_end, float* __restrict__ variance, int out_D, int out_d0, int tiles_x,
+    int ncg, int nsplit) {
+  constexpr int kPL = kWsPL, kThreads = kWsThreads;
+  static_assert(4 * kPL == 32, "the producer warp plans a step: 4 corner pixels x kPL planes");
+  extern __shared__ __align__(128) unsigned char s_buf[];   // kWsBufs staged rectangles
+  __shared__ float s_M[kMaxMvsViews][12];
+  __shared__ __align__(16) int s_rect[kWsBufs][4];   // {rx, ry, rw, rh} of the step in each buffer; rw = 0: nothing staged
+  __shared__ __align__(8) unsigned long long s_bar[2 * kWsBufs];   // full[b]: rectangle landed; empty[b]: every consumer warp is done with it
+  __shared__ float2 s_ref[(kCG / 2) * kPx];   // key-view features of the tile, [channel pair][tile pixel]
+  const int t = threadIdx.x, lane = t & 31;
+  const int b = blockIdx.z;
+  const int P = h * w, nV = Vt - 1;
+  const int tyi = blockIdx.x / tiles_x, txi = blockIdx.x - tyi * tiles_x;
+  const int split = blockIdx.y / ncg, cg = blockIdx.y - split * ncg;
+  const int c0 = cg * kCG;
+  for (int e = t; e < nV * 12; e += kThreads) {
+    const int v = 1 + e / 12, i = (e % 12) / 4, j = e % 4;
+    s_M[v - 1][i * 4 + j] = matmul4_elem(proj + ((size_t)b * Vt + v) * 16, proj + ((size_t)b * Vt) * 16, i, j);
+  }
+  const unsigned bar0 = smem_u32(s_bar);
+  if (t == 0) {
+    for (int bb = 0; bb < kWsBufs; ++bb) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar0 + 8 * bb), "r"(129));                   // 128 copy completions + 1 release of the plan
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar0 + 8 * (kWsBufs + bb)), "r"(kWsConsumers / 32));
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+
+  const bool producer = t >= kWsConsumers;
+  const int px = t & (kPx - 1), pl = producer ? 0 : t / kPx;   // producer lanes: pl unused
+  const int xi = txi * kTW + (px % kTW), yi = tyi * kTH + (px / kTW);
+  const bool in_img = (xi < w) && (yi < h);
+  const int p = min(yi, h - 1) * w + min(xi, w - 1);
+  const int Dl = d_end - d_begin;
+  const int npg = (Dl + kPL - 1) / kPL, pg_per = (npg + nsplit - 1) / nsplit;
+  const int pg0 = split * pg_per, pg1 = min(npg, pg0 + pg_per);
+  if (pg0 >= pg1) return;                                   // uniform
+  for (int e = t; e < kCG * kPx; e += kThreads) {           // visible after the first barrier below
+    const int k = e / kPx, q = e - k * kPx;
+    const int qx = txi * kTW + (q % kTW), qy = tyi * kTH + (q / kTW);
+    reinterpret_cast<float*>(s_ref)[((k >> 1) * kPx + q) * 2 + (k & 1)] =
+        (qx < w && qy < h) ? __ldg(feats + (((size_t)b * Vt) * C + c0 + k) * P + (size_t)qy * w + qx) : 0.f;
+  }
+  const int nsteps = (pg1 - pg0) * nV;
+  const float y_w = rcp_refined((float)(w - 1) * 0.5f), y_h = rcp_refined((float)(h - 1) * 0.5f);
+  const float wm = (float)(w - 1), hm = (float)(h - 1);
+  const float xf = (float)xi, yf = (float)yi;
+  const unsigned sbase = smem_u32(s_buf);
+  const float* src_b = src_cl + ((size_t)b * nV * P) * C + c0;
+  const float* dep_b = depths + (size_t)b * D + d_begin;
+
+  // warp 0: rectangle of (plane group pg, view v) -> s_rect[slot]
+  auto plan = [&](int pg, int v, int slot) {
+    const int corner = lane & 3, cpl = lane >> 2;
+    const int dl = pg * kPL + cpl;
+    const bool valid = (cpl < kPL) && (dl < Dl);
+    const int cx = (corner & 1) ? min(txi * kTW + kTW - 1, w - 1) : txi * kTW;
+    const int cy = (corner & 2) ? min(tyi * kTH + kTH - 1, h - 1) : tyi * kTH;
+    const float d = __ldg(dep_b + min(dl, Dl - 1));
+    const float* M = s_M[v - 1];
+    float ix, iy;
+    homo_coord_fast(M, (float)cx, (float)cy, d, h, w, y_w, y_h, ix, iy);
+    const float den = fadd(__fmaf_rn(M[10], d, __fmaf_rn(M[9], fmul((float)cy, d), fmul(M[8], fmul((float)cx, d)))), M[11]);
+    const bool pos = den > 0.f;
+    const bool pos0 = __shfl_sync(kFullMask, pos, lane & ~3);
+    const bool regular = !valid || (isfinite(ix) && isfinite(iy) && (den != 0.f) && (pos == pos0));
+    const bool all_regular = __all_sync(kFullMask, regular);
+    // clamp before the conversion; margin 2^-8 px for the rounding differences between a corner's chain and an interior pixel's
+    const float lo_x = fminf(fmaxf(floorf(ix - 0.00390625f), -1.f), (float)w), hi_x = fminf(fmaxf(floorf(ix + 0.00390625f) + 1.f, -1.f), (float)w);
+    const float lo_y = fminf(fmaxf(floorf(iy - 0.00390625f), -1.f), (float)h), hi_y = fminf(fmaxf(floorf(iy + 0.00390625f) + 1.f, -1.f), (float)h);
+    const bool use = valid && all_regular;
+    const int xlo = __reduce_min_sync(kFullMask, use ? (int)lo_x : kNone), xhi = __reduce_max_sync(kFullMask, use ? (int)hi_x : -kNone);
+    const int ylo = __reduce_min_sync(kFullMask, use ? (int)lo_y : kNone), yhi = __reduce_max_sync(kFullMask, use ? (int)hi_y : -kNone);
+    if (lane == 0) {
+      int rw = 0, rh = 0;
+      // some cell with a corner inside the map: x0 in [-1, w-1] <=> columns [x0, x0 + 1] meet [0, w-1]
+      if (all_regular && xlo != kNone && xlo <= w - 1 && xhi >= 0 && ylo <= h - 1 && yhi >= 0) {
+        rw = xhi - xlo + 1;
+        rh = yhi - ylo + 1;
+        if (rw * rh > kCap) rw = rh = 0;
+      }
+      s_rect[slot][0] = xlo; s_rect[slot][1] = ylo; s_rect[slot][2] = rw; s_rect[slot][3] = rh;
+    }
+  };
+  // copies of the rectangle in s_rect[slot] (view v) into buffer bufi.  Warp = one rectangle row at a time, lane = (texel l >> 3, chunk
+  // l & 7): one warp instruction covers 4 whole 128-byte lines of the channels-last copy (an LDGSTS costs one shared-memory wavefront
+  // per global line it touches: with one texel per lane it was 27 wavefronts per instruction, profiles/r02p), addresses advance by
+  // constants inside a row
+  const int st_c = lane & 7, st_t = lane >> 3;
+  auto stage = [&](int v, int slot, int bufi, int r0, int rstep) {
+    const int4 R = *reinterpret_cast<const int4*>(s_rect[slot]);
+    const int rx = R.x, ry = R.y, rw = R.z, rh = R.w;
+    const float* src = src_b + ((size_t)(v - 1) * P) * C + 4 * st_c;
+    const unsigned dst_c = sbase + bufi * kBufBytes + st_c * kChunkPitch + st_t * 16;
+    for (int r = r0; r < rh; r += rstep) {                 // the producer warps share the rows
+      const int y = ry + r;
+      const bool row_ok = (unsigned)y < (unsigned)h;
+      const float* rowp = src + (size_t)(unsigned)(min(max(y, 0), h - 1) * w * C);
+      unsigned dst = dst_c + r * rw * 16;
+      for (int tx = st_t; tx < rw; tx += 4, dst += 64) {
+        const int x = rx + tx;
+        const bool inb = row_ok && ((unsigned)x < (unsigned)w);
+        const float* g = rowp + (unsigned)(min(max(x, 0), w - 1) * C);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(dst), "l"(g), "r"(inb ? 16 : 0) : "memory");   // 0: zero fill
+      }
+    }
+  };
+
+  float2 sum[kCG / 2], sq[kCG / 2];         // sums over the SOURCE views; the key view's terms (:125-126) are added when a group is written
+  auto init_acc = [&]() {
+#pragma unroll
+    for (int k = 0; k < kCG / 2; ++k) sum[k] = sq[k] = make_float2(0.f, 0.f);
+  };
+  auto gather = [&](float depth, bool plane_ok, int slot, int bufi, int v) {
+    float ix, iy;
+    homo_coord_fast(s_M[v - 1], xf, yf, depth, h, w, y_w, y_h, ix, iy);
+    const float fx = floorf(ix), fy = floorf(iy);
+    // ATen zeros padding: a corner outside the map contributes nothing; some corner inside <=> x0 in [-1, w-1], y0 in [-1, h-1]
+    const bool needed = plane_ok && (fx >= -1.0f) && (fx <= wm) && (fy >= -1.0f) && (fy <= hm);   // false for nan / inf
+    if (!needed) return;
+    const int x0 = (int)fx, y0 = (int)fy;
+    const float wx = fsub(ix, fx), wy = fsub(iy, fy);
+    const float wx0 = fsub(1.0f, wx), wy0 = fsub(1.0f, wy);
+    const float nw = fmul(wy0, wx0), ne = fmul(wy0, wx), sw = fmul(wy, wx0), se = fmul(wy, wx);
+    const int4 R = *reinterpret_cast<const int4*>(s_rect[slot]);
+    const int rw = R.z, rh = R.w;
+    const int dx = x0 - R.x, dy = y0 - R.y;
+    if ((dx >= 0) && (dx < rw - 1) && (dy >= 0) && (dy < rh - 1)) {   // the whole cell is staged (never when rw = 0)
+      const unsigned char* a0 = s_buf + bufi * kBufBytes + (dy * rw + dx) * 16;
+      const unsigned char* a1 = a0 + rw * 16;
+#pragma unroll
+      for (int c = 0; c < kChunks; ++c) {
+        const float4 A = *reinterpret_cast<const float4*>(a0 + c * kChunkPitch), Bq = *reinterpret_cast<const float4*>(a0 + c * kChunkPitch + 16);
+        const float4 Cq = *reinterpret_cast<const float4*>(a1 + c * kChunkPitch), Dq = *reinterpret_cast<const float4*>(a1 + c * kChunkPitch + 16);
+        accumulate4<kPacked>(A, Bq, Cq, Dq, nw, ne, sw, se, sum + 2 * c, sq + 2 * c);
+      }
+    } else {
+      const float* src = src_b + ((size_t)(v - 1) * P) * C;
+      const bool xl = x0 >= 0, xr = x0 + 1 < w, yt = y0 >= 0, yb = y0 + 1 < h;
+      const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+      const float* g00 = src + ((size_t)max(y0, 0) * w + max(x0, 0)) * C;
+      const float* g01 = src + ((size_t)max(y0, 0) * w + min(x0 + 1, w - 1)) * C;
+      const float* g10 = src + ((size_t)min(y0 + 1, h - 1) * w + max(x0, 0)) * C;
+      const float* g11 = src + ((size_t)min(y0 + 1, h - 1) * w + min(x0 + 1, w - 1)) * C;
+#pragma unroll
+      for (int c = 0; c < kChunks; ++c) {   // fully unrolled: a dynamic index would move the accumulators to local memory
+        const float4 A = (yt && xl) ? ldg4(g00 + 4 * c) : zero, Bq = (yt && xr) ? ldg4(g01 + 4 * c) : zero;
+        const float4 Cq = (yb && xl) ? ldg4(g10 + 4 * c) : zero, Dq = (yb && xr) ? ldg4(g11 + 4 * c) : zero;
+        accumulate4<kPacked>(A, Bq, Cq, Dq, nw, ne, sw, se, sum + 2 * c, sq + 2 * c);
+      }
+    }
+  };
+  const float inv_V = 1.0f / (float)Vt;        // x / V as x * (1 / V): within 1 ulp, far inside the 1e-4 volume tolerance
+  const size_t cstride = (size_t)out_D * P;
+  auto write_out = [&](int pg) {               // variance = sq / V - (sum / V)^2 (:135), streaming stores
+    const int dl = pg * kPL + pl;
+    if (!in_img || dl >= Dl) return;
+    float* out = variance + (((size_t)b * C + c0) * out_D + out_d0 + dl) * P + p;
+    const float2 iv = make_float2(inv_V, inv_V);
+#pragma unroll
+    for (int k = 0; k < kCG / 2; ++k) {
+      const float2 r = s_ref[k * kPx + px];
+      const float2 m = __fmul2_rn(__fadd2_rn(sum[k], r), iv);
+      const float2 q = __fmul2_rn(__ffma2_rn(r, r, sq[k]), iv);
+      __stcs(out, fsub(q.x, fmul(m.x, m.x)));
+      __stcs(out + cstride, fsub(q.y, fmul(m.y, m.y)));
+      out += 2 * cstride;
+    }
+  };
+  auto advance = [&](int& pg, int& v) {
+    if (++v > nV) { v = 1; ++pg; }
+  };
+
+  auto mbar_wait = [&](unsigned bar, unsigned parity) {
+    unsigned done = 0;
+    while (!done)
+      asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.b32 %0, 1, 0, p;\n\t}\n"
+                   : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+  };
+  __syncthreads();                             // transforms, key tile and barriers are set up; the roles part ways here
+  int pg = pg0, v = 1;
+  // 640 threads x 96 registers at launch (5 warps per scheduler partition); the producer's warpgroup gives 32 registers per thread
+  // back and the four consumer warpgroups take 8 each: 4 x 104 + 64 = 5 x 96
+  if (producer) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 64;\n");
+    // producer warpgroup (4 warps): per step j, as soon as the consumers have released buffer j % kWsBufs, warp 0 plans the
+    // rectangle, the group meets on a named barrier, every warp copies every fourth row
+    const int pw = (t - kWsConsumers) >> 5;
+    for (int j = 0; j < nsteps; ++j) {
+      const int bb = j % kWsBufs, u = j / kWsBufs;
+      if (u > 0) mbar_wait(bar0 + 8 * (kWsBufs + bb), (unsigned)(u - 1) & 1u);
+      if (pw == 0) plan(pg, v, bb);
+      asm volatile("bar.sync 1, 128;\n" ::: "memory");
+      stage(v, bb, bb, pw, 4);
+      asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar0 + 8 * bb) : "memory");   // arrives when this lane's copies have landed
+      if (t == kWsConsumers) asm volatile("mbarrier.arrive.release.cta.shared::cta.b64 _, [%0];" ::"r"(bar0 + 8 * bb) : "memory");   // publishes s_rect[bb]
+      advance(pg, v);
+    }
+    asm volatile("cp.async.wait_all;\n" ::: "memory");
+    return;
+  }
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 104;\n");
+  init_acc();
+  float depth = __ldg(dep_b + min(pg * kPL + pl, Dl - 1));
+  for (int s = 0; s < nsteps; ++s) {
+    const int bb = s % kWsBufs, u = s / kWsBufs;
+    const float depth_next = (v == nV) ? __ldg(dep_b + min((pg + 1) * kPL + pl, Dl - 1)) : depth;
+    mbar_wait(bar0 + 8 * bb, (unsigned)u & 1u);
+    gather(depth, in_img && (pg * kPL + pl < Dl), bb, bb, v);
+    __syncwarp();
+    if (lane == 0) asm volatile("mbarrier.arrive.release.cta.shared::cta.b64 _, [%0];" ::"r"(bar0 + 8 * (kWsBufs + bb)) : "memory");
+    if (v == nV) {
+      write_out(pg);
+      if (s + 1 < nsteps) init_acc();
+    }
+    depth = depth_next;
+    advance(pg, v);
+  }
+}
+
 }  // namespace varcl
 }  // namespace rmvd
 
@@ -369,6 +605,38 @@ int launch_cl(const float* feats, float* ws, const float* proj, const float* dep
                                             nsplit);
   return (int)cudaGetLastError();
 }
+
+template <bool kPacked>
+int launch_ws(const float* feats, float* ws, const float* proj, const float* depths, int B, int Vt, int C, int h, int w, int D, int d_begin,
+              int d_end, float* variance, int out_D, int out_d0, cudaStream_t stream) {
+  using namespace rmvd::varcl;
+  auto kernel = mvs_variance_ws_kernel<kPacked>;
+  static int sm_count = 0;
+  if (sm_count == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
+    if (sm_count <= 0) sm_count = 148;
+  }
+  const int smem = kWsBufs * kBufBytes;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return (int)e;
+  const int P = h * w, nV = Vt - 1;
+  dim3 g1((P + 31) / 32, C / 32, B * nV);
+  if (g1.z > 65535) return RMVD_E_SHAPE;
+  nchw_to_cl_kernel<<<g1, 256, 0, stream>>>(feats, ws, Vt, C, P);
+  const int tiles_x = (w + kTW - 1) / kTW, tiles_y = (h + kTH - 1) / kTH, ncg = C / kCG;
+  const int npg = (d_end - d_begin + kWsPL - 1) / kWsPL;
+  const long long base = (long long)tiles_x * tiles_y * ncg * B;
+  int nsplit = (int)((6LL * sm_count + base - 1) / base);      // at least ~6 waves of one CTA per SM (measured at cfg3: 1 split 1.008 ms, 2: 1.033, 4: 1.10)
+  nsplit = nsplit < 1 ? 1 : (nsplit > npg ? npg : nsplit);
+  if (const char* s = getenv("RMVD_MVS_VARIANCE_SPLIT")) nsplit = max(1, min(npg, atoi(s)));
+  if ((long long)nsplit * ncg > 65535) return RMVD_E_SHAPE;
+  dim3 grid((unsigned)(tiles_x * tiles_y), (unsigned)(nsplit * ncg), B);
+  kernel<<<grid, kWsThreads, smem, stream>>>(feats, ws, proj, depths, B, Vt, C, h, w, D, d_begin, d_end, variance, out_D, out_d0, tiles_x, ncg,
+                                             nsplit);
+  return (int)cudaGetLastError();
+}
 }  // namespace
 
 extern "C" int rmvd_mvs_variance_fwd(const float* feats, const float* proj, const float* depths, int B, int Vt, int C, int h, int w, int D,
@@ -391,10 +659,11 @@ extern "C" int rmvd_mvs_variance_fwd_ws(const float* feats, const float* proj, c
   if ((uintptr_t)workspace % 16 != 0) return RMVD_E_WORKSPACE;   // 16-byte copies
   float* ws = (float*)workspace;
   cudaStream_t st = (cudaStream_t)stream;
-  switch (mode) {
-    case 1: return launch_cl<4, false>(feats, ws, proj, depths, B, Vt, C, h, w, D, d_begin, d_end, variance, out_D, out_d0, st);
-    case 2: return launch_cl<8, true>(feats, ws, proj, depths, B, Vt, C, h, w, D, d_begin, d_end, variance, out_D, out_d0, st);
-    case 3: return launch_cl<8, false>(feats, ws, proj, depths, B, Vt, C, h, w, D, d_begin, d_end, variance, out_D, out_d0, st);
-    default: return launch_cl<4, true>(feats, ws, proj, depths, B, Vt, C, h, w, D, d_begin, d_end, variance, out_D, out_d0, st);
+  switch (mode) {   // 0 (default): warp-specialised kernel, packed fp32; the others are the A/B variants of DESIGN.md 5
+    case 1: return launch_ws<false>(feats, ws, proj, depths, B, Vt, C, h, w, D, d_begin, d_end, variance, out_D, out_d0, st);
+    case 2: return launch_cl<4, true>(feats, ws, proj, depths, B, Vt, C, h, w, D, d_begin, d_end, variance, out_D, out_d0, st);
+    case 3: return launch_cl<4, false>(feats, ws, proj, depths, B, Vt, C, h, w, D, d_begin, d_end, variance, out_D, out_d0, st);
+    case 4: return launch_cl<8, true>(feats, ws, proj, depths, B, Vt, C, h, w, D, d_begin, d_end, variance, out_D, out_d0, st);
+    default: return launch_ws<true>(feats, ws, proj, depths, B, Vt, C, h, w, D, d_begin, d_end, variance, out_D, out_d0, st);
   }
 }
