@@ -649,29 +649,89 @@ __global__ void softargmax_confidence_kernel(const float* __restrict__ cost_slab
   conf_part[o] = acc / Z;
 }
 
-// soft_argmin + entropy (blocks/utils.py:51-68): thread = pixel, three sweeps over D (the volume stays in L2).
-__global__ void __launch_bounds__(256) soft_argmin_kernel(const float* __restrict__ vol, int D, int P, float window,
-                                                          float* __restrict__ prob, float* __restrict__ eidx_out,
-                                                          float* __restrict__ prob_map, float* __restrict__ entropy) {
-  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+// soft_argmin + entropy (blocks/utils.py:51-68).  CTA = 32 adjacent pixels x 8 plane groups (warp g owns planes g, g + 8, ...,
+// 128-byte rows, 8 loads in flight per thread).  Sweep 1: online-softmax state (m, Z, I = sum e * index) per group, merged through
+// shared memory -> expected index.  Sweep 2 (the volume is L2-resident by then): probabilities, windowed probability around the
+// expected index, entropy; the per-group sums meet in shared memory.
+__global__ void __launch_bounds__(kRegWarps * 32) soft_argmin_kernel(const float* __restrict__ vol, int D, int P, float window,
+                                                                     float* __restrict__ prob, float* __restrict__ eidx_out,
+                                                                     float* __restrict__ prob_map, float* __restrict__ entropy) {
+  __shared__ SoftState s_state[kRegWarps][32];
+  __shared__ float s_m[32], s_Z[32], s_E[32];
+  __shared__ float s_pm[kRegWarps][32], s_ent[kRegWarps][32];
   const int b = blockIdx.y;
-  if (p >= P) return;
+  const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int p = blockIdx.x * 32 + lane;
+  const bool act = p < P;
   const float* x = vol + (size_t)b * D * P + p;
   SoftState st{-INFINITY, 0.f, 0.f, 0.f};
-  for (int d = 0; d < D; ++d) soft_push(st, __ldg(x + (size_t)d * P), 0.f, (float)d);
-  const float E = st.I / st.Z;
-  const size_t o = (size_t)b * P + p;
-  eidx_out[o] = E;
-  if (!prob && !prob_map && !entropy) return;
-  float pm = 0.f, ent = 0.f;
-  for (int d = 0; d < D; ++d) {
-    const float pd = expf(__ldg(x + (size_t)d * P) - st.m) / st.Z;
-    if (prob) prob[(size_t)b * D * P + (size_t)d * P + p] = pd;
-    if (fabsf((float)d - E) <= window) pm += pd;
-    ent = fmaf(-pd, logf(fminf(fmaxf(pd, 1e-9f), 1.0f)), ent);
+  constexpr int kB = 8;
+  if (act) {
+    int d = g;
+    for (; d + (kB - 1) * kRegWarps < D; d += kB * kRegWarps) {
+      float xv[kB];
+#pragma unroll
+      for (int k = 0; k < kB; ++k) xv[k] = __ldg(x + (size_t)(d + k * kRegWarps) * P);
+      float mx = st.m;
+#pragma unroll
+      for (int k = 0; k < kB; ++k) mx = fmaxf(mx, xv[k]);
+      const float r = expf(st.m - mx);                     // exp(-inf) = 0 on the first batch
+      st.Z *= r; st.I *= r; st.m = mx;
+#pragma unroll
+      for (int k = 0; k < kB; ++k) {
+        const float e = expf(xv[k] - mx);
+        st.Z += e;
+        st.I = fmaf(e, (float)(d + k * kRegWarps), st.I);
+      }
+    }
+    for (; d < D; d += kRegWarps) soft_push(st, __ldg(x + (size_t)d * P), 0.f, (float)d);
   }
-  if (prob_map) prob_map[o] = pm;
-  if (entropy) entropy[o] = ent;
+  s_state[g][lane] = st;
+  __syncthreads();
+  if (g == 0) {
+#pragma unroll
+    for (int k = 1; k < kRegWarps; ++k) soft_merge(st, s_state[k][lane]);
+    const float E = st.I / st.Z;
+    s_m[lane] = st.m; s_Z[lane] = st.Z; s_E[lane] = E;
+    if (act) eidx_out[(size_t)b * P + p] = E;
+  }
+  if (!prob && !prob_map && !entropy) return;
+  __syncthreads();
+  float pm = 0.f, ent = 0.f;
+  if (act) {
+    const float m = s_m[lane], inv_Z = 1.0f / s_Z[lane], E = s_E[lane];
+    float* po = prob ? prob + (size_t)b * D * P + p : nullptr;
+    int d = g;
+    for (; d + (kB - 1) * kRegWarps < D; d += kB * kRegWarps) {
+      float xv[kB];
+#pragma unroll
+      for (int k = 0; k < kB; ++k) xv[k] = __ldg(x + (size_t)(d + k * kRegWarps) * P);
+#pragma unroll
+      for (int k = 0; k < kB; ++k) {
+        const int dd = d + k * kRegWarps;
+        const float pd = expf(xv[k] - m) * inv_Z;
+        if (po) __stcs(po + (size_t)dd * P, pd);
+        if (fabsf((float)dd - E) <= window) pm += pd;
+        ent = fmaf(-pd, logf(fminf(fmaxf(pd, 1e-9f), 1.0f)), ent);
+      }
+    }
+    for (; d < D; d += kRegWarps) {
+      const float pd = expf(__ldg(x + (size_t)d * P) - m) * inv_Z;
+      if (po) __stcs(po + (size_t)d * P, pd);
+      if (fabsf((float)d - E) <= window) pm += pd;
+      ent = fmaf(-pd, logf(fminf(fmaxf(pd, 1e-9f), 1.0f)), ent);
+    }
+  }
+  if (!prob_map && !entropy) return;
+  s_pm[g][lane] = pm; s_ent[g][lane] = ent;
+  __syncthreads();
+  if (g == 0 && act) {
+#pragma unroll
+    for (int k = 1; k < kRegWarps; ++k) { pm += s_pm[k][lane]; ent += s_ent[k][lane]; }
+    const size_t o = (size_t)b * P + p;
+    if (prob_map) prob_map[o] = pm;
+    if (entropy) entropy[o] = ent;
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -858,8 +918,8 @@ extern "C" int rmvd_soft_argmin_fwd(const float* volume, int B, int D, int h, in
   if (!volume || !expected_index) return RMVD_E_NULL;
   if (B <= 0 || D <= 0 || h <= 0 || w <= 0 || B > 65535) return RMVD_E_SHAPE;
   const int P = h * w;
-  dim3 grid((P + 255) / 256, B);
-  soft_argmin_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(volume, D, P, window, prob, expected_index, prob_map, entropy);
+  dim3 grid((P + 31) / 32, B);
+  soft_argmin_kernel<<<grid, kRegWarps * 32, 0, (cudaStream_t)stream>>>(volume, D, P, window, prob, expected_index, prob_map, entropy);
   return (int)cudaGetLastError();
 }
 

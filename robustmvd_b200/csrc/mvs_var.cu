@@ -560,6 +560,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) mvs_variance_ws_kernel(
   }
 }
 
+
 }  // namespace varcl
 }  // namespace rmvd
 

@@ -285,7 +285,23 @@ __global__ void __launch_bounds__(256) psweep_warp_kernel(const WarpArgs A) {
     }
     onorm = sqrtf(acc) + 1e-9f;
   }
-  for (int c = 0; c < A.C; ++c) {
+  // 8 channels per trip: 32 independent gathers in flight per thread (the loop is latency-bound otherwise), streaming stores
+  const float wnw = b.nw * mf, wne = b.ne * mf, wsw = b.sw * mf, wse = b.se * mf;   // mf is 0 or 1: (sum q w) * mf, :138
+  const bool plain = !nb && (A.norm != RMVD_NORM_AFTER);
+  int c = 0;
+  if (plain) {
+    for (; c + 8 <= A.C; c += 8) {
+      float q[8][4];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float* sc = src + (size_t)(c + k) * Ps;
+        q[k][0] = __ldg(sc + o_nw); q[k][1] = __ldg(sc + o_ne); q[k][2] = __ldg(sc + o_sw); q[k][3] = __ldg(sc + o_se);
+      }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) __stcs(out + (size_t)(c + k) * P, q[k][0] * wnw + q[k][1] * wne + q[k][2] * wsw + q[k][3] * wse);
+    }
+  }
+  for (; c < A.C; ++c) {
     const float* sc = src + (size_t)c * Ps;
     float q0 = __ldg(sc + o_nw), q1 = __ldg(sc + o_ne), q2 = __ldg(sc + o_sw), q3 = __ldg(sc + o_se);
     if (nb) { q0 = fdiv(q0, in_nw); q1 = fdiv(q1, in_ne); q2 = fdiv(q2, in_sw); q3 = fdiv(q3, in_se); }
