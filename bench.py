@@ -230,8 +230,21 @@ def secondary_records(torch, dev, peaks, with_cpu):
         blk = PlanesweepCorrelation()
         cold, warm = _cold_warm(torch, lambda: blk(**kw), flush)
         ab = algorithmic_bytes(frames, cfg, V)
+        # the same call as a CUDA graph (robustmvd_b200.pipeline.GraphedPlanesweep): device time of the launch sequence without the host
+        ms_graph = None
+        try:
+            from robustmvd_b200.pipeline import GraphedPlanesweep
+            gp = GraphedPlanesweep(kw)
+            c0, m0, _ = blk(**kw)
+            c1, m1, _ = gp(**kw)
+            same = all(torch.equal(a, b) for a, b in zip(c0, c1)) and all(torch.equal(a, b) for a, b in zip(m0, m1))
+            ms_graph = dict(zip(("cold", "warm"), _cold_warm(torch, lambda: gp.graph.replay(), flush)))
+            if not same:
+                ms_graph = "graph replay differs from the eager call"
+        except Exception as e:  # noqa: BLE001
+            ms_graph = repr(e)[:200]
         out.append({"name": name, "metric": METRIC, "unit": "voxels/s", "value": voxels(frames, cfg, V) / (cold * 1e-3), "ms_cold": cold,
-                    "ms_warm": warm, "frames": frames, "views": V,
+                    "ms_warm": warm, "ms_cuda_graph": ms_graph, "frames": frames, "views": V,
                     "roofline": {"bound": "hbm", "achieved": ab / cold / 1e6, "peak": hbm, "unit": "GB/s", "frac": ab / cold / 1e6 / hbm,
                                  "algorithmic_bytes_per_launch": ab, "timing": "ms_cold"}})
 

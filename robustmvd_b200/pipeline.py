@@ -120,3 +120,46 @@ class HostPlanesweepPipeline:
         if wait:
             self.finish()
         return out_corr, out_mask
+
+
+class GraphedPlanesweep:
+    """One ``PlanesweepCorrelation.forward`` of a fixed shape, captured in a CUDA graph and replayed: the launch sequence (two
+    split-copy kernels + the persistent plane-sweep kernel) costs no Python, no ctypes marshalling and no allocation per call.
+    That is the latency mode for the batch size the reference evaluates at (one frame per call,
+    rmvd/eval/multi_view_depth_evaluation.py:234-240): 0.061 ms per KITTI-shape frame against 0.093 ms through the eager block.
+
+    ``example`` = the keyword arguments of one representative call (device tensors).  ``__call__(**kwargs)`` copies the tensors
+    it is given into the captured input buffers (device-to-device, stream-ordered) and replays; it returns the block's outputs,
+    which live in the graph's own memory pool and are overwritten by the next call."""
+
+    TENSOR_KEYS = ("feat_key", "intrinsics_key", "feat_sources", "source_to_key_transforms", "intrinsics_sources", "sampling_invdepths")
+
+    def __init__(self, example, block=None):
+        self.block = block if block is not None else PlanesweepCorrelation()
+        clone = lambda v: [t.clone() for t in v] if isinstance(v, (list, tuple)) else v.clone()  # noqa: E731
+        self.static = {k: (clone(v) if k in self.TENSOR_KEYS and v is not None else v) for k, v in example.items()}
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side), torch.no_grad():          # warm-up outside the capture (library load, workspace, schedule cache)
+            self.block(**self.static)
+        torch.cuda.current_stream().wait_stream(side)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph), torch.no_grad():
+            self.out = self.block(**self.static)
+
+    @torch.no_grad()
+    def __call__(self, **kwargs):
+        for k, v in kwargs.items():
+            if k not in self.TENSOR_KEYS or v is None:
+                if k not in self.TENSOR_KEYS and self.static.get(k) != v:
+                    raise ValueError(f"GraphedPlanesweep was captured with {k}={self.static.get(k)!r}")
+                continue
+            dst = self.static[k]
+            if isinstance(v, (list, tuple)):
+                for d, s in zip(dst, v):
+                    if d.data_ptr() != s.data_ptr():
+                        d.copy_(s, non_blocking=True)
+            elif dst.data_ptr() != v.data_ptr():
+                dst.copy_(v, non_blocking=True)
+        self.graph.replay()
+        return self.out

@@ -358,3 +358,26 @@ def test_warp_multi_and_warponlycorr_one_launch(cuda_lib, padding):
     wo, wm = WarpOnlyCorr(normalize="after", padding_mode=padding)(None, x.cuda(), grids.cuda())
     expect = ro / (torch.linalg.norm(ro, dim=2, keepdim=True) + 1e-9) * rm.unsqueeze(2)
     assert float((wo.cpu() - expect).abs().max()) < 1e-5 and torch.equal(wm.cpu(), rm)
+
+
+def test_graphed_planesweep_replays_the_block(cuda_lib):
+    """pipeline.GraphedPlanesweep: the block's launch sequence captured in a CUDA graph; replays with new inputs of the captured
+    shape equal the eager call bit for bit."""
+    from robustmvd_b200.blocks.planesweep_corr import PlanesweepCorrelation
+    from robustmvd_b200.pipeline import GraphedPlanesweep
+    cu = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
+
+    def kwargs(seed):
+        inp = syn.planesweep_inputs(24, 40, 64, 2, seed=seed)
+        return dict(feat_key=cu(inp["feat_key"]), intrinsics_key=cu(inp["intrinsics_key"]), feat_sources=[cu(f) for f in inp["feat_sources"]],
+                    source_to_key_transforms=[cu(t) for t in inp["transforms"]], num_sampling_points=48, min_depth=0.4, max_depth=1000.0)
+    gp = GraphedPlanesweep(kwargs(1))
+    blk = PlanesweepCorrelation()
+    for seed in (1, 2, 3):
+        kw = kwargs(seed)
+        c0, m0, i0 = blk(**kw)
+        c1, m1, i1 = gp(**kw)
+        torch.cuda.synchronize()
+        assert all(torch.equal(a, b) for a, b in zip(c0, c1)) and all(torch.equal(a, b) for a, b in zip(m0, m1)) and torch.equal(i0, i1)
+    with pytest.raises(ValueError):
+        gp(**dict(kwargs(1), num_sampling_points=32))
