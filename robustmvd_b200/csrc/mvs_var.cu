@@ -1,5 +1,5 @@
-// MVSNet variance volume, channels-last staged forms (sm_100a; the warp-specialised kernel at the end of the namespace is the default): homo_warp (blocks/utils.py:222-268) fused with the volume
-// assembly of mvsnet.py:123-136 for C a multiple of 32.  What changed against mvs_variance_tile_kernel (mvs.cu), which spent
+// MVSNet variance volume, channels-last staged forms (sm_100a; the warp-specialised kernel at the end of the namespace is the
+// default): homo_warp (blocks/utils.py:222-268) fused with the volume assembly of mvsnet.py:123-136 for C a multiple of 32.  What changed against mvs_variance_tile_kernel (mvs.cu), which spent
 // its issue slots on 128 scalar shared-memory loads per (voxel, view):
 //
 //   * the source maps are repacked once per call into channels-last [B, Vt-1, h*w, C] (nchw_to_cl_kernel, 2 % of the bytes the
@@ -11,14 +11,16 @@
 //     neighbouring texels) both cover all 32 banks, and the chunk offset is an immediate of the load (no address arithmetic in
 //     the channel loop);
 //   * packed fp32 arithmetic (FFMA2 / FMUL2 / FADD2, two channels per instruction) for the interpolation and the running sums;
-//   * the rectangle of step s + 1 (next view, or next plane group) is located, reduced and in flight (cp.async) while step s is
-//     gathered: two buffers, two barriers per step, no exposed copy latency;
+//   * the rectangle of a step (plane group, view) is planned from the tile's corner pixels and copied ahead of the gather: by every
+//     warp one step ahead with one CTA barrier per step (mvs_variance_cl_kernel), or by a producer warpgroup through a ring of four
+//     buffers on full / empty mbarriers (mvs_variance_ws_kernel, the default): no exposed copy latency;
 //   * tiles of 16 x 4 key pixels (staged texels per voxel: 0.19-0.24 at the DTU shape against 0.34-0.51 for 64 x 1).
 //
-// Thread = one voxel (key pixel, plane) x 32 channels: sum and sum of squares (mvsnet.py:124-133) in 64 registers across the
-// views; the sampling coordinate comes from the reference's own chain (homo_coord_shared, every operation rounded).
-// CTA = 64 key pixels x kPL planes, loops over plane groups and views.  A rectangle that does not fit (strong rotation between
-// the views) is gathered from the channels-last copy in global memory, with bounds tests.
+// Thread = one voxel (key pixel, plane) x 32 channels: sum and sum of squares of the source views (mvsnet.py:124-133) in 64 registers
+// across the views, the key view's terms added when a plane group is written; the sampling coordinate comes from the reference's own
+// chain with shared reciprocals (homo_coord_fast).  CTA = 64 key pixels x kPL planes, loops over plane groups and views.  A voxel whose
+// cell is not inside the planned rectangle (strong rotation between the views, irregular geometry) is gathered from the channels-last
+// copy in global memory, with bounds tests.
 #include <climits>
 
 #include "mvs_coord.cuh"
