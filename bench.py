@@ -432,9 +432,12 @@ def slab_records(torch, dist, dev, world, rank):
         # "planes" / "tiles": the fused kernel, the ranks split the planes (depth slabs proper) or the tiles; every rank's sampling loop
         # stores its rows into all ranks' tensors over NVLink and the kernel ends with a flag handshake.  "planes_copy": depth slabs by
         # the single-GPU kernel per view group, the slabs pushed to the peers by the copy engines under the next group's kernel
-        for part in ("planes", "tiles", "planes_copy"):
+        for part in ("planes", "tiles", "planes_copy", "planes_multicast", "tiles_multicast"):
             gather = parallel.SlabGather(blk, V, 1, cfg["S"], cfg["h"], cfg["w"], dev, partition=part.split("_")[0],
-                                         transport="copy" if part.endswith("_copy") else "stores")
+                                         transport=part.split("_")[1] if "_" in part else "stores")
+            if gather.mode == "all_gather" and "_" in part:      # NVLS / symmetric memory not available: variant not measured
+                rec[part] = {"ms_total": None, "speedup": 0.0, "bit_exact": True, "mode": "unavailable: " + getattr(gather, "why", "")[:120]}
+                continue
             corrs, masks, _ = gather(**kw)
             torch.cuda.synchronize()
             ok = all(torch.equal(a, b) for a, b in zip(corrs, full_c)) and all(torch.equal(a, b) for a, b in zip(masks, full_m))
@@ -443,7 +446,7 @@ def slab_records(torch, dist, dev, world, rank):
             ms_total = timed(lambda: gather(**kw))
             rec[part] = {"ms_total": ms_total, "speedup": ms_full / ms_total, "bit_exact": bool(okt.item()), "mode": gather.mode}
             del gather
-        variants = ("planes", "tiles", "planes_copy")
+        variants = ("planes", "tiles", "planes_copy", "planes_multicast", "tiles_multicast")
         best = max(variants, key=lambda k: rec[k]["speedup"])
         rec.update(ms_slab_total=rec[best]["ms_total"], speedup=rec[best]["speedup"], bit_exact=all(rec[k]["bit_exact"] for k in variants),
                    mode=rec[best]["mode"], partition=best)

@@ -98,6 +98,9 @@ int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* feat_src, co
  *            num_peers-th (tile, sample, view) work item of it: the same tensors result on every rank, but the per-tile costs that
  *            do not depend on the plane count (key tile, calibration, band planning, the band's rows) are divided between the
  *            ranks too, which the plane split cannot do.
+ * corr_multicast / mask_multicast (both or neither): NVSwitch multicast addresses (NVLS) of the same symmetric tensors; the sampling
+ *            loop then issues ONE multimem.st per value, which the switch replicates into every rank's tensor (own rank included),
+ *            instead of num_peers stores: the SM's egress falls from (num_peers - 1) to 1 copy of its slab.
  */
 #define RMVD_PARTITION_PLANES 0
 #define RMVD_PARTITION_TILES 1
@@ -107,7 +110,8 @@ int rmvd_psweep_corr_fwd_peers(const float* feat_key, const float* const* feat_s
                                int V, const int* hs_host, const int* ws_host, int S, int s_begin, int s_end,
                                int normalize_mode, int out_S, int out_s0, int num_peers, int rank,
                                float* const* corr_peers, float* const* mask_peers, uint32_t* const* flag_peers,
-                               uint32_t epoch, int partition, void* workspace, size_t workspace_bytes, void* stream);
+                               uint32_t epoch, int partition, float* corr_multicast, float* mask_multicast,
+                               void* workspace, size_t workspace_bytes, void* stream);
 
 /*
  * Transport of the depth-slab gather by the copy engines (no counterpart in the reference, see rmvd_psweep_corr_fwd_peers): `rows`

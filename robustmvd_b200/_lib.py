@@ -42,7 +42,7 @@ def _declare(lib):
     lib.rmvd_psweep_corr_fwd_static.argtypes = [P, PP, P, PP, PP, P, PL] + [c_int] * 5 + [PI, PI] + [c_int] * 4 + \
         [P, P, c_int, c_int, P]
     lib.rmvd_psweep_corr_fwd_peers.argtypes = [P, PP, P, PP, PP, P, PL] + [c_int] * 5 + [PI, PI] + [c_int] * 8 + \
-        [PP, PP, PP, ctypes.c_uint32, c_int, P, c_size_t, P]
+        [PP, PP, PP, ctypes.c_uint32, c_int, P, P, P, c_size_t, P]
     lib.rmvd_copy_rows.argtypes = [P, P, c_size_t, c_size_t, c_int, P]
     lib.rmvd_psweep_bwd_workspace_bytes.restype = c_size_t
     lib.rmvd_psweep_bwd_workspace_bytes.argtypes = [c_int, c_int, c_int, c_int, c_int, PI, PI]

@@ -8,6 +8,8 @@ them, the correlation outputs carry an autograd node whose backward is the CUDA 
 (SURVEY.md row f-4); sampling points carry no gradient, like in the reference (:436, :464, :489 are ``no_grad``).
 """
 import numpy as np
+import ctypes
+
 import torch
 import torch.nn as nn
 
@@ -509,7 +511,8 @@ class PlanesweepCorrelation(nn.Module):
                 _lib.ptr(inv_c), ist, N, C, h, w, V, _lib.int_array(hs), _lib.int_array(ws), S, s0, s1,
                 _corr_norm_mode(self.normalize) if norm_mode is None else norm_mode, S, s0, G, peers["rank"],
                 _lib.raw_ptr_array(peers["corr"]), _lib.raw_ptr_array(peers["mask"]), _lib.raw_ptr_array(peers["flags"]),
-                peers["epoch"], int(peers.get("partition", 0)), _lib.ptr(wsp), wsp.numel(), _lib.stream_ptr())
+                peers["epoch"], int(peers.get("partition", 0)), ctypes.c_void_p(peers.get("corr_mc") or None),
+                ctypes.c_void_p(peers.get("mask_mc") or None), _lib.ptr(wsp), wsp.numel(), _lib.stream_ptr())
             _lib.check(st, "rmvd_psweep_corr_fwd_peers")
             return None, None, inv
         if not self.warp_only:

@@ -499,12 +499,15 @@ extern "C" int rmvd_psweep_corr_fwd_peers(const float* feat_key, const float* co
                                           int V, const int* hs, const int* ws, int S, int s_begin, int s_end,
                                           int normalize_mode, int out_S, int out_s0, int num_peers, int rank,
                                           float* const* corr_peers, float* const* mask_peers, uint32_t* const* flag_peers,
-                                          uint32_t epoch, int partition, void* workspace, size_t workspace_bytes, void* stream) {
+                                          uint32_t epoch, int partition, float* corr_multicast, float* mask_multicast, void* workspace,
+                                          size_t workspace_bytes, void* stream) {
   if (!corr_peers || !mask_peers || !flag_peers) return RMVD_E_NULL;
   if (num_peers < 1 || num_peers > RMVD_MAX_PEERS || rank < 0 || rank >= num_peers) return RMVD_E_RANGE;
   if (partition != RMVD_PARTITION_PLANES && partition != RMVD_PARTITION_TILES) return RMVD_E_MODE;
   PsweepPeers P{};
+  if ((corr_multicast == nullptr) != (mask_multicast == nullptr)) return RMVD_E_NULL;
   P.n = num_peers; P.rank = rank; P.epoch = epoch; P.by_tiles = (partition == RMVD_PARTITION_TILES);
+  P.corr_mc = corr_multicast; P.mask_mc = mask_multicast;
   for (int g = 0; g < num_peers; ++g) {
     if (!corr_peers[g] || !mask_peers[g] || !flag_peers[g]) return RMVD_E_NULL;
     P.corr[g] = corr_peers[g]; P.mask[g] = mask_peers[g]; P.flags[g] = flag_peers[g];

@@ -50,6 +50,7 @@ struct PsweepPeers {
   float* corr[RMVD_MAX_PEERS]; float* mask[RMVD_MAX_PEERS];
   unsigned* flags[RMVD_MAX_PEERS];
   unsigned epoch;
+  float* corr_mc; float* mask_mc;  // optional NVSwitch multicast addresses of the same tensors (multimem.st: one store reaches every rank); NULL: one store per rank
   int by_tiles;                    // 0: the ranks split the planes (the caller's [s_begin, s_end)); 1: they split the work items (tiles), all planes each
 };
 // counter: 16 bytes of device memory: [0] work-item counter, [2] finished-CTA counter of the slab handshake

@@ -79,6 +79,7 @@ struct PeerArgs {                  // depth-slab mode (n > 0): peer-mapped outpu
   unsigned* flags[kMaxPeers];      // every rank's flag array [n] (symmetric memory): slot r = last epoch rank r completed
   unsigned epoch;                  // this call's epoch (monotone per communicator)
   unsigned* done_ctas;             // local counter of finished CTAs
+  float* corr_mc; float* mask_mc;  // multicast addresses of the output tensors, or NULL
   int item_stride, item_offset;    // this launch works on items j * item_stride + item_offset (tile partition between the ranks); 1, 0 otherwise
 };
 
@@ -112,6 +113,7 @@ struct WsConst {                   // per-launch constants of the out-of-line pa
   float inv_scale;
   int npeers;                      // depth-slab mode: every output row also goes to the peers' tensors (NVLink stores)
   float* pcorr[kMaxPeers]; float* pmask[kMaxPeers];
+  float* mc_corr; float* mc_mask;  // multicast addresses (NVLS): one multimem.st lands in every rank's tensor
 };
 __shared__ WsConst s_k;
 
@@ -135,7 +137,12 @@ __device__ __forceinline__ void store_out(const WsConst& W, float* __restrict__ 
     stcs_at(corr, o, c);
     stcs_at(mask, o, m);
   } else {
-    for (int g = 0; g < W.npeers; ++g) { W.pcorr[g][base + o] = c; W.pmask[g][base + o] = m; }
+    if (W.mc_corr) {             // NVSwitch multicast: the switch replicates the store, this SM sends each value once
+      asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;\n" ::"l"(W.mc_corr + base + o), "f"(c) : "memory");
+      asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;\n" ::"l"(W.mc_mask + base + o), "f"(m) : "memory");
+    } else {
+      for (int g = 0; g < W.npeers; ++g) { W.pcorr[g][base + o] = c; W.pmask[g][base + o] = m; }
+    }
   }
 }
 
@@ -1332,6 +1339,7 @@ __global__ void __launch_bounds__(kThreads, 1) psweep_ws_kernel(const PsweepArgs
     s_k.inv_scale = (A.norm == RMVD_NORM_DIM) ? 1.0f / sqrtf((float)A.C) : 1.0f;    // corr / sqrt(C), :178-179
     s_k.npeers = PA.n;
     for (int g = 0; g < kMaxPeers; ++g) { s_k.pcorr[g] = PA.corr[g]; s_k.pmask[g] = PA.mask[g]; }
+    s_k.mc_corr = PA.n > 0 ? PA.corr_mc : nullptr; s_k.mc_mask = PA.n > 0 ? PA.mask_mc : nullptr;
   }
   asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
   __syncthreads();
@@ -1494,6 +1502,7 @@ int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, uns
   if (peers && peers->n > 0) {
     if (peers->n > ws::kMaxPeers || peers->rank < 0 || peers->rank >= peers->n || A.dbg_ix0) return (int)cudaErrorInvalidValue;
     PA.n = peers->n; PA.rank = peers->rank; PA.epoch = peers->epoch; PA.done_ctas = counter + 2;
+    PA.corr_mc = peers->corr_mc; PA.mask_mc = peers->mask_mc;
     if (peers->by_tiles) {           // this rank's share of the items: rank, rank + n, rank + 2 n, ...
       PA.item_stride = peers->n; PA.item_offset = peers->rank;
       items = (items - peers->rank + peers->n - 1) / peers->n;

@@ -85,7 +85,8 @@ class SlabGather:
     alternate between consecutive calls: a rank that runs ahead writes set ``(k + 1) % 2`` while a slower rank still reads set
     ``k % 2``, and cannot start call ``k + 2`` before the slower rank has finished call ``k + 1`` (the handshake).
 
-    ``partition="tiles"``: the ranks split the (tile, sample, view) work items instead of the planes -- same result on every rank, and
+    ``transport="multicast"``: the sampling loop issues one ``multimem.st`` per value to the buffers' NVSwitch multicast address (NVLS)
+    instead of one store per rank; ``transport="copy"``: see ``_call_copy``.  ``partition="tiles"``: the ranks split the (tile, sample, view) work items instead of the planes -- same result on every rank, and
     the per-tile costs that do not shrink with the plane count (key tile, band planning, band rows) are divided too; at one frame
     this is the partition that is faster than one GPU.
 
@@ -95,7 +96,7 @@ class SlabGather:
     """
 
     def __init__(self, block, V, N, S, h, w, device, group=None, partition="planes", transport="stores", view_groups=None):
-        assert partition in ("planes", "tiles") and transport in ("stores", "copy")
+        assert partition in ("planes", "tiles") and transport in ("stores", "multicast", "copy")
         self.block, self.group = block, group
         self.G, self.rank = _world(group)
         self.S = S
@@ -120,7 +121,13 @@ class SlabGather:
                 torch.cuda.synchronize(device)
                 self.fh.barrier(channel=0)           # every rank's flags are zero before anyone's first epoch arrives
                 torch.cuda.synchronize(device)
-                self.mode = "peer_stores" if transport == "stores" else "copy_engine"
+                self.mode = "peer_stores" if transport in ("stores", "multicast") else "copy_engine"
+                self.mc = [0, 0]
+                if transport == "multicast":     # NVLS: one multimem.st per value, replicated by the switch into every rank's buffer
+                    self.mc = [int(hd.multicast_ptr) for hd in self.hdls]
+                    if not all(self.mc):
+                        raise RuntimeError("no multicast address: NVLS is not available for this group")
+                    self.mode = "peer_multicast"
                 if transport == "copy":
                     self.side = torch.cuda.Stream(device=device)
                     shape = (2, V, N, S, h, w)
@@ -184,7 +191,7 @@ class SlabGather:
     def __call__(self, **kwargs):
         if self.mode == "copy_engine":
             return self._call_copy(**kwargs)
-        if self.mode != "peer_stores":
+        if self.mode not in ("peer_stores", "peer_multicast"):
             return planesweep_correlation_slabs(self.block, self.group, **kwargs)
         self.epoch += 1
         k = self.epoch % 2
@@ -192,6 +199,8 @@ class SlabGather:
         half = buf[0].numel() * 4                   # bytes of the corr half of a buffer; the mask half follows it
         peers = dict(rank=self.rank, epoch=self.epoch, corr=[int(p) for p in hdl.buffer_ptrs],
                      mask=[int(p) + half for p in hdl.buffer_ptrs], flags=[int(p) for p in self.fh.buffer_ptrs])
+        if self.mode == "peer_multicast":
+            peers.update(corr_mc=self.mc[k], mask_mc=self.mc[k] + half)
         lo, hi = slab_range(self.S, self.G, self.rank)
         if self.partition == "tiles":               # every rank sweeps all planes of every G-th tile (RMVD_PARTITION_TILES)
             lo, hi = 0, self.S

@@ -8,7 +8,7 @@ import json
 d=json.load(open("$O/bench_n$N.json"))
 print({k:d[k] for k in ('value','ms_per_step','n_gpus')}, 'e2e', d['e2e']['value'], d['e2e']['ms_per_step'])
 sl=d.get('slab',{})
-for r in sl.get('planesweep',[]): print(r['views'], round(r['ms_1gpu'],4), {k:(round(r[k]['ms_total'],4), round(r[k]['speedup'],3), r[k]['bit_exact']) for k in ('planes','tiles','planes_copy')})
+for r in sl.get('planesweep',[]): print(r['views'], round(r['ms_1gpu'],4), {k:(r[k]['ms_total'] and round(r[k]['ms_total'],4), round(r[k]['speedup'],3), r[k]['bit_exact'], r[k]['mode'][:30]) for k in ('planes','tiles','planes_copy','planes_multicast','tiles_multicast')})
 print(sl.get('regress'), sl.get('error'))
 print([ (c['S'],c['V'],round(c['voxels_per_s']/1e9,1)) for c in d.get('sweep',{}).get('cells',[])][:20])
 PY
