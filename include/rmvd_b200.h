@@ -114,6 +114,26 @@ int rmvd_psweep_corr_fwd_peers(const float* feat_key, const float* const* feat_s
                                void* workspace, size_t workspace_bytes, void* stream);
 
 /*
+ * Depth slabs with a PUSHER kernel as the transport (no counterpart in the reference, see rmvd_psweep_corr_fwd_peers).  The sweep
+ * (on `stream`) stores its planes [s_begin, s_end) into this rank's own tensors corr_peers[rank] / mask_peers[rank] and publishes
+ * every finished chunk in `queue`; a second kernel (on `push_stream`, push_ctas CTAs on SMs the sweep leaves free) forwards the
+ * chunks' rows to the same place in every peer's tensors with 16-byte stores and ends with the ranks' flag handshake: when the work
+ * of `push_stream` has completed, all ranks' slabs are present in this rank's tensors.  The remote stores stall the pusher's warps
+ * instead of the sweep's sampling warps.  queue: 16-byte aligned device memory of rmvd_psweep_push_queue_bytes(N, h, w, V, planes of
+ * the slab) bytes, zeroed once when it is allocated, owned by the communicator (one call at a time); `epoch` as in
+ * rmvd_psweep_corr_fwd_peers.  stream != push_stream; the caller makes `stream` wait for `push_stream` before the next call.
+ */
+size_t rmvd_psweep_push_queue_bytes(int N, int h, int w, int V, int planes);
+int rmvd_psweep_corr_fwd_push(const float* feat_key, const float* const* feat_src, const float* intrinsics_key,
+                              const float* const* intrinsics_src, const float* const* src_to_key,
+                              const float* invdepths, const int64_t* inv_stride_host, int N, int C, int h, int w,
+                              int V, const int* hs_host, const int* ws_host, int S, int s_begin, int s_end,
+                              int normalize_mode, int out_S, int out_s0, int num_peers, int rank,
+                              float* const* corr_peers, float* const* mask_peers, uint32_t* const* flag_peers,
+                              uint32_t epoch, void* queue, size_t queue_bytes, int push_ctas, void* workspace,
+                              size_t workspace_bytes, void* stream, void* push_stream);
+
+/*
  * Transport of the depth-slab gather by the copy engines (no counterpart in the reference, see rmvd_psweep_corr_fwd_peers): `rows`
  * runs of row_bytes bytes, pitch_bytes apart in both buffers, from this rank's tensor to the same place in a peer-mapped tensor
  * (one cudaMemcpy2DAsync).  Used by parallel.SlabGather(transport="copy"): the slab of view group k travels while the kernel of

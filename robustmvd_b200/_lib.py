@@ -14,7 +14,8 @@ ABI_VERSION = 4
 
 EXPORTS = (
     "rmvd_abi_version", "rmvd_status_string", "rmvd_psweep_workspace_bytes", "rmvd_psweep_corr_fwd",
-    "rmvd_psweep_corr_fwd_peers", "rmvd_psweep_corr_fwd_static", "rmvd_copy_rows",
+    "rmvd_psweep_corr_fwd_peers", "rmvd_psweep_corr_fwd_static", "rmvd_copy_rows", "rmvd_psweep_corr_fwd_push",
+    "rmvd_psweep_push_queue_bytes",
     "rmvd_psweep_warp_fwd", "rmvd_psweep_bwd_workspace_bytes", "rmvd_psweep_corr_bwd",
     "rmvd_corr_grid_fwd", "rmvd_warp_grid_fwd", "rmvd_sampling_points_fwd", "rmvd_mvs_variance_fwd", "rmvd_mvs_variance_fwd_ws",
     "rmvd_mvs_variance_workspace_bytes",
@@ -43,6 +44,10 @@ def _declare(lib):
         [P, P, c_int, c_int, P]
     lib.rmvd_psweep_corr_fwd_peers.argtypes = [P, PP, P, PP, PP, P, PL] + [c_int] * 5 + [PI, PI] + [c_int] * 8 + \
         [PP, PP, PP, ctypes.c_uint32, c_int, P, P, P, c_size_t, P]
+    lib.rmvd_psweep_push_queue_bytes.restype = c_size_t
+    lib.rmvd_psweep_push_queue_bytes.argtypes = [c_int] * 5
+    lib.rmvd_psweep_corr_fwd_push.argtypes = [P, PP, P, PP, PP, P, PL] + [c_int] * 5 + [PI, PI] + [c_int] * 8 + \
+        [PP, PP, PP, ctypes.c_uint32, P, c_size_t, c_int, P, c_size_t, P, P]
     lib.rmvd_copy_rows.argtypes = [P, P, c_size_t, c_size_t, c_int, P]
     lib.rmvd_psweep_bwd_workspace_bytes.restype = c_size_t
     lib.rmvd_psweep_bwd_workspace_bytes.argtypes = [c_int, c_int, c_int, c_int, c_int, PI, PI]
@@ -73,7 +78,7 @@ def _declare(lib):
     lib.rmvd_debug_div_check.argtypes = [P, P, c_int, P, P, P]
     for name in EXPORTS:
         if name not in ("rmvd_abi_version", "rmvd_status_string", "rmvd_psweep_workspace_bytes",
-                        "rmvd_psweep_bwd_workspace_bytes", "rmvd_mvs_variance_workspace_bytes"):
+                        "rmvd_psweep_bwd_workspace_bytes", "rmvd_mvs_variance_workspace_bytes", "rmvd_psweep_push_queue_bytes"):
             getattr(lib, name).restype = c_int
 
 

@@ -506,6 +506,17 @@ class PlanesweepCorrelation(nn.Module):
             nb = lib.rmvd_psweep_workspace_bytes(N, C, h, w, V, _lib.int_array(hs), _lib.int_array(ws))
             wsp = _workspace(nb, dev)
             G = len(peers["corr"])
+            if peers.get("queue") is not None:       # push transport: a pusher kernel on peers["push_stream"] forwards the chunks
+                q = peers["queue"]
+                st = lib.rmvd_psweep_corr_fwd_push(
+                    _lib.ptr(feat_key), _lib.ptr_array(srcs), _lib.ptr(Kk), _lib.ptr_array(Ks), _lib.ptr_array(Ts),
+                    _lib.ptr(inv_c), ist, N, C, h, w, V, _lib.int_array(hs), _lib.int_array(ws), S, s0, s1,
+                    _corr_norm_mode(self.normalize) if norm_mode is None else norm_mode, S, s0, G, peers["rank"],
+                    _lib.raw_ptr_array(peers["corr"]), _lib.raw_ptr_array(peers["mask"]), _lib.raw_ptr_array(peers["flags"]),
+                    peers["epoch"], _lib.ptr(q), q.numel() * q.element_size(), int(peers.get("push_ctas", 8)), _lib.ptr(wsp),
+                    wsp.numel(), _lib.stream_ptr(), ctypes.c_void_p(peers["push_stream"].cuda_stream))
+                _lib.check(st, "rmvd_psweep_corr_fwd_push")
+                return None, None, inv
             st = lib.rmvd_psweep_corr_fwd_peers(
                 _lib.ptr(feat_key), _lib.ptr_array(srcs), _lib.ptr(Kk), _lib.ptr_array(Ks), _lib.ptr_array(Ts),
                 _lib.ptr(inv_c), ist, N, C, h, w, V, _lib.int_array(hs), _lib.int_array(ws), S, s0, s1,

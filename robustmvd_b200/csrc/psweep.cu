@@ -517,6 +517,51 @@ extern "C" int rmvd_psweep_corr_fwd_peers(const float* feat_key, const float* co
                               workspace, workspace_bytes, stream, &P);
 }
 
+// Push transport of the depth-slab gather (psweep_push.cu): the sweep stores locally and publishes finished chunks, a pusher kernel on
+// `push_stream` forwards them to the peers from the SMs the sweep leaves free and ends with the ranks' flag handshake.
+static unsigned push_queue_cap(int N, int h, int w, int V, int planes) {
+  int tw, th;
+  psweep_ws_tile_shape(h, w, &tw, &th);
+  const long long tiles = (long long)((w + tw - 1) / tw) * ((h + th - 1) / th);
+  const long long cap = tiles * N * V * ((planes + 3) / 4 + 1);      // a chunk holds at least 4 planes (or the item's last ones)
+  return (unsigned)(((cap > 0x3fffffffLL ? 0x3fffffffLL : cap) + 3) & ~3LL);
+}
+
+extern "C" size_t rmvd_psweep_push_queue_bytes(int N, int h, int w, int V, int planes) {
+  if (N <= 0 || h <= 0 || w <= 0 || V <= 0 || planes <= 0) return 0;
+  return 16 + (size_t)push_queue_cap(N, h, w, V, planes) * 20;
+}
+
+extern "C" int rmvd_psweep_corr_fwd_push(const float* feat_key, const float* const* feat_src, const float* intrinsics_key,
+                                         const float* const* intrinsics_src, const float* const* src_to_key, const float* invdepths,
+                                         const int64_t* inv_stride, int N, int C, int h, int w, int V, const int* hs, const int* ws, int S,
+                                         int s_begin, int s_end, int normalize_mode, int out_S, int out_s0, int num_peers, int rank,
+                                         float* const* corr_peers, float* const* mask_peers, uint32_t* const* flag_peers, uint32_t epoch,
+                                         void* queue, size_t queue_bytes, int push_ctas, void* workspace, size_t workspace_bytes,
+                                         void* stream, void* push_stream) {
+  if (!corr_peers || !mask_peers || !flag_peers || !queue) return RMVD_E_NULL;
+  if (num_peers < 1 || num_peers > RMVD_MAX_PEERS || rank < 0 || rank >= num_peers || push_ctas < 1 || push_ctas > 64) return RMVD_E_RANGE;
+  if (s_begin < 0 || s_end > S || s_begin > s_end) return RMVD_E_RANGE;
+  if (stream == push_stream) return RMVD_E_MODE;            // the pusher waits for the sweep: they must be able to run side by side
+  const size_t need = rmvd_psweep_push_queue_bytes(N, h, w, V, s_end > s_begin ? s_end - s_begin : 1);
+  if (queue_bytes < need || (uintptr_t)queue % 16 != 0) return RMVD_E_WORKSPACE;
+  PsweepPeers P{};
+  P.n = num_peers; P.rank = rank; P.epoch = epoch;
+  for (int g = 0; g < num_peers; ++g) {
+    if (!corr_peers[g] || !mask_peers[g] || !flag_peers[g]) return RMVD_E_NULL;
+    P.corr[g] = corr_peers[g]; P.mask[g] = mask_peers[g]; P.flags[g] = flag_peers[g];
+  }
+  P.q_head = (unsigned*)queue;
+  P.q_cap = (unsigned)((queue_bytes - 16) / 20) & ~3u;
+  P.push_ctas = push_ctas;
+  // the sweep first: only a sweep that was launched will ever close the queue (a pusher without one would wait for its time-out)
+  int rc = psweep_corr_fwd_impl(feat_key, feat_src, intrinsics_key, intrinsics_src, src_to_key, invdepths, inv_stride, N, C, h, w, V, hs, ws,
+                                S, s_begin, s_end, normalize_mode, P.corr[rank], P.mask[rank], out_S, out_s0, nullptr, nullptr, nullptr,
+                                workspace, workspace_bytes, stream, &P);
+  if (rc) return rc;
+  return launch_psweep_push(P, h, w, out_S, (cudaStream_t)push_stream);
+}
+
 // Copy-engine transport of the depth-slab gather: `rows` runs of `row_bytes` bytes, `pitch_bytes` apart in both buffers (a rank's
 // planes [lo, hi) of several [S,h,w] volumes), device to (peer) device.  One cudaMemcpy2DAsync: the copy engines move it at NVLink
 // speed without occupying an SM, so it overlaps the persistent plane-sweep kernel of the next view group (parallel.SlabGather).

@@ -51,9 +51,14 @@ struct PsweepPeers {
   unsigned* flags[RMVD_MAX_PEERS];
   unsigned epoch;
   float* corr_mc; float* mask_mc;  // optional NVSwitch multicast addresses of the same tensors (multimem.st: one store reaches every rank); NULL: one store per rank
+  unsigned* q_head; unsigned q_cap; int push_ctas;   // push transport: chunk queue (NULL: stores from the sampling loop), SMs left to the pusher kernel
   int by_tiles;                    // 0: the ranks split the planes (the caller's [s_begin, s_end)); 1: they split the work items (tiles), all planes each
 };
 // counter: 16 bytes of device memory: [0] work-item counter, [2] finished-CTA counter of the slab handshake
 int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, unsigned* counter, const PsweepPeers* peers, cudaStream_t st);
+// Pusher kernel of the depth-slab push transport: forwards the chunks the plane-sweep kernel publishes in the queue to every peer and
+// ends with the ranks' flag handshake.  corr / mask: this rank's own [V,N,out_S,h,w] tensors (entry `rank` of peers->corr / mask).
+int launch_psweep_push(const PsweepPeers& peers, int h, int w, int out_S, cudaStream_t st);
+void psweep_ws_tile_shape(int h, int w, int* tw_out, int* th_out);   // pixel tile of psweep_ws_kernel for an h x w key image
 
 }  // namespace rmvd

@@ -80,6 +80,8 @@ struct PeerArgs {                  // depth-slab mode (n > 0): peer-mapped outpu
   unsigned epoch;                  // this call's epoch (monotone per communicator)
   unsigned* done_ctas;             // local counter of finished CTAs
   float* corr_mc; float* mask_mc;  // multicast addresses of the output tensors, or NULL
+  unsigned* q_head;                // push mode: queue header {total, final epoch, pusher CTAs done, -}, then cap flags, then cap records
+  unsigned q_cap;
   int item_stride, item_offset;    // this launch works on items j * item_stride + item_offset (tile partition between the ranks); 1, 0 otherwise
 };
 
@@ -88,7 +90,8 @@ struct __align__(16) PlaneTerm { float ed, id, md, zs; };   // e*d, i*d, m*d, 1/
 struct __align__(16) RowSpan { int xa, lenm1, offp, len; };
 
 enum { kStop = 0, kGemm = 1, kDirect = 2 };
-enum { kModePlain = 0, kModePeers = 1, kModeDebug = 2 };   // kernel variants: outputs only / + peer stores (depth slabs) / + debug outputs
+enum { kModePlain = 0, kModePeers = 1, kModeDebug = 2, kModePush = 3 };   // kernel variants: outputs only / + peer stores (depth slabs) / + debug outputs /
+                                                                          // local stores + a record of every finished chunk for the pusher kernel
 
 struct __align__(16) ChunkDesc {
   RowSpan rows[kMaxRows];
@@ -133,7 +136,10 @@ __device__ __forceinline__ void stcs_at(float* base, size_t off, float v) { __st
 template <int kMode, typename Off>
 __device__ __forceinline__ void store_out(const WsConst& W, float* __restrict__ corr, float* __restrict__ mask, size_t base, Off o, float c,
                                           float m) {
-  if (kMode != kModePeers) {
+  if (kMode == kModePush) {      // the pusher kernel re-reads these rows within microseconds: keep them in L2 (no evict-first hint)
+    corr[o] = c;
+    mask[o] = m;
+  } else if (kMode != kModePeers) {
     stcs_at(corr, o, c);
     stcs_at(mask, o, m);
   } else {
@@ -269,7 +275,7 @@ __global__ void __launch_bounds__(256) nchw_to_grouped_kernel(const GroupBatch B
   __shared__ float tile[kRpCh][33];
   __shared__ float s_norm[32];
   const int which = blockIdx.z / N, n = blockIdx.z - which * N;
-  if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0) { B.counter[0] = 0u; B.counter[2] = 0u; }
+  if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0) { B.counter[0] = 0u; B.counter[1] = 0u; B.counter[2] = 0u; }
   const int hs = B.hs[which], ws = B.ws[which];
   const int wg = (ws + 7) >> 3, tpr = (wg + 3) >> 2;        // groups per row, 32-texel tiles per row
   if ((int)blockIdx.x >= tpr * hs) return;                   // maps of different sizes share the grid of the largest
@@ -1200,8 +1206,20 @@ __device__ void direct_chunk(const PsweepArgs& A, const ChunkDesc* D, int cw, in
   }
 }
 
+// push mode: one record per finished chunk {view-sample index, first output plane, planes, first pixel of the tile}; the slot's flag
+// carries the call's epoch once the record AND the chunk's output rows are visible device-wide
+__device__ __forceinline__ void publish_chunk(unsigned* q_head, unsigned q_cap, unsigned* tail, unsigned epoch, const int4& rec) {
+  const unsigned slot = atomicAdd(tail, 1u);
+  if (slot >= q_cap) return;                          // the host sized the queue for the worst case; never expected
+  int4* recs = reinterpret_cast<int4*>(q_head + 4 + q_cap);
+  recs[slot] = rec;
+  __threadfence();                                    // cumulative: the consumer barrier before this call ordered every warp's stores before it
+  asm volatile("st.release.gpu.global.u32 [%0], %1;\n" ::"l"(q_head + 4 + slot), "r"(epoch) : "memory");
+}
+
 template <int kMode>
-__device__ void consumer(const PsweepArgs& A, ChunkDesc* descs, float* G, unsigned bars, unsigned tmem) {
+__device__ void consumer(const PsweepArgs& A, ChunkDesc* descs, float* G, unsigned bars, unsigned tmem, unsigned* q_head, unsigned q_cap,
+                         unsigned* q_tail, unsigned epoch) {
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int cw = warp - 4, q = warp & 3, part = (warp >> 2) - 1;   // TMEM lane quadrant, which of its four warps
   const unsigned bar_cready = bars + 8 * kBarCReady, bar_cfree = bars + 8 * kBarCFree, bar_acc = bars + 8 * kBarAcc,
@@ -1215,6 +1233,8 @@ __device__ void consumer(const PsweepArgs& A, ChunkDesc* descs, float* G, unsign
   const bool rec = (t == 128);
   const long long cs_t0 = clock64();
 #endif
+  int4 prev_rec = make_int4(0, 0, 0, 0);
+  bool have_prev = false;
   for (unsigned seq = 0;; ++seq) {
     const unsigned slot = seq % kDescs;
     {
@@ -1242,6 +1262,11 @@ __device__ void consumer(const PsweepArgs& A, ChunkDesc* descs, float* G, unsign
 #ifdef RMVD_WS_STATS
       if (rec) WS_ADD(17);
 #endif
+    }
+    if (kMode == kModePush && t == 128) {              // ... and its output rows are complete: hand the previous chunk to the pusher
+      if (have_prev) publish_chunk(q_head, q_cap, q_tail, epoch, prev_rec);
+      prev_rec = make_int4((int)(D->out_base / ((unsigned long long)A.out_S * (unsigned long long)(A.h * A.w))), D->out_plane0, D->len, D->pix[0]);
+      have_prev = true;
     }
 #ifdef RMVD_WS_STATS
     const long long dr_t0 = clock64();
@@ -1302,6 +1327,10 @@ __device__ void consumer(const PsweepArgs& A, ChunkDesc* descs, float* G, unsign
 #endif
     if (lane == 0) mbar_arrive(bar_cfree + 8 * slot);
   }
+  if (kMode == kModePush) {                            // the last chunk of this CTA
+    cons_bar();
+    if (t == 128 && have_prev) publish_chunk(q_head, q_cap, q_tail, epoch, prev_rec);
+  }
 #ifdef RMVD_WS_STATS
   if (rec) atomicAdd(&g_ws_stats[23], (unsigned long long)(clock64() - cs_t0));
 #endif
@@ -1359,13 +1388,25 @@ __global__ void __launch_bounds__(kThreads, 1) psweep_ws_kernel(const PsweepArgs
     }
   } else {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" ::"n"(kRegsConsumer));
-    consumer<kMode>(A, descs, G, bars, tmem);
+    consumer<kMode>(A, descs, G, bars, tmem, PA.q_head, PA.q_cap, counter + 1, PA.epoch);
   }
 
   if (kMode == kModePeers) __threadfence_system();                // this thread's peer stores are ordered before the handshake below
   asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
   __syncthreads();
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem), "r"(kTmemCols));
+  if (kMode == kModePush && t == 0) {
+    // the last CTA of the launch closes the queue: total number of records, then the call's epoch in the final flag
+    __threadfence();
+    const unsigned prev = atomicAdd(PA.done_ctas, 1u);
+    if (prev == gridDim.x - 1) {
+      *PA.done_ctas = 0u;
+      const unsigned total = atomicAdd(counter + 1, 0u);
+      PA.q_head[0] = total < PA.q_cap ? total : PA.q_cap;
+      __threadfence();
+      asm volatile("st.release.gpu.global.u32 [%0], %1;\n" ::"l"(PA.q_head + 1), "r"(PA.epoch) : "memory");
+    }
+  }
   if (kMode == kModePeers && t == 0) {
     // End-of-kernel handshake of the depth-slab mode: the last CTA of this rank publishes the call's epoch in every rank's flag
     // array and waits until all ranks have published theirs, so that when this kernel completes, every rank's rows have landed
@@ -1487,6 +1528,7 @@ int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, uns
     if (e == cudaSuccess) e = cudaFuncSetAttribute(ws::psweep_ws_kernel<ws::kModePlain>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws::smem_bytes());
     if (e == cudaSuccess) e = cudaFuncSetAttribute(ws::psweep_ws_kernel<ws::kModePeers>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws::smem_bytes());
     if (e == cudaSuccess) e = cudaFuncSetAttribute(ws::psweep_ws_kernel<ws::kModeDebug>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws::smem_bytes());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(ws::psweep_ws_kernel<ws::kModePush>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws::smem_bytes());
     if (e != cudaSuccess) return (int)e;
     attr_set = true;
   }
@@ -1503,13 +1545,16 @@ int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, uns
     if (peers->n > ws::kMaxPeers || peers->rank < 0 || peers->rank >= peers->n || A.dbg_ix0) return (int)cudaErrorInvalidValue;
     PA.n = peers->n; PA.rank = peers->rank; PA.epoch = peers->epoch; PA.done_ctas = counter + 2;
     PA.corr_mc = peers->corr_mc; PA.mask_mc = peers->mask_mc;
+    PA.q_head = peers->q_head; PA.q_cap = peers->q_cap;
     if (peers->by_tiles) {           // this rank's share of the items: rank, rank + n, rank + 2 n, ...
       PA.item_stride = peers->n; PA.item_offset = peers->rank;
       items = (items - peers->rank + peers->n - 1) / peers->n;
     }
     for (int g = 0; g < peers->n; ++g) { PA.corr[g] = peers->corr[g]; PA.mask[g] = peers->mask[g]; PA.flags[g] = peers->flags[g]; }
   }
-  const unsigned grid = (unsigned)(items < num_sms ? (items > 0 ? items : 1) : num_sms);   // a rank without items still runs the handshake
+  const bool push = PA.n > 0 && PA.q_head != nullptr;
+  const int sms = push ? (num_sms - peers->push_ctas > 8 ? num_sms - peers->push_ctas : 8) : num_sms;   // push transport: the pusher kernel's SMs stay free
+  const unsigned grid = (unsigned)(items < sms ? (items > 0 ? items : 1) : sms);   // a rank without items still runs the handshake
 #ifdef RMVD_WS_STATS
   {
     unsigned long long z[32] = {0};
@@ -1517,7 +1562,9 @@ int launch_psweep_ws(const PsweepArgs& A, const void* key_split, int nviews, uns
   }
 #endif
   const auto ks = reinterpret_cast<const __nv_bfloat16*>(key_split);
-  if (PA.n > 0)
+  if (push)
+    ws::psweep_ws_kernel<ws::kModePush><<<grid, ws::kThreads, ws::smem_bytes(), st>>>(A, ks, tw, th, tiles_x, tiles, items, counter, PA);
+  else if (PA.n > 0)
     ws::psweep_ws_kernel<ws::kModePeers><<<grid, ws::kThreads, ws::smem_bytes(), st>>>(A, ks, tw, th, tiles_x, tiles, items, counter, PA);
   else if (A.dbg_ix0)
     ws::psweep_ws_kernel<ws::kModeDebug><<<grid, ws::kThreads, ws::smem_bytes(), st>>>(A, ks, tw, th, tiles_x, tiles, items, counter, PA);

@@ -86,7 +86,8 @@ class SlabGather:
     ``k % 2``, and cannot start call ``k + 2`` before the slower rank has finished call ``k + 1`` (the handshake).
 
     ``transport="multicast"``: the sampling loop issues one ``multimem.st`` per value to the buffers' NVSwitch multicast address (NVLS)
-    instead of one store per rank; ``transport="copy"``: see ``_call_copy``.  ``partition="tiles"``: the ranks split the (tile, sample, view) work items instead of the planes -- same result on every rank, and
+    instead of one store per rank; ``transport="copy"``: see ``_call_copy``; ``transport="push"``: the sweep stores locally and a pusher
+    kernel on ``push_ctas`` SMs of a side stream forwards the finished chunks (``rmvd_psweep_corr_fwd_push``).  ``partition="tiles"``: the ranks split the (tile, sample, view) work items instead of the planes -- same result on every rank, and
     the per-tile costs that do not shrink with the plane count (key tile, band planning, band rows) are divided too; at one frame
     this is the partition that is faster than one GPU.
 
@@ -95,8 +96,11 @@ class SlabGather:
     not available (``mode == "all_gather"``), e.g. in the CPU tests of the host logic.
     """
 
-    def __init__(self, block, V, N, S, h, w, device, group=None, partition="planes", transport="stores", view_groups=None):
-        assert partition in ("planes", "tiles") and transport in ("stores", "multicast", "copy")
+    def __init__(self, block, V, N, S, h, w, device, group=None, partition="planes", transport="stores", view_groups=None,
+                 push_ctas=8):
+        assert partition in ("planes", "tiles") and transport in ("stores", "multicast", "copy", "push")
+        assert not (transport == "push" and partition != "planes")
+        self.push_ctas = push_ctas
         self.block, self.group = block, group
         self.G, self.rank = _world(group)
         self.S = S
@@ -121,13 +125,21 @@ class SlabGather:
                 torch.cuda.synchronize(device)
                 self.fh.barrier(channel=0)           # every rank's flags are zero before anyone's first epoch arrives
                 torch.cuda.synchronize(device)
-                self.mode = "peer_stores" if transport in ("stores", "multicast") else "copy_engine"
+                self.mode = "peer_stores" if transport in ("stores", "multicast", "push") else "copy_engine"
                 self.mc = [0, 0]
                 if transport == "multicast":     # NVLS: one multimem.st per value, replicated by the switch into every rank's buffer
                     self.mc = [int(hd.multicast_ptr) for hd in self.hdls]
                     if not all(self.mc):
                         raise RuntimeError("no multicast address: NVLS is not available for this group")
                     self.mode = "peer_multicast"
+                if transport == "push":          # a pusher kernel on a side stream forwards finished chunks to the peers
+                    from . import _lib
+                    lo, hi = slab_range(S, self.G, self.rank)
+                    nb = _lib.load().rmvd_psweep_push_queue_bytes(N, h, w, V, max(hi - lo, 1))
+                    self.queue = torch.zeros((nb + 15) // 16 * 4, dtype=torch.int32, device=device)
+                    self.side = torch.cuda.Stream(device=device)
+                    torch.cuda.synchronize(device)
+                    self.mode = "peer_push"
                 if transport == "copy":
                     self.side = torch.cuda.Stream(device=device)
                     shape = (2, V, N, S, h, w)
@@ -191,7 +203,7 @@ class SlabGather:
     def __call__(self, **kwargs):
         if self.mode == "copy_engine":
             return self._call_copy(**kwargs)
-        if self.mode not in ("peer_stores", "peer_multicast"):
+        if self.mode not in ("peer_stores", "peer_multicast", "peer_push"):
             return planesweep_correlation_slabs(self.block, self.group, **kwargs)
         self.epoch += 1
         k = self.epoch % 2
@@ -205,6 +217,12 @@ class SlabGather:
         if self.partition == "tiles":               # every rank sweeps all planes of every G-th tile (RMVD_PARTITION_TILES)
             lo, hi = 0, self.S
             peers["partition"] = 1
+        if self.mode == "peer_push":
+            main = torch.cuda.current_stream()
+            peers.update(queue=self.queue, push_stream=self.side, push_ctas=self.push_ctas)
+            _, _, inv = self.block._forward_impl(plane_range=(lo, hi), peers=peers, **kwargs)
+            main.wait_stream(self.side)             # the pusher's handshake closes the call; it also guards the queue's reuse
+            return list(buf[0].unbind(0)), list(buf[1].unbind(0)), inv
         _, _, inv = self.block._forward_impl(plane_range=(lo, hi), peers=peers, **kwargs)
         return list(buf[0].unbind(0)), list(buf[1].unbind(0)), inv
 

@@ -68,6 +68,15 @@ def test_argument_validation_needs_no_device(lib):
                                     one, arr, one, 16, null) == -4                  # RMVD_E_WORKSPACE
     assert lib.rmvd_psweep_bwd_workspace_bytes(1, 8, 4, 4, 1, ints, ints) == 3 * 512
     assert lib.rmvd_homography_groupcorr_fwd(one, one, one, st, 1, 10, 4, 4, 2, 4, one, null) == -2  # C % groups != 0
+    # push transport of the depth slabs: queue size, same stream twice, queue too small (all before any device work)
+    q1, q2 = lib.rmvd_psweep_push_queue_bytes(1, 96, 144, 1, 128), lib.rmvd_psweep_push_queue_bytes(1, 96, 144, 2, 128)
+    assert q1 > 16 and (q1 - 16) % 80 == 0 and q2 - 16 == 2 * (q1 - 16) and lib.rmvd_psweep_push_queue_bytes(1, 96, 144, 0, 8) == 0
+    big = ctypes.c_void_p(4096)
+    push = lambda q_bytes, s0, s1, ctas: lib.rmvd_psweep_corr_fwd_push(  # noqa: E731
+        one, arr, one, arr, arr, one, st, 1, 64, 4, 4, 1, ints, ints, 4, 0, 4, 1, 4, 0, 1, 0, arr, arr, arr, 1, big, q_bytes, ctas, one, 1 << 20, s0, s1)
+    assert push(1 << 20, null, null, 8) == -3            # RMVD_E_MODE: the pusher cannot share the sweep's stream
+    assert push(64, null, one, 8) == -4                  # RMVD_E_WORKSPACE: queue smaller than rmvd_psweep_push_queue_bytes
+    assert push(1 << 20, null, one, 0) == -5             # RMVD_E_RANGE: no pusher CTAs
 
 
 def test_missing_library_fails_loudly(monkeypatch, tmp_path):

@@ -68,3 +68,50 @@ def test_emulated_ranks_assemble_to_the_full_volume(cuda_lib):
         for v in range(2):
             assert torch.equal(torch.cat([p[0][v] for p in parts], 1), full_c[v])
             assert torch.equal(torch.cat([p[1][v] for p in parts], 1), full_m[v])
+
+
+@pytest.mark.parametrize("variant,w", [("planes", 40), ("tiles", 40), ("push", 40), ("push", 42)])
+@pytest.mark.parametrize("G", [2, 3])
+def test_peer_transports_with_emulated_ranks(cuda_lib, variant, w, G):
+    """The depth-slab kernels of ``parallel.SlabGather`` (rmvd_psweep_corr_fwd_peers with the plane and the tile partition,
+    rmvd_psweep_corr_fwd_push) with G ranks emulated one after another on one GPU: every "rank" owns a [2,V,N,S,h,w] buffer,
+    all of them addressable by all (the same device), and the flags of the closing handshake are preset so that no rank waits
+    for one that has not run yet.  After the G calls every buffer holds the full volumes, bit for bit those of one plain call."""
+    from robustmvd_b200.blocks.planesweep_corr import PlanesweepCorrelation
+    cu = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
+    h, V, S = 24, 3, 37                                  # (w = 42: rows that are not 16-byte multiples, the pusher's scalar path)
+    inp = syn.planesweep_inputs(h, w, 64, V, seed=11)
+    kw = dict(feat_key=cu(inp["feat_key"]), intrinsics_key=cu(inp["intrinsics_key"]),
+              feat_sources=[cu(f) for f in inp["feat_sources"]], source_to_key_transforms=[cu(t) for t in inp["transforms"]],
+              num_sampling_points=S, min_depth=0.4, max_depth=1000.0)
+    blk = PlanesweepCorrelation()
+    full_c, full_m, _ = blk(**kw)
+    N = full_c[0].shape[0]
+    lib = cuda_lib
+    side = torch.cuda.Stream()
+    for epoch in (1, 2):                                 # the second call reuses flags, queues and counters
+        bufs = [torch.full((2, V, N, S, h, w), float("nan"), device="cuda") for _ in range(G)]
+        flags = [torch.full((64,), epoch, dtype=torch.int32, device="cuda") for _ in range(G)]
+        if epoch == 1:
+            queues = []
+            for r in range(G):
+                lo, hi = parallel.slab_range(S, G, r)
+                nb = lib.rmvd_psweep_push_queue_bytes(N, h, w, V, max(hi - lo, 1))
+                assert nb > 16
+                queues.append(torch.zeros((nb + 15) // 16 * 4, dtype=torch.int32, device="cuda"))
+        half = bufs[0][0].numel() * 4
+        for r in range(G):
+            peers = dict(rank=r, epoch=epoch, corr=[b.data_ptr() for b in bufs], mask=[b.data_ptr() + half for b in bufs],
+                         flags=[f.data_ptr() for f in flags])
+            lo, hi = parallel.slab_range(S, G, r)
+            if variant == "tiles":
+                lo, hi = 0, S
+                peers["partition"] = 1
+            if variant == "push":
+                peers.update(queue=queues[r], push_stream=side, push_ctas=4)
+            blk._forward_impl(plane_range=(lo, hi), peers=peers, **kw)
+            torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        for b in bufs:
+            assert all(torch.equal(b[0, v], full_c[v]) for v in range(V)) and all(torch.equal(b[1, v], full_m[v]) for v in range(V))
+        assert all(int(f[r].item()) == epoch for f in flags for r in range(G))
