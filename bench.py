@@ -513,13 +513,19 @@ def run_ours(args):
     P = CFG["h"] * CFG["w"]
     out_host = torch.empty((2, CFG["V"], frames, CFG["S"], CFG["h"], CFG["w"]), dtype=torch.float32).pin_memory()
 
-    pipe = HostPlanesweepPipeline(dev, block, chunk_frames=[int(c) for c in str(args.e2e_chunk).split(',')])
+    chunks = [int(c) for c in str(args.e2e_chunk).split(',')]
+    pipe = HostPlanesweepPipeline(dev, block, chunk_frames=chunks, compact_mask=True,      # mask over PCIe as bytes, expanded on the host
+                                  mask_threads=args.e2e_mask_threads or None)
+    pipe_f32 = HostPlanesweepPipeline(dev, block, chunk_frames=chunks, compact_mask=False)  # mask over PCIe as float32
 
     def step_e2e():   # pinned host features in, corr + mask back in pinned host memory; returns after the last byte landed
         pipe.run(host["feat_key"], Kk, host["feat_sources"], Ts, out_host[0], out_host[1], **KW)
 
     def step_e2e_stream():   # same, as a stream of batches: queued, consecutive batches overlap; finish() ends the timed region
         pipe.run(host["feat_key"], Kk, host["feat_sources"], Ts, out_host[0], out_host[1], wait=False, **KW)
+
+    def step_e2e_stream_f32():
+        pipe_f32.run(host["feat_key"], Kk, host["feat_sources"], Ts, out_host[0], out_host[1], wait=False, **KW)
 
     def barrier():
         torch.cuda.synchronize()
@@ -551,8 +557,16 @@ def run_ours(args):
         sampler.start()
     ms_step = timed(step_device, args.steps, args.warmup)
     clocks = sampler.stop() if rank == 0 else None
+    pipe_threads = pipe.mask_threads
     ms_e2e_blocking = timed(step_e2e, max(2, args.steps // 4), 2)
     ms_e2e = timed(step_e2e_stream, max(4, args.steps // 4), 3, finish=pipe.finish)
+    ms_e2e_f32 = timed(step_e2e_stream_f32, max(4, args.steps // 4), 3, finish=pipe_f32.finish)
+    # the compact transport must leave exactly the float32 mask of the plain copy in the host buffer (checked on the last step)
+    mask_compact = out_host[1].clone()
+    step_e2e_stream_f32()
+    pipe_f32.finish()
+    e2e_mask_equal = bool(torch.equal(mask_compact, out_host[1]))
+    del mask_compact
 
     # per-call device time of the hot path alone (no flush), CUDA events on the launching stream
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
@@ -569,7 +583,7 @@ def run_ours(args):
 
     extra = {}
     if not args.no_secondary:
-        del pipe, out_host
+        del pipe, pipe_f32, out_host
         extra["sweep"] = sweep_records(torch, dist, dev, world, peaks)
         if world > 1:
             try:
@@ -592,7 +606,8 @@ def run_ours(args):
         ms_launch = ms_call if flush is not None else ms_step
         achieved = ab / (ms_launch * 1e-3) / 1e9
         h2d = 4 * frames * CFG["C"] * P * (1 + CFG["V"])
-        d2h = 2 * 4 * frames * CFG["V"] * CFG["S"] * P
+        d2h_f32 = 2 * 4 * frames * CFG["V"] * CFG["S"] * P
+        d2h = (4 + 1) * frames * CFG["V"] * CFG["S"] * P       # corr float32 + mask as bytes
         line = base_line(args, frames, world)
         line.update({
             "impl": "ours", "value": voxels(frames) * world / (ms_step * 1e-3), "ms_per_step": ms_step,
@@ -602,12 +617,18 @@ def run_ours(args):
                     "h2d_gbs_per_rank": h2d / ms_e2e / 1e6, "d2h_gbs_per_rank": d2h / ms_e2e / 1e6,
                     "ms_per_step_blocking": ms_e2e_blocking,
                     "value_blocking": voxels(frames) * world / (ms_e2e_blocking * 1e-3),
+                    "mask_transport": "u8 over PCIe (rmvd_mask_pack_u8) + host expansion to float32 (rmvd_host_expand_mask_async, "
+                                      "%d worker threads) inside the timed region" % pipe_threads,
+                    "host_mask_bit_identical_to_float32_copy": e2e_mask_equal,
+                    "float32_mask_transport": {"ms_per_step": ms_e2e_f32, "value": voxels(frames) * world / (ms_e2e_f32 * 1e-3),
+                                               "d2h_bytes_per_step": d2h_f32, "h2d_gbs_per_rank": h2d / ms_e2e_f32 / 1e6,
+                                               "d2h_gbs_per_rank": d2h_f32 / ms_e2e_f32 / 1e6},
                     "api": "HostPlanesweepPipeline.run(wait=False) per step + finish(): PlanesweepCorrelation.forward per chunk "
-                           "of %s frames from pinned host buffers, corr + mask copied back to pinned host memory every step; "
-                           "H2D / kernels / D2H of consecutive chunks AND of consecutive steps overlap on 3 streams "
-                           "(double-buffered device inputs).  *_blocking: each step waits for its last byte before the next "
-                           "starts (latency of one batch)" % args.e2e_chunk},
-            "gpu_launches": args.steps * 3,   # key repack + source repack (all views) + one persistent plane-sweep kernel per step
+                           "of %s frames from pinned host buffers, corr + mask (float32, the block's outputs bit for bit) back in "
+                           "pinned host memory every step; H2D / kernels / D2H / host expansion of consecutive chunks AND of "
+                           "consecutive steps overlap on 4 streams (double-buffered device inputs).  *_blocking: each step waits "
+                           "for its last byte before the next starts (latency of one batch)" % args.e2e_chunk},
+            "gpu_launches": args.steps * 3,   # (device-resident leg) key repack + source repack (all views) + one persistent plane-sweep kernel per step
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": achieved / peaks["hbm_gbs"], "traffic": ncu_traffic(frames), "peak_source": which,
                          "kernel": "rmvd_psweep_corr_fwd = nchw_to_keytiles_kernel + nchw_to_grouped_kernel (split copies) + "
@@ -647,6 +668,7 @@ def main():
     ap.add_argument("--frames", type=int, default=16, help="frames per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true", help="headline line only (no secondary / baseline / sweep / slab records)")
+    ap.add_argument("--e2e-mask-threads", type=int, default=0, help="worker threads of the host-side mask expansion (0 = pipeline default)")
     ap.add_argument("--e2e-chunk", default="2", help="frames per chunk of the host pipeline (e2e leg); a,b,c = schedule, last repeats")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define RMVD_ABI_VERSION 4
+#define RMVD_ABI_VERSION 5
 #define RMVD_MAX_PEERS 8      /* ranks of one depth-slab communicator (GPUs of one NVSwitch box) */
 
 #define RMVD_OK 0
@@ -164,6 +164,23 @@ int rmvd_psweep_corr_fwd_static(const float* feat_key, const float* const* feat_
                                 const float* invdepths, const int64_t* inv_stride_host, int N, int C, int h, int w,
                                 int V, const int* hs_host, const int* ws_host, int S, int s_begin, int s_end,
                                 int normalize_mode, float* corr, float* mask, int out_S, int out_s0, void* stream);
+
+/*
+ * Compact transport of the sampling mask for callers whose outputs go back to HOST memory (pipeline.HostPlanesweepPipeline; the
+ * reference keeps corr and mask on the device, robust_mvd.py:71-82, so these three have no counterpart there).  The mask of
+ * PlanesweepCorrelation.forward (planesweep_corr.py:99-102, :189-191) is a float32 tensor of 0.0 / 1.0 values: half of the bytes
+ * of a device-to-host copy of the block's outputs.
+ *   rmvd_mask_pack_u8            device: packed[i] = mask[i] != 0 (one byte per element; mask 16-byte, packed 4-byte aligned)
+ *   rmvd_host_expand_mask        host, synchronous: mask_host[i] = (float)packed_host[i] on `threads` worker threads (streaming
+ *                                stores); the result is bit-identical to a float32 copy of the device mask
+ *   rmvd_host_expand_mask_async  the same as a host function queued on `stream` (cudaLaunchHostFunc): runs after the work queued
+ *                                before it (the device-to-host copy of `packed`), work queued after it on the stream waits for it
+ * Both host pointers must stay valid until the expansion has run.  The worker pool (<= 32 threads, created on first use) is the one
+ * piece of process-wide state; concurrent expansions are serialised.
+ */
+int rmvd_mask_pack_u8(const float* mask, uint8_t* packed, size_t n, void* stream);
+int rmvd_host_expand_mask(const uint8_t* packed_host, float* mask_host, size_t n, int threads);
+int rmvd_host_expand_mask_async(const uint8_t* packed_host, float* mask_host, size_t n, int threads, void* stream);
 
 /*
  * Backward of rmvd_psweep_corr_fwd with respect to the feature maps.  The reference obtains it from

@@ -94,11 +94,38 @@ class RobustMVD(nn.Module):
         if (orig_ht, orig_wd) != (ht, wd):
             resized = ResizeInputs(size=(ht, wd))({"images": images, "intrinsics": intrinsics})
             images, intrinsics = resized["images"], resized["intrinsics"]
-        images = [image / 255.0 - 0.4 for image in images]
         scale_arr = np.array([[wd] * 3, [ht] * 3, [1.0] * 3], dtype=np.float32)
         intrinsics = [K / scale_arr for K in intrinsics]
-        images, keyview_idx, poses, intrinsics = to_torch((images, keyview_idx, poses, intrinsics), device=device)
+        if (device.type == "cuda" and os.environ.get("RMVD_DEVICE_NORMALIZE", "1") != "0"
+                and all(isinstance(im, np.ndarray) and im.dtype == np.float32 and im.shape == images[0].shape for im in images)):
+            images = self._upload_and_normalize(images, device)
+            keyview_idx, poses, intrinsics = to_torch((keyview_idx, poses, intrinsics), device=device)
+        else:
+            images = [image / 255.0 - 0.4 for image in images]
+            images, keyview_idx, poses, intrinsics = to_torch((images, keyview_idx, poses, intrinsics), device=device)
         return {"images": images, "keyview_idx": keyview_idx, "poses": poses, "intrinsics": intrinsics}
+
+    def _upload_and_normalize(self, images, device):
+        """``image / 255.0 - 0.4`` (robust_mvd.py:118) on the device instead of in numpy: the raw float32 images go through ONE pinned
+        staging buffer and one host-to-device copy, the two float32 operations (a true IEEE division by a device scalar -- torch
+        turns a division by a Python scalar into a multiplication by the reciprocal -- and a subtraction) run as two launches on
+        the whole stack.  Bit-identical to the numpy expression; ``RMVD_DEVICE_NORMALIZE=0`` restores the host path."""
+        shape = (len(images),) + tuple(images[0].shape)
+        st = getattr(self, "_stage", None)
+        if st is None or tuple(st[0].shape) != shape or st[2].device != device:
+            st = [torch.empty(shape, dtype=torch.float32).pin_memory(), None, torch.full((), 255.0, dtype=torch.float32, device=device)]
+            self._stage = st
+        if st[1] is not None:
+            st[1].synchronize()                           # the previous call's copy out of the staging buffer has completed
+        buf = st[0].numpy()
+        for i, im in enumerate(images):
+            np.copyto(buf[i], im)
+        d = st[0].to(device, non_blocking=True)
+        st[1] = torch.cuda.Event()
+        st[1].record(torch.cuda.current_stream(device))
+        d = torch.div(d, st[2])
+        d -= 0.4
+        return list(d.unbind(0))
 
     def output_adapter(self, model_output):
         pred, aux = model_output

@@ -9,15 +9,42 @@ rmvd/models/blocks/planesweep_corr.py:396-427) on a slice of the batch.
 A stream of batches (``run(..., wait=False)`` per batch, ``finish()`` at the end) also overlaps consecutive batches: the
 device-side input buffers are double-buffered, so the H2D copy of batch i+1 runs under the kernels and the D2H copy of batch
 i and the steady-state cost of a batch is the longer of its two PCIe directions.
+
+``compact_mask=True`` (default) sends the sampling mask over PCIe as one byte per element instead of four: the mask holds only
+0.0 and 1.0 (planesweep_corr.py:99-102, :189-191) and is half of the device-to-host bytes.  ``rmvd_mask_pack_u8`` packs it on the
+device, the bytes land in a pinned staging ring, and ``rmvd_host_expand_mask_async`` -- a host function queued on a fourth stream,
+running on the library's worker threads -- writes the float32 values into ``out_mask``; the host buffer ends up bit-identical to
+the plain float32 copy (``compact_mask=False``).
 """
+import ctypes
+import os
+
 import torch
 
+from . import _lib
 from .blocks.planesweep_corr import PlanesweepCorrelation
 
 
+def _default_mask_threads():
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        cores = os.cpu_count() or 1
+    ranks = int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", "1")) or 1)
+    # measured on the B200 box (16 host cores, cfg2, 16 frames per step): 8.60 / 8.81 / 9.16 / 9.71 ms per step with 2 / 4 / 8 / 12
+    # threads (more threads take memory bandwidth and cores from the DMA engines and the issuing Python thread), 2 is at the
+    # edge of keeping up with the copies: 3
+    return max(1, min(3, cores // max(1, ranks) - 1))
+
+
 class HostPlanesweepPipeline:
-    def __init__(self, device, block=None, chunk_frames=2):
+    def __init__(self, device, block=None, chunk_frames=2, compact_mask=True, mask_threads=None):
         self.device = torch.device(device)
+        self.compact_mask = bool(compact_mask)
+        self.mask_threads = int(mask_threads) if mask_threads else _default_mask_threads()
+        self.s_exp = torch.cuda.Stream(self.device)      # carries the host-side mask expansion (host functions only)
+        self._stage = [None] * 4                          # pinned byte staging ring: [tensor, event after its expansion]
+        self._stages = 0
         self.block = block if block is not None else PlanesweepCorrelation()
         # int: equal chunks; sequence: chunk sizes in order, the last one repeating (a small first chunk starts the D2H
         # stream earlier, which is the longer of the two copy directions)
@@ -52,10 +79,25 @@ class HostPlanesweepPipeline:
             if e is not None:
                 e[3].synchronize()
             e = [shape, torch.empty(shape, dtype=torch.float32, device=self.device),
-                 torch.empty(shape, dtype=torch.float32, device=self.device), None]
+                 torch.empty(shape, dtype=torch.float32, device=self.device), None,
+                 torch.empty(shape, dtype=torch.uint8, device=self.device) if self.compact_mask else None]
             self._out_ring[slot] = e
         elif e[3] is not None:
             self.s_cmp.wait_event(e[3])                   # the previous contents have been copied out
+        return e
+
+    def _staging(self, shape):
+        """Next pinned byte buffer of the staging ring; ``s_out`` waits until the expansion that last read it has run."""
+        slot = self._stages % len(self._stage)
+        self._stages += 1
+        e = self._stage[slot]
+        if e is None or tuple(e[0].shape) != tuple(shape):
+            if e is not None and e[1] is not None:
+                e[1].synchronize()
+            e = [torch.empty(shape, dtype=torch.uint8).pin_memory(), None]
+            self._stage[slot] = e
+        elif e[1] is not None:
+            self.s_out.wait_event(e[1])
         return e
 
     def finish(self):
@@ -74,11 +116,14 @@ class HostPlanesweepPipeline:
         with ``wait=False`` it returns once the work is queued (the host buffers must stay untouched until ``finish()``)."""
         N = host_key.shape[0]
         V = len(host_sources)
+        lib = _lib.load()
+        if self.compact_mask and not (out_mask.is_contiguous() and out_mask.dtype == torch.float32 and not out_mask.is_cuda):
+            raise _lib.RmvdError("compact_mask needs a contiguous float32 host tensor for out_mask")
         slot = self._calls & 1
         self._calls += 1
         d_key, d_src = self._inputs(host_key, host_sources, slot)
         cur = torch.cuda.current_stream(self.device)
-        for s in (self.s_in, self.s_cmp, self.s_out):
+        for s in (self.s_in, self.s_cmp, self.s_out, self.s_exp):
             s.wait_stream(cur)
         if self._cmp_done[slot] is not None:              # kernels of the call before last read this set of input buffers
             self.s_in.wait_event(self._cmp_done[slot])
@@ -106,17 +151,38 @@ class HostPlanesweepPipeline:
                                              feat_sources=[f[n0:n1] for f in d_src],
                                              source_to_key_transforms=[t[n0:n1] for t in source_to_key_transforms],
                                              out=(ring[1], ring[2]), **kw)
+                if self.compact_mask:
+                    _lib.check(lib.rmvd_mask_pack_u8(_lib.ptr(ring[2]), _lib.ptr(ring[4]), ring[2].numel(), _lib.stream_ptr()),
+                               "rmvd_mask_pack_u8")
                 ev_cmp.record(self.s_cmp)
             with torch.cuda.stream(self.s_out):
                 self.s_out.wait_event(ev_cmp)
+                stage = self._staging(ring[4].shape) if self.compact_mask else None
                 for v in range(V):                        # one contiguous block per view
                     out_corr[v, n0:n1].copy_(ring[1][v], non_blocking=True)
-                    out_mask[v, n0:n1].copy_(ring[2][v], non_blocking=True)
+                    if not self.compact_mask:
+                        out_mask[v, n0:n1].copy_(ring[2][v], non_blocking=True)
+                if self.compact_mask:
+                    stage[0].copy_(ring[4], non_blocking=True)
                 ring[3] = torch.cuda.Event()
                 ring[3].record(self.s_out)
+            if self.compact_mask:
+                with torch.cuda.stream(self.s_exp):
+                    self.s_exp.wait_event(ring[3])
+                    for v in range(V):
+                        dst = out_mask[v, n0:n1]
+                        _lib.check(lib.rmvd_host_expand_mask_async(ctypes.c_void_p(stage[0][v].data_ptr()), ctypes.c_void_p(dst.data_ptr()),
+                                                                   dst.numel(), self.mask_threads, _lib.stream_ptr()),
+                                   "rmvd_host_expand_mask_async")
+                    stage[1] = torch.cuda.Event()
+                    stage[1].record(self.s_exp)
             self._cmp_done[slot] = ev_cmp
         self._done = torch.cuda.Event()
-        self._done.record(self.s_out)
+        if self.compact_mask:
+            self.s_exp.wait_stream(self.s_out)            # (already implied by the last chunk's event; keeps the intent explicit)
+            self._done.record(self.s_exp)
+        else:
+            self._done.record(self.s_out)
         if wait:
             self.finish()
         return out_corr, out_mask

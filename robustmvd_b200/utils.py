@@ -77,7 +77,7 @@ def numpy_collate(batch):
     if isinstance(elem, torch.Tensor):
         return numpy_collate([b.detach().cpu().numpy() for b in batch])
     if isinstance(elem, np.ndarray):
-        return np.stack(batch, 0)
+        return elem[None] if len(batch) == 1 else np.stack(batch, 0)   # one sample: a view, not a copy
     if isinstance(elem, np.generic) or isinstance(elem, (float, int)):
         return np.array(batch)
     if isinstance(elem, (str, bytes)):

@@ -79,6 +79,22 @@ def test_argument_validation_needs_no_device(lib):
     assert push(1 << 20, null, one, 0) == -5             # RMVD_E_RANGE: no pusher CTAs
 
 
+def test_host_mask_expansion(lib):
+    """rmvd_host_expand_mask is host code (the worker pool of the compact mask transport): bytes -> float32, any alignment, any
+    thread count, nothing written outside [0, n)."""
+    import numpy as np
+    rng = np.random.default_rng(3)
+    assert lib.rmvd_host_expand_mask(None, None, 4, 2) == -1
+    for n in (0, 1, 15, 16, 17, 3 * 65536 + 5, 1 << 21):
+        src = (rng.random(n + 3) < 0.5).astype(np.uint8)
+        for off in (0, 1, 3):
+            for threads in (1, 3, 8):
+                dst = np.full(n + 8, 7.0, np.float32)
+                s, d = src[off:off + n], dst[off:off + n]
+                assert lib.rmvd_host_expand_mask(ctypes.c_void_p(s.ctypes.data), ctypes.c_void_p(d.ctypes.data), n, threads) == 0
+                assert np.array_equal(d, s.astype(np.float32)) and np.all(dst[:off] == 7) and np.all(dst[off + n:] == 7)
+
+
 def test_missing_library_fails_loudly(monkeypatch, tmp_path):
     monkeypatch.setattr(_lib, "_lib", None)
     monkeypatch.setattr(_build, "LIB", str(tmp_path / "nope.so"))

@@ -74,6 +74,23 @@ def test_model_uses_the_cuda_library(cuda_lib):
     assert set(torch.unique(m).tolist()) <= {0.0, 1.0} and 0.05 < float(m.mean()) < 1.0
 
 
+def test_input_adapter_device_normalisation_is_bit_identical(cuda_lib, monkeypatch):
+    """robust_mvd's input_adapter normalises the images on the device (one pinned upload, true division by a device scalar):
+    the tensors equal the reference's numpy expression ``image / 255.0 - 0.4`` (robust_mvd.py:118) bit for bit, on a second
+    call through the reused staging buffer as well."""
+    torch.manual_seed(cases.MODEL_SEED)
+    model = rb.create_model("robust_mvd", pretrained=False, num_gpus=1)
+    for seed in (3, 4):
+        raw = syn.model_sample(64, 128, 2, seed=seed, batch=1)
+        got = model.input_adapter(**raw)
+        for im, t in zip(raw["images"], got["images"]):
+            assert t.is_cuda and np.array_equal((im / 255.0 - 0.4).view(np.int32), t.cpu().numpy().view(np.int32))
+    monkeypatch.setenv("RMVD_DEVICE_NORMALIZE", "0")
+    host = model.input_adapter(**raw)
+    for a, b in zip(host["images"], got["images"]):
+        assert torch.equal(a, b)
+
+
 def _model_grads(case_name):
     case = cases.MODEL_CASES[case_name]
     torch.manual_seed(cases.MODEL_SEED)

@@ -207,8 +207,10 @@ def test_shared_reciprocal_division_is_exact(cuda_lib):
     assert float((q1 - q2).abs().max()) == 0.0
 
 
-def test_host_pipeline_equals_direct_call(cuda_lib):
-    """HostPlanesweepPipeline (chunked H2D / kernels / D2H on three streams) returns the block's outputs bit for bit."""
+@pytest.mark.parametrize("compact", [True, False])
+def test_host_pipeline_equals_direct_call(cuda_lib, compact):
+    """HostPlanesweepPipeline (chunked H2D / kernels / D2H on three streams) returns the block's outputs bit for bit, with the
+    mask sent as bytes and expanded on the host (compact_mask=True) or as float32."""
     from robustmvd_b200 import synthetic as syn
     from robustmvd_b200.blocks.planesweep_corr import PlanesweepCorrelation
     from robustmvd_b200.pipeline import HostPlanesweepPipeline
@@ -221,8 +223,9 @@ def test_host_pipeline_equals_direct_call(cuda_lib):
     hk = torch.from_numpy(inp["feat_key"]).pin_memory()
     hs = [torch.from_numpy(f).pin_memory() for f in inp["feat_sources"]]
     out = torch.zeros((2, V, N, S, 24, 40), dtype=torch.float32).pin_memory()
-    pipe = HostPlanesweepPipeline(dev, PlanesweepCorrelation(), chunk_frames=2)
+    pipe = HostPlanesweepPipeline(dev, PlanesweepCorrelation(), chunk_frames=2, compact_mask=compact, mask_threads=3)
     for _ in range(2):   # second call reuses the persistent device buffers
+        out.fill_(7.0)
         pipe.run(hk, Kk, hs, Ts, out[0], out[1], **kw)
     corrs, masks, _ = PlanesweepCorrelation()(feat_key=hk.to(dev), intrinsics_key=Kk, feat_sources=[f.to(dev) for f in hs],
                                               source_to_key_transforms=Ts, **kw)
@@ -231,7 +234,8 @@ def test_host_pipeline_equals_direct_call(cuda_lib):
 
 
 @pytest.mark.gpu
-def test_host_pipeline_stream_of_batches(cuda_lib):
+@pytest.mark.parametrize("compact", [True, False])
+def test_host_pipeline_stream_of_batches(cuda_lib, compact):
     """run(wait=False) per batch + finish(): consecutive batches overlap (double-buffered device inputs) and every batch
     still equals the direct call on its own inputs."""
     from robustmvd_b200 import synthetic as syn
@@ -240,14 +244,14 @@ def test_host_pipeline_stream_of_batches(cuda_lib):
     N, V, S, B = 3, 2, 40, 5
     kw = dict(num_sampling_points=S, min_depth=0.4, max_depth=1000.0)
     dev = torch.device("cuda:0")
-    pipe = HostPlanesweepPipeline(dev, PlanesweepCorrelation(), chunk_frames=[1, 2])
+    pipe = HostPlanesweepPipeline(dev, PlanesweepCorrelation(), chunk_frames=[1, 2], compact_mask=compact)
     batches = []
     for b in range(B):
         inp = syn.planesweep_inputs(24, 40, 64, V, n=N, seed=200 + b)
         batches.append(dict(
             Kk=torch.from_numpy(inp["intrinsics_key"]).to(dev), Ts=[torch.from_numpy(x).to(dev) for x in inp["transforms"]],
             hk=torch.from_numpy(inp["feat_key"]).pin_memory(), hs=[torch.from_numpy(f).pin_memory() for f in inp["feat_sources"]],
-            out=torch.zeros((2, V, N, S, 24, 40), dtype=torch.float32).pin_memory()))
+            out=torch.full((2, V, N, S, 24, 40), 7.0, dtype=torch.float32).pin_memory()))
     for x in batches:
         pipe.run(x["hk"], x["Kk"], x["hs"], x["Ts"], x["out"][0], x["out"][1], wait=False, **kw)
     pipe.finish()
@@ -257,6 +261,27 @@ def test_host_pipeline_stream_of_batches(cuda_lib):
                               source_to_key_transforms=x["Ts"], **kw)
         for v in range(V):
             assert torch.equal(x["out"][0, v], corrs[v].cpu()) and torch.equal(x["out"][1, v], masks[v].cpu())
+
+
+def test_mask_pack_and_host_expand(cuda_lib):
+    """rmvd_mask_pack_u8 (device) + rmvd_host_expand_mask_async (host function on the stream) reproduce a 0 / 1 float32 tensor bit for
+    bit, for sizes with a tail and for an unaligned host destination."""
+    import ctypes
+    from robustmvd_b200 import _lib
+    g = torch.Generator().manual_seed(5)
+    for n in (4, 7, 1023, 70001, 3 * 65536 + 9):
+        m = (torch.rand(n, generator=g) < 0.4).float().cuda()
+        packed = torch.full((n + 4,), 9, dtype=torch.uint8, device="cuda")
+        _lib.check(cuda_lib.rmvd_mask_pack_u8(_lib.ptr(m), _lib.ptr(packed), n, _lib.stream_ptr()), "pack")
+        stage = torch.empty(n + 4, dtype=torch.uint8).pin_memory()
+        stage.copy_(packed, non_blocking=True)
+        host = torch.full((n + 9,), 7.0).pin_memory()
+        dst = host[1:1 + n]                       # 4-byte aligned only
+        _lib.check(cuda_lib.rmvd_host_expand_mask_async(ctypes.c_void_p(stage.data_ptr()), ctypes.c_void_p(dst.data_ptr()), n, 4,
+                                                        _lib.stream_ptr()), "expand")
+        torch.cuda.synchronize()
+        assert torch.equal(dst, m.cpu()) and float(host[0]) == 7.0 and bool((host[1 + n:] == 7.0).all())
+        assert bool((packed[n:] == 9).all())
 
 
 def test_cfg4_full_size_against_reference_golden(cuda_lib):
