@@ -166,6 +166,27 @@ int rmvd_psweep_corr_fwd_static(const float* feat_key, const float* const* feat_
                                 int normalize_mode, float* corr, float* mask, int out_S, int out_s0, void* stream);
 
 /*
+ * rmvd_psweep_corr_fwd with the activation of the feature encoder's last layer fused into the emission of the kernel's operand
+ * layouts (second half).  The reference computes the features with Conv2d + LeakyReLU(0.2)
+ * (dispnet_encoder.py:23-27 through blocks/utils.py:14-28; robust_mvd.py:66-67) and hands the activated NCHW maps to the block; here
+ * the caller passes the convolution's PRE-activation outputs and the split copies (bf16 hi / lo, tile-ordered key map, grouped
+ * source maps) apply x > 0 ? x : x * act_slope as they read them: the activated float32 source maps are never materialised and
+ * the separate activation pass disappears.
+ *   pre_key, pre_src   as feat_key / feat_src of rmvd_psweep_corr_fwd, before the activation
+ *   act_slope          negative slope (0.2 for the DispNet encoder; 1.0 = identity, 0.0 = ReLU)
+ *   key_act_out        [N,C,h,w] or NULL: receives the activated key map (it has other consumers: dispnet_context_encoder.py:12,
+ *                      the decoder's skip connection); must not overlap pre_key
+ * Results are bit-identical to rmvd_psweep_corr_fwd on the activated maps.  Needs the persistent kernel's shapes (C % 32 == 0,
+ * C <= 256, per-plane hypotheses); otherwise RMVD_E_MODE and the caller activates first.  No debug outputs.
+ */
+int rmvd_psweep_corr_fwd_act(const float* pre_key, const float* const* pre_src, float act_slope, float* key_act_out,
+                             const float* intrinsics_key, const float* const* intrinsics_src, const float* const* src_to_key,
+                             const float* invdepths, const int64_t* inv_stride_host, int N, int C, int h, int w,
+                             int V, const int* hs_host, const int* ws_host, int S, int s_begin, int s_end,
+                             int normalize_mode, float* corr, float* mask, int out_S, int out_s0, void* workspace,
+                             size_t workspace_bytes, void* stream);
+
+/*
  * Compact transport of the sampling mask for callers whose outputs go back to HOST memory (pipeline.HostPlanesweepPipeline; the
  * reference keeps corr and mask on the device, robust_mvd.py:71-82, so these three have no counterpart there).  The mask of
  * PlanesweepCorrelation.forward (planesweep_corr.py:99-102, :189-191) is a float32 tensor of 0.0 / 1.0 values: half of the bytes

@@ -407,9 +407,20 @@ class PlanesweepCorrelation(nn.Module):
 
     def forward(self, feat_key, intrinsics_key, feat_sources, source_to_key_transforms, intrinsics_sources=None,
                 num_sampling_points=None, min_depth=None, max_depth=None, sampling_invdepths=None,
-                sampling_type="linear_invdepth", plane_range=None, debug=False, out=None):
+                sampling_type="linear_invdepth", plane_range=None, debug=False, out=None, fused_leaky_relu=None,
+                key_activated_out=None):
+        """The reference's signature (planesweep_corr.py:396-427) plus this library's extensions ``plane_range``, ``debug``, ``out``
+        and ``fused_leaky_relu=slope``: ``feat_key`` / ``feat_sources`` are then the PRE-activation outputs of the encoder's last
+        convolution and LeakyReLU(slope) is applied inside the kernel's operand emission (rmvd_psweep_corr_fwd_act, SURVEY 8f-2);
+        ``key_activated_out`` ([N,C,h,w], not overlapping ``feat_key``) receives the activated key map.  Forward only."""
         needs_grad = torch.is_grad_enabled() and not self.warp_only and len(feat_sources) > 0 and (
             feat_key.requires_grad or any(f.requires_grad for f in feat_sources))
+        if fused_leaky_relu is not None:
+            if needs_grad or self.warp_only or debug:
+                raise _lib.RmvdError("fused_leaky_relu: forward-only correlation path (no grad, no warp_only, no debug outputs)")
+            return self._forward_impl(feat_key, intrinsics_key, feat_sources, source_to_key_transforms,
+                                      intrinsics_sources, num_sampling_points, min_depth, max_depth, sampling_invdepths,
+                                      sampling_type, plane_range, debug, out, act=(float(fused_leaky_relu), key_activated_out))
         if not needs_grad:
             return self._forward_impl(feat_key, intrinsics_key, feat_sources, source_to_key_transforms,
                                       intrinsics_sources, num_sampling_points, min_depth, max_depth, sampling_invdepths,
@@ -468,7 +479,7 @@ class PlanesweepCorrelation(nn.Module):
     @torch.no_grad()
     def _forward_impl(self, feat_key, intrinsics_key, feat_sources, source_to_key_transforms, intrinsics_sources=None,
                       num_sampling_points=None, min_depth=None, max_depth=None, sampling_invdepths=None,
-                      sampling_type="linear_invdepth", plane_range=None, debug=False, out=None, norm_mode=None, peers=None):
+                      sampling_type="linear_invdepth", plane_range=None, debug=False, out=None, norm_mode=None, peers=None, act=None):
         self.reset()
         dev = feat_key.device
         if intrinsics_sources is None:  # :441-442
@@ -499,6 +510,8 @@ class PlanesweepCorrelation(nn.Module):
         self.coeffs = [EpipolarCoeffs(z) for z in lazy]
         self.sampling_points = [EpipolarSamplingPoints(z) for z in lazy]
         if V == 0:
+            if act is not None and act[1] is not None:
+                act[1].copy_(torch.nn.functional.leaky_relu(feat_key, act[0]))
             return self.corrs, self.masks, inv
         if peers is not None:
             # depth-slab mode (parallel.SlabGather): rows go to every rank's [V,N,S,h,w] tensors from inside the kernel
@@ -543,7 +556,25 @@ class PlanesweepCorrelation(nn.Module):
                 dbg.append(torch.empty((V, N, Sl, h, w), dtype=torch.uint8, device=dev))
             nb = lib.rmvd_psweep_workspace_bytes(N, C, h, w, V, _lib.int_array(hs), _lib.int_array(ws))
             wsp = _workspace(nb, dev)
-            st = lib.rmvd_psweep_corr_fwd(
+            if act is not None:
+                slope, key_out = act
+                if key_out is not None:
+                    assert key_out.shape == feat_key.shape and key_out.dtype == torch.float32 and key_out.is_contiguous() and \
+                        key_out.device == dev and key_out.data_ptr() != feat_key.data_ptr()
+                st = lib.rmvd_psweep_corr_fwd_act(
+                    _lib.ptr(feat_key), _lib.ptr_array(srcs), slope, _lib.ptr(key_out), _lib.ptr(Kk), _lib.ptr_array(Ks),
+                    _lib.ptr_array(Ts), _lib.ptr(inv_c), ist, N, C, h, w, V, _lib.int_array(hs), _lib.int_array(ws), S, s0, s1,
+                    _corr_norm_mode(self.normalize) if norm_mode is None else norm_mode, _lib.ptr(corr), _lib.ptr(mask), out_S, out_s0,
+                    _lib.ptr(wsp), wsp.numel(), _lib.stream_ptr())
+                if st == -3:       # RMVD_E_MODE: shapes outside the persistent kernel -> activate first, then the ordinary call
+                    feat_key = torch.nn.functional.leaky_relu(feat_key, slope)
+                    srcs = [torch.nn.functional.leaky_relu(f, slope) for f in srcs]
+                    if key_out is not None:
+                        key_out.copy_(feat_key)
+                    act = None
+                else:
+                    _lib.check(st, "rmvd_psweep_corr_fwd_act")
+            st = 0 if act is not None else lib.rmvd_psweep_corr_fwd(
                 _lib.ptr(feat_key), _lib.ptr_array(srcs), _lib.ptr(Kk), _lib.ptr_array(Ks), _lib.ptr_array(Ts),
                 _lib.ptr(inv_c), ist, N, C, h, w, V, _lib.int_array(hs), _lib.int_array(ws), S, s0, s1,
                 _corr_norm_mode(self.normalize) if norm_mode is None else norm_mode, _lib.ptr(corr), _lib.ptr(mask), out_S, out_s0,

@@ -393,7 +393,8 @@ static int psweep_corr_fwd_impl(const float* feat_key, const float* const* feat_
                                 int V, const int* hs, const int* ws, int S, int s_begin, int s_end,
                                 int normalize_mode, float* corr, float* mask, int out_S, int out_s0,
                                 int32_t* dbg_ix0, int32_t* dbg_iy0, uint8_t* dbg_geom, void* workspace,
-                                size_t workspace_bytes, void* stream, const PsweepPeers* peers) {
+                                size_t workspace_bytes, void* stream, const PsweepPeers* peers, bool act = false, float act_slope = 1.f,
+                                float* key_act_out = nullptr) {
   if (!feat_key || !feat_src || !intrinsics_key || !intrinsics_src || !src_to_key || !invdepths || !inv_stride ||
       !hs || !ws || !corr || !mask)
     return RMVD_E_NULL;
@@ -428,6 +429,7 @@ static int psweep_corr_fwd_impl(const float* feat_key, const float* const* feat_
     wsk = wsk && psweep_ws_eligible(T, 0) && (long long)N * (V < kMaxViews ? V : kMaxViews) <= 65535;
   }
   if (peers && (!wsk || V > kMaxViews)) return RMVD_E_MODE;
+  if (act && !wsk) return RMVD_E_MODE;                 // the fused activation lives in the split copies of the persistent kernel
 
   char* wsp = (char*)workspace;
   unsigned* counter = (unsigned*)(wsp + rmvd_psweep_workspace_bytes(N, C, h, w, V, hs, ws) - 256);
@@ -435,7 +437,7 @@ static int psweep_corr_fwd_impl(const float* feat_key, const float* const* feat_
   wsp += (psweep_ws_key_bytes(N, C, h, w) + 255) / 256 * 256;
   const int l2 = normalize_mode == RMVD_NORM_BEFORE;
   if (wsk) {
-    int rc = repack_key_tiles(feat_key, key_nhwc, N, C, h, w, l2, st);
+    int rc = repack_key_tiles(feat_key, key_nhwc, N, C, h, w, l2, st, act, act_slope, key_act_out);
     if (rc) return rc;
   } else if (band) {
     int rc = repack(feat_key, key_nhwc, N, C, h * w, l2, st);
@@ -468,7 +470,7 @@ static int psweep_corr_fwd_impl(const float* feat_key, const float* const* feat_
       A.ws[j] = ws[v];
     }
     if (wsk) {
-      int rc = repack_grouped_batch(rp_src, rp_dst, hs + v0, ws + v0, rp_n, N, C, l2, counter, st);
+      int rc = repack_grouped_batch(rp_src, rp_dst, hs + v0, ws + v0, rp_n, N, C, l2, counter, st, act, act_slope);
       if (rc) return rc;
     }
     A.N = N; A.C = C; A.h = h; A.w = w; A.S = S; A.s_begin = s_begin; A.s_end = s_end;
@@ -491,6 +493,18 @@ extern "C" int rmvd_psweep_corr_fwd(const float* feat_key, const float* const* f
   return psweep_corr_fwd_impl(feat_key, feat_src, intrinsics_key, intrinsics_src, src_to_key, invdepths, inv_stride, N, C, h, w, V, hs, ws,
                               S, s_begin, s_end, normalize_mode, corr, mask, out_S, out_s0, dbg_ix0, dbg_iy0, dbg_geom, workspace,
                               workspace_bytes, stream, nullptr);
+}
+
+extern "C" int rmvd_psweep_corr_fwd_act(const float* pre_key, const float* const* pre_src, float act_slope, float* key_act_out,
+                                        const float* intrinsics_key, const float* const* intrinsics_src, const float* const* src_to_key,
+                                        const float* invdepths, const int64_t* inv_stride, int N, int C, int h, int w,
+                                        int V, const int* hs, const int* ws, int S, int s_begin, int s_end,
+                                        int normalize_mode, float* corr, float* mask, int out_S, int out_s0, void* workspace,
+                                        size_t workspace_bytes, void* stream) {
+  if (!(act_slope == act_slope)) return RMVD_E_MODE;
+  return psweep_corr_fwd_impl(pre_key, pre_src, intrinsics_key, intrinsics_src, src_to_key, invdepths, inv_stride, N, C, h, w, V, hs, ws,
+                              S, s_begin, s_end, normalize_mode, corr, mask, out_S, out_s0, nullptr, nullptr, nullptr, workspace,
+                              workspace_bytes, stream, nullptr, true, act_slope, key_act_out);
 }
 
 extern "C" int rmvd_psweep_corr_fwd_peers(const float* feat_key, const float* const* feat_src, const float* intrinsics_key,

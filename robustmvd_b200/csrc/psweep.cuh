@@ -39,10 +39,11 @@ int launch_psweep_band(const PsweepArgs& A, const float* key_nhwc, int nviews, c
 bool psweep_ws_eligible(const PsweepArgs& A, int nviews);
 size_t psweep_ws_src_bytes(int N, int C, int hs, int ws);
 size_t psweep_ws_key_bytes(int N, int C, int h, int w);
-int repack_key_tiles(const float* key, void* dst, int N, int C, int h, int w, int l2norm, cudaStream_t st);
+int repack_key_tiles(const float* key, void* dst, int N, int C, int h, int w, int l2norm, cudaStream_t st, bool act = false, float slope = 1.f,
+                     float* act_out = nullptr);
 // `counter`: 4 bytes of device memory (the kernel's work-item counter), zeroed by the repack launch
 int repack_grouped_batch(const float* const* srcs, void* const* dsts, const int* hs, const int* ws, int count, int N, int C, int l2norm,
-                         unsigned* counter, cudaStream_t st);
+                         unsigned* counter, cudaStream_t st, bool act = false, float slope = 1.f);
 // Depth-slab mode: the sampling loop stores every output row into the tensors of all ranks (peer-mapped pointers, own rank
 // included) and the kernel ends with a flag handshake between the ranks.
 struct PsweepPeers {

@@ -270,8 +270,9 @@ struct GroupBatch {
   unsigned* counter;               // work-item counter of the plane-sweep launch that follows: zeroed here
 };
 
-template <bool kNorm>
-__global__ void __launch_bounds__(256) nchw_to_grouped_kernel(const GroupBatch B, int C, int N) {
+// kAct: the maps hold PRE-activation values; LeakyReLU(slope) (x > 0 ? x : x * slope, as ATen computes it) is applied as they are read
+template <bool kNorm, bool kAct>
+__global__ void __launch_bounds__(256) nchw_to_grouped_kernel(const GroupBatch B, int C, int N, float slope) {
   __shared__ float tile[kRpCh][33];
   __shared__ float s_norm[32];
   const int which = blockIdx.z / N, n = blockIdx.z - which * N;
@@ -290,7 +291,8 @@ __global__ void __launch_bounds__(256) nchw_to_grouped_kernel(const GroupBatch B
   if (kNorm) {
     float acc = 0.f;
     for (int c = ty; c < C; c += 8) {
-      const float v = in ? __ldg(src + (size_t)c * Ps + x0 + tx) : 0.f;
+      float v = in ? __ldg(src + (size_t)c * Ps + x0 + tx) : 0.f;
+      if (kAct) v = v > 0.f ? v : __fmul_rn(v, slope);
       acc = fmaf(v, v, acc);
     }
     tile[ty][tx] = acc;
@@ -310,6 +312,10 @@ __global__ void __launch_bounds__(256) nchw_to_grouped_kernel(const GroupBatch B
     float v[kRpCh / 8];
 #pragma unroll
     for (int k = 0; k < kRpCh / 8; ++k) v[k] = (ty + 8 * k < nc && in) ? __ldg(src + (size_t)(c0 + ty + 8 * k) * Ps + x0 + tx) : 0.f;
+    if (kAct) {
+#pragma unroll
+      for (int k = 0; k < kRpCh / 8; ++k) v[k] = v[k] > 0.f ? v[k] : __fmul_rn(v[k], slope);
+    }
 #pragma unroll
     for (int k = 0; k < kRpCh / 8; ++k) tile[ty + 8 * k][tx] = kNorm ? fdiv(v[k], inv_norm) : v[k];
     __syncthreads();
@@ -345,9 +351,11 @@ __global__ void __launch_bounds__(256) nchw_to_grouped_kernel(const GroupBatch B
 // NCHW fp32 key map -> tile-ordered split copy.  CTA = one tile x 64 channels (one 16 KB stage of the plane-sweep kernel);
 // kNorm: L2-normalised along C first, the CTA then walks all channel blocks itself.
 // ---------------------------------------------------------------------------------------------------------
-template <bool kNorm>
+// kAct: `key` holds PRE-activation values; LeakyReLU(slope) is applied as they are read and, if act_out is given, the activated map is
+// also written there in NCHW float32 (the key map has other consumers: context encoder, decoder skip connection).
+template <bool kNorm, bool kAct>
 __global__ void __launch_bounds__(256) nchw_to_keytiles_kernel(const float* __restrict__ key, __nv_bfloat16* __restrict__ dst, int C, int h, int w,
-                                                               int tw, int th, int tiles_x) {
+                                                               int tw, int th, int tiles_x, float slope, float* __restrict__ act_out) {
   __shared__ float tile[64][66];                    // [channel][tile slot]; pitch 66: conflict-free chunk reads below
   __shared__ float s_norm[64];
   const int tiles = gridDim.x, tl = blockIdx.x, n = blockIdx.z;
@@ -365,7 +373,8 @@ __global__ void __launch_bounds__(256) nchw_to_keytiles_kernel(const float* __re
   if (kNorm) {
     float acc = 0.f;
     for (int c = t >> 6; c < C; c += 4) {
-      const float v = in ? __ldg(src + (size_t)c * P + poff) : 0.f;
+      float v = in ? __ldg(src + (size_t)c * P + poff) : 0.f;
+      if (kAct) v = v > 0.f ? v : __fmul_rn(v, slope);
       acc = fmaf(v, v, acc);
     }
     tile[t >> 6][slot] = acc;
@@ -382,6 +391,14 @@ __global__ void __launch_bounds__(256) nchw_to_keytiles_kernel(const float* __re
     for (int k = 0; k < 16; ++k) {
       const int c = (t >> 6) + 4 * k;
       v[k] = (c < nc && in) ? __ldg(src + (size_t)(c0 + c) * P + poff) : 0.f;
+    }
+    if (kAct) {
+#pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        const int c = (t >> 6) + 4 * k;
+        v[k] = v[k] > 0.f ? v[k] : __fmul_rn(v[k], slope);
+        if (act_out && c < nc && in) act_out[(size_t)n * C * P + (size_t)(c0 + c) * P + poff] = v[k];
+      }
     }
 #pragma unroll
     for (int k = 0; k < 16; ++k) tile[(t >> 6) + 4 * k][slot] = kNorm ? fdiv(v[k], nrm) : v[k];
@@ -1471,18 +1488,18 @@ size_t psweep_ws_key_bytes(int N, int C, int h, int w) {
   return (size_t)N * tiles * C * 256;
 }
 
-int repack_key_tiles(const float* key, void* dst, int N, int C, int h, int w, int l2norm, cudaStream_t st) {
+int repack_key_tiles(const float* key, void* dst, int N, int C, int h, int w, int l2norm, cudaStream_t st, bool act, float slope,
+                     float* act_out) {
   int tw, th;
   psweep_ws_tile_shape(h, w, &tw, &th);
   const int tiles_x = (w + tw - 1) / tw, tiles = tiles_x * ((h + th - 1) / th);
   if (N > 65535) return (int)cudaErrorInvalidValue;
-  if (l2norm) {
-    dim3 grid(tiles, 1, N);
-    ws::nchw_to_keytiles_kernel<true><<<grid, 256, 0, st>>>(key, reinterpret_cast<__nv_bfloat16*>(dst), C, h, w, tw, th, tiles_x);
-  } else {
-    dim3 grid(tiles, (C + 63) / 64, N);
-    ws::nchw_to_keytiles_kernel<false><<<grid, 256, 0, st>>>(key, reinterpret_cast<__nv_bfloat16*>(dst), C, h, w, tw, th, tiles_x);
-  }
+  __nv_bfloat16* d = reinterpret_cast<__nv_bfloat16*>(dst);
+  const dim3 grid(tiles, l2norm ? 1 : (C + 63) / 64, N);
+  if (l2norm && act) ws::nchw_to_keytiles_kernel<true, true><<<grid, 256, 0, st>>>(key, d, C, h, w, tw, th, tiles_x, slope, act_out);
+  else if (l2norm) ws::nchw_to_keytiles_kernel<true, false><<<grid, 256, 0, st>>>(key, d, C, h, w, tw, th, tiles_x, 1.f, nullptr);
+  else if (act) ws::nchw_to_keytiles_kernel<false, true><<<grid, 256, 0, st>>>(key, d, C, h, w, tw, th, tiles_x, slope, act_out);
+  else ws::nchw_to_keytiles_kernel<false, false><<<grid, 256, 0, st>>>(key, d, C, h, w, tw, th, tiles_x, 1.f, nullptr);
   return (int)cudaGetLastError();
 }
 
@@ -1495,7 +1512,7 @@ bool psweep_ws_eligible(const PsweepArgs& A, int nviews) {
 }
 
 int repack_grouped_batch(const float* const* srcs, void* const* dsts, const int* hs, const int* wss, int count, int N, int C, int l2norm,
-                         unsigned* counter, cudaStream_t st) {
+                         unsigned* counter, cudaStream_t st, bool act, float slope) {
   if (count < 1 || count > kMaxViews || (long long)N * count > 65535) return (int)cudaErrorInvalidValue;
   ws::GroupBatch B;
   B.counter = counter;
@@ -1508,13 +1525,11 @@ int repack_grouped_batch(const float* const* srcs, void* const* dsts, const int*
       if (tiles > gmax) gmax = tiles;
     }
   }
-  if (l2norm) {
-    dim3 grid(gmax, 1, N * count);
-    ws::nchw_to_grouped_kernel<true><<<grid, 256, 0, st>>>(B, C, N);
-  } else {
-    dim3 grid(gmax, (C + ws::kRpCh - 1) / ws::kRpCh, N * count);
-    ws::nchw_to_grouped_kernel<false><<<grid, 256, 0, st>>>(B, C, N);
-  }
+  const dim3 grid(gmax, l2norm ? 1 : (C + ws::kRpCh - 1) / ws::kRpCh, N * count);
+  if (l2norm && act) ws::nchw_to_grouped_kernel<true, true><<<grid, 256, 0, st>>>(B, C, N, slope);
+  else if (l2norm) ws::nchw_to_grouped_kernel<true, false><<<grid, 256, 0, st>>>(B, C, N, 1.f);
+  else if (act) ws::nchw_to_grouped_kernel<false, true><<<grid, 256, 0, st>>>(B, C, N, slope);
+  else ws::nchw_to_grouped_kernel<false, false><<<grid, 256, 0, st>>>(B, C, N, 1.f);
   return (int)cudaGetLastError();
 }
 

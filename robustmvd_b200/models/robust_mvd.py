@@ -54,25 +54,46 @@ class RobustMVD(nn.Module):
         intrinsics_key = select_by_index(intrinsics, keyview_idx)
         intrinsics_source = exclude_index(intrinsics, keyview_idx)
         source_to_key_transforms = exclude_index(poses, keyview_idx)
+        fused_slope = None
 
         if image_key.is_cuda and len(images_source) > 0 and os.environ.get("RMVD_BATCH_ENCODER", "1") != "0":
             # key and source views through the encoder as ONE (1 + V) * N batch (robust_mvd.py:66-67 runs
             # it once per view): the same convolutions with 1 / (1 + V) of the launches; the per-view features are
             # contiguous slices of one tensor, which is also what the correlation call's single repack launch reads
             nb = image_key.shape[0]
-            all_enc, enc = self.encoder(torch.cat([image_key] + list(images_source), 0))
-            all_enc_key = {k: v[:nb] for k, v in all_enc.items()}
-            enc_key = enc[:nb]
-            enc_sources = list(enc[nb:].split(nb, 0))
+            stack = torch.cat([image_key] + list(images_source), 0)
+            if not torch.is_grad_enabled() and os.environ.get("RMVD_FUSED_ACT", "1") != "0":
+                # second half of row f-2: the last encoder layer's LeakyReLU (dispnet_encoder.py:23-27) is applied by the
+                # correlation call as it emits its bf16 operand layouts: the activated source maps are never written, the key
+                # map's activated copy (context encoder, decoder skip connection) is written by the same kernel
+                c1 = self.encoder.conv1(stack)
+                c2 = self.encoder.conv2(c1)
+                pre = self.encoder.conv3[0](c2)
+                fused_slope = self.encoder.conv3[1].negative_slope
+                enc_key = torch.empty_like(pre[:nb])
+                all_enc_key = {"conv1": c1[:nb], "conv2": c2[:nb], "conv3a": enc_key}
+                enc_pre_key, enc_sources = pre[:nb], list(pre[nb:].split(nb, 0))
+            else:
+                all_enc, enc = self.encoder(stack)
+                all_enc_key = {k: v[:nb] for k, v in all_enc.items()}
+                enc_key = enc[:nb]
+                enc_sources = list(enc[nb:].split(nb, 0))
         else:
             all_enc_key, enc_key = self.encoder(image_key)
             enc_sources = [self.encoder(image_source)[1] for image_source in images_source]
-        ctx = self.context_encoder(enc_key)
 
-        corrs, masks, _ = self.corr_block(
-            feat_key=enc_key, intrinsics_key=intrinsics_key, feat_sources=enc_sources,
-            source_to_key_transforms=source_to_key_transforms, intrinsics_sources=intrinsics_source,
-            num_sampling_points=NUM_PLANES, min_depth=MIN_DEPTH, max_depth=MAX_DEPTH)
+        if fused_slope is not None:
+            corrs, masks, _ = self.corr_block(
+                feat_key=enc_pre_key, intrinsics_key=intrinsics_key, feat_sources=enc_sources,
+                source_to_key_transforms=source_to_key_transforms, intrinsics_sources=intrinsics_source,
+                num_sampling_points=NUM_PLANES, min_depth=MIN_DEPTH, max_depth=MAX_DEPTH,
+                fused_leaky_relu=fused_slope, key_activated_out=enc_key)
+        else:
+            corrs, masks, _ = self.corr_block(
+                feat_key=enc_key, intrinsics_key=intrinsics_key, feat_sources=enc_sources,
+                source_to_key_transforms=source_to_key_transforms, intrinsics_sources=intrinsics_source,
+                num_sampling_points=NUM_PLANES, min_depth=MIN_DEPTH, max_depth=MAX_DEPTH)
+        ctx = self.context_encoder(enc_key)
 
         fused_corr, _ = self.fusion_block(corrs=corrs, masks=masks)
         all_enc_fused, enc_fused = self.fusion_enc_block(corr=fused_corr, ctx=ctx)

@@ -91,6 +91,22 @@ def test_input_adapter_device_normalisation_is_bit_identical(cuda_lib, monkeypat
         assert torch.equal(a, b)
 
 
+def test_fused_encoder_activation_leaves_the_model_output_unchanged(cuda_lib, monkeypatch):
+    """SURVEY 8f-2, second half: with the encoder's last LeakyReLU applied inside the correlation call (default) the correlation
+    volume is bit-identical to the one behind the stock Conv2d + LeakyReLU encoder (RMVD_FUSED_ACT=0); the model outputs agree to
+    float32 rounding of the cuDNN layers after it (their inputs live at other addresses, cuDNN may pick other kernels)."""
+    torch.manual_seed(cases.MODEL_SEED)
+    model = rb.create_model("robust_mvd", pretrained=False, num_gpus=1)
+    sample = syn.model_sample(128, 192, 3, seed=11)
+    pred_fused, aux_fused = model.run(**sample)
+    corr_fused = model.corr_block.corrs[1].clone()
+    monkeypatch.setenv("RMVD_FUSED_ACT", "0")
+    pred, aux = model.run(**sample)
+    assert torch.equal(corr_fused, model.corr_block.corrs[1])
+    inv, inv_fused = 1.0 / pred["depth"], 1.0 / pred_fused["depth"]
+    assert float(np.abs(inv - inv_fused).max()) <= 1e-4 * float(np.abs(inv).max())
+
+
 def _model_grads(case_name):
     case = cases.MODEL_CASES[case_name]
     torch.manual_seed(cases.MODEL_SEED)

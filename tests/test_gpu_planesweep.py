@@ -263,6 +263,37 @@ def test_host_pipeline_stream_of_batches(cuda_lib, compact):
             assert torch.equal(x["out"][0, v], corrs[v].cpu()) and torch.equal(x["out"][1, v], masks[v].cpu())
 
 
+@pytest.mark.parametrize("C,normalize,h,w", [(64, "dim", 24, 40), (256, "dim", 13, 37), (96, True, 10, 70), (48, "dim", 8, 16)])
+def test_fused_leaky_relu_equals_activation_then_call(cuda_lib, C, normalize, h, w):
+    """rmvd_psweep_corr_fwd_act (the encoder's last LeakyReLU fused into the operand emission) on pre-activation maps
+    equals torch's leaky_relu followed by the ordinary call, bit for bit, and hands back the activated key map; C = 48 takes the
+    documented fallback (shape outside the persistent kernel)."""
+    from robustmvd_b200.blocks.planesweep_corr import PlanesweepCorrelation
+    N, V, S = 2, 2, 40
+    inp = syn.planesweep_inputs(h, w, C, V, n=N, seed=300 + C)
+    dev = torch.device("cuda:0")
+    g = torch.Generator(device="cpu").manual_seed(C)
+    pre_key = (torch.from_numpy(inp["feat_key"]) * torch.where(torch.rand(N, C, h, w, generator=g) < 0.5, -3.0, 1.0)).to(dev)
+    pre_src = [(torch.from_numpy(f) * torch.where(torch.rand(f.shape, generator=g) < 0.5, -3.0, 1.0)).to(dev) for f in inp["feat_sources"]]
+    pre_key[0, 0, 0, :4] = torch.tensor([0.0, -0.0, float("nan"), -1e-40])
+    Kk = torch.from_numpy(inp["intrinsics_key"]).to(dev)
+    Ts = [torch.from_numpy(x).to(dev) for x in inp["transforms"]]
+    kw = dict(intrinsics_key=Kk, source_to_key_transforms=Ts, num_sampling_points=S, min_depth=0.4, max_depth=1000.0)
+    blk = PlanesweepCorrelation(normalize=normalize)
+    key_out = torch.full_like(pre_key, 7.0)
+    c1, m1, _ = blk(feat_key=pre_key, feat_sources=pre_src, fused_leaky_relu=0.2, key_activated_out=key_out, **kw)
+    c1, m1 = [c.clone() for c in c1], [m.clone() for m in m1]
+    lr = torch.nn.functional.leaky_relu
+    c2, m2, _ = blk(feat_key=lr(pre_key, 0.2), feat_sources=[lr(f, 0.2) for f in pre_src], **kw)
+    assert torch.equal(key_out.view(torch.int32), lr(pre_key, 0.2).view(torch.int32))
+    for v in range(V):
+        assert torch.equal(m1[v], m2[v])
+        assert torch.equal(c1[v].view(torch.int32), c2[v].view(torch.int32))
+    with pytest.raises(Exception):
+        with torch.enable_grad():
+            blk(feat_key=pre_key.clone().requires_grad_(True), feat_sources=pre_src, fused_leaky_relu=0.2, **kw)
+
+
 def test_mask_pack_and_host_expand(cuda_lib):
     """rmvd_mask_pack_u8 (device) + rmvd_host_expand_mask_async (host function on the stream) reproduce a 0 / 1 float32 tensor bit for
     bit, for sizes with a tail and for an unaligned host destination."""
