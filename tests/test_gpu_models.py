@@ -44,7 +44,10 @@ def test_robust_mvd_run_matches_reference(cuda_lib, case_name):
     assert np.abs(inv - ginv).max() <= 1e-3 * np.abs(ginv).max()
     live = ginv > 1e-2 * ginv.max()                     # depth = 1/(invdepth + 1e-9): compare where it is well conditioned
     rel = np.abs(pred["depth"] - g["pred_depth"])[live] / g["pred_depth"][live]
-    assert np.mean(rel <= 1e-3) >= 0.995 and np.median(rel) < 1e-4, (np.mean(rel <= 1e-3), np.median(rel))
+    n_out = int(np.sum(rel > 1e-3))
+    print(f"MODEL_PARITY {case_name}: {n_out} of {rel.size} well-conditioned pixels beyond 1e-3 (max {rel.max():.3g}, median {np.median(rel):.3g})")
+    assert np.mean(rel <= 1e-3) >= 0.995 and np.median(rel) < 1e-4, \
+        f"{n_out} of {rel.size} well-conditioned pixels beyond 1e-3 relative depth error (max {rel.max():.3g}, median {np.median(rel):.3g})"
     assert np.abs(aux["invdepth_log_b"] - g["aux_invdepth_log_b"]).max() < 1e-2
     assert set(pred) == {"depth", "depth_uncertainty"} and "invdepths_all" in aux and len(aux["invdepths_all"]) == 6
 
@@ -54,7 +57,10 @@ def test_mvsnet_run_matches_reference(cuda_lib, case_name):
     pred, aux, g = _run(case_name)
     assert pred["depth"].shape == g["pred_depth"].shape and aux == {}
     rel = np.abs(pred["depth"] - g["pred_depth"]) / g["pred_depth"]
-    assert np.mean(rel <= 1e-3) >= 0.995 and np.median(rel) < 1e-4, (np.mean(rel <= 1e-3), np.median(rel))
+    n_out = int(np.sum(rel > 1e-3))
+    print(f"MODEL_PARITY {case_name}: {n_out} of {rel.size} pixels beyond 1e-3 (max {rel.max():.3g}, median {np.median(rel):.3g})")
+    assert np.mean(rel <= 1e-3) >= 0.995 and np.median(rel) < 1e-4, \
+        f"{n_out} of {rel.size} pixels beyond 1e-3 relative depth error (max {rel.max():.3g}, median {np.median(rel):.3g})"
     du = np.abs(pred["depth_uncertainty"] - g["pred_depth_uncertainty"])
     assert np.mean(du <= 1e-3) >= 0.98, np.mean(du <= 1e-3)   # the 4-bin window moves when trunc(E[index]) flips
 

@@ -8,6 +8,8 @@ python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke.log 2>&1
 python bench.py --impl reference --steps 3 --warmup 1 > $O/bench_ref.json 2> $O/bench_ref.err
 python bench.py > $O/bench.json 2> $O/bench.err
 python tools/bench_kernels.py > $O/kernels.jsonl 2> $O/kernels.err
+python tools/profile_model_run.py > $O/model_run.json 2> $O/model_run.err
+python tools/pcie_probe.py > $O/pcie.json 2> $O/pcie.err
 python bench.py --steps 2 --warmup 1 --no-secondary --no-cpu-baseline > $O/b_small.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches.csv python bench.py --steps 2 --warmup 1 --no-secondary --no-cpu-baseline > $O/ncu_list.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:psweep_ws_kernel -s 2 -c 1 -o $O/ws_full python bench.py --steps 2 --warmup 1 --no-secondary --no-cpu-baseline > $O/ncu_full.log 2>&1
