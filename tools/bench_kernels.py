@@ -4,7 +4,7 @@
 
 Each kernel is timed with CUDA events on the launching stream, one event pair per repetition, with a 256 MB scratch
 write between repetitions so that nothing is served from the 126 MB L2 (cold = `ms_cold`; `ms_warm` = back-to-back
-without the flush).  `frac` = algorithmic bytes / ms_cold / MEASURED_PEAKS.json hbm_gbs.  One JSON line per kernel.
+without the flush; `ms_warm_graph` = the same loop replayed from a CUDA graph, i.e. without host time between launches).  `frac` = algorithmic bytes / ms_cold / MEASURED_PEAKS.json hbm_gbs.  One JSON line per kernel.
 """
 import argparse
 import json
@@ -42,7 +42,31 @@ def time_fn(fn, reps, flush):
         fn()
     b.record()
     torch.cuda.synchronize()
-    return float(np.mean(cold)), float(np.min(cold)), a.elapsed_time(b) / reps
+    warm = a.elapsed_time(b) / reps
+    # the same back-to-back loop replayed from a CUDA graph: no Python, ctypes or allocator time between the launches (for kernels of
+    # a few tens of microseconds `ms_warm` is the host's call rate, not the kernel)
+    graph_ms = None
+    try:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            fn()
+        torch.cuda.current_stream().wait_stream(side)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for _ in range(reps):
+                fn()
+        g.replay()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        g.replay()
+        b.record()
+        torch.cuda.synchronize()
+        graph_ms = a.elapsed_time(b) / reps
+    except Exception:  # noqa: BLE001  (a wrapper that synchronises cannot be captured: the number is simply left out)
+        torch.cuda.synchronize()
+    return float(np.mean(cold)), float(np.min(cold)), warm, graph_ms
 
 
 def psweep_case(cfg, V, frames, S=None):
@@ -152,8 +176,8 @@ def main():
     add("cvp_proj_cost_128x160_c16_d8", lambda: cvpc.proj_cost(cset, cref, csrc, 0, cK, cK[:, None].repeat(1, cV, 1, 1), cE, cEs, chyp),
         4 * cC * cH * cW * (1 + cV) + 4 * cD * cH * cW + 4 * cC * cD * cH * cW, cD * cH * cW, "voxels")
     for name, fn, nbytes, units, unit_name in jobs:
-        cold, best, warm = time_fn(fn, args.reps, flush)
-        print(json.dumps({"kernel": name, "ms_cold": cold, "ms_cold_min": best, "ms_warm": warm, "algorithmic_bytes": nbytes,
+        cold, best, warm, graph_ms = time_fn(fn, args.reps, flush)
+        print(json.dumps({"kernel": name, "ms_cold": cold, "ms_cold_min": best, "ms_warm": warm, "ms_warm_graph": graph_ms, "algorithmic_bytes": nbytes,
                           "achieved_gbs": nbytes / cold / 1e6, "frac_of_measured_hbm": nbytes / cold / 1e6 / peaks["hbm_gbs"],
                           f"{unit_name}_per_s": units / (cold * 1e-3)}), flush=True)
 
