@@ -2,8 +2,8 @@
 convolutions in cuDNN) against golden predictions of the UNMODIFIED reference models run on CPU in the build container
 (tools/make_model_golden.py) with identical seeded weights.  Bar (north_star): regressed depth within 1e-3 relative.
 
-cuDNN and CPU convolutions round differently, so a handful of pixels whose prediction sits on a ReLU / floor boundary
-may differ: the bar must hold on >= 99.5 % of the pixels and the median error must be far below it."""
+cuDNN and CPU convolutions round differently; measured on the B200: 0 pixels beyond the bar (max 2.4e-4, median 2e-6 for
+robust_mvd; max 2.2e-5 for MVSNet), so the bar must hold on EVERY pixel where the inverse depth is well conditioned."""
 import os
 
 import numpy as np
@@ -46,7 +46,7 @@ def test_robust_mvd_run_matches_reference(cuda_lib, case_name):
     rel = np.abs(pred["depth"] - g["pred_depth"])[live] / g["pred_depth"][live]
     n_out = int(np.sum(rel > 1e-3))
     print(f"MODEL_PARITY {case_name}: {n_out} of {rel.size} well-conditioned pixels beyond 1e-3 (max {rel.max():.3g}, median {np.median(rel):.3g})")
-    assert np.mean(rel <= 1e-3) >= 0.995 and np.median(rel) < 1e-4, \
+    assert n_out == 0 and np.median(rel) < 1e-4, \
         f"{n_out} of {rel.size} well-conditioned pixels beyond 1e-3 relative depth error (max {rel.max():.3g}, median {np.median(rel):.3g})"
     assert np.abs(aux["invdepth_log_b"] - g["aux_invdepth_log_b"]).max() < 1e-2
     assert set(pred) == {"depth", "depth_uncertainty"} and "invdepths_all" in aux and len(aux["invdepths_all"]) == 6
@@ -59,7 +59,7 @@ def test_mvsnet_run_matches_reference(cuda_lib, case_name):
     rel = np.abs(pred["depth"] - g["pred_depth"]) / g["pred_depth"]
     n_out = int(np.sum(rel > 1e-3))
     print(f"MODEL_PARITY {case_name}: {n_out} of {rel.size} pixels beyond 1e-3 (max {rel.max():.3g}, median {np.median(rel):.3g})")
-    assert np.mean(rel <= 1e-3) >= 0.995 and np.median(rel) < 1e-4, \
+    assert n_out == 0 and np.median(rel) < 1e-4, \
         f"{n_out} of {rel.size} pixels beyond 1e-3 relative depth error (max {rel.max():.3g}, median {np.median(rel):.3g})"
     du = np.abs(pred["depth_uncertainty"] - g["pred_depth_uncertainty"])
     assert np.mean(du <= 1e-3) >= 0.98, np.mean(du <= 1e-3)   # the 4-bin window moves when trunc(E[index]) flips
