@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define RMVD_ABI_VERSION 5
+#define RMVD_ABI_VERSION 6
 #define RMVD_MAX_PEERS 8      /* ranks of one depth-slab communicator (GPUs of one NVSwitch box) */
 
 #define RMVD_OK 0
@@ -307,6 +307,21 @@ int rmvd_homo_warp_fwd(const float* src_feat, const float* src_proj, const float
 int rmvd_mvs_regress_fwd(const float* cost, const float* depths, int B, int D, int h, int w, float* depth,
                          float* confidence, int64_t* depth_index, float* expected_index, float* prob,
                          void* stream);
+
+/*
+ * Backward of the MVSNet cost-volume path (training direction; extends SURVEY.md row 8f-4 to the MVSNet family).  The reference
+ * obtains both from autograd: through homo_warp's grid_sample (blocks/utils.py:262) and the variance expression
+ * (mvsnet.py:123-136), and through F.softmax + depth_regression (mvsnet.py:140-141, blocks/utils.py:271-274).  Sampling positions
+ * carry no gradient (depth hypotheses and projections are data); the confidence is computed under no_grad (mvsnet.py:143-158).
+ *   rmvd_mvs_variance_bwd  grad_variance [B,C,D,h,w] -> grad_feats [B,Vt,C,h,w] (zeroed by the call; view 0 = key view).
+ *                          d var / d x_v = (2 / Vt) (x_v - mean) with x_0 = ref, x_v = warp_v(src_v): the warps are recomputed,
+ *                          source views receive the transpose of their bilinear gather (float atomics: sums in any order)
+ *   rmvd_mvs_regress_bwd   grad_depth [B,h,w] -> grad_cost [B,D,h,w]: g * softmax(cost)_d * (depth_d - depth)
+ */
+int rmvd_mvs_variance_bwd(const float* feats, const float* proj_mats, const float* depth_values, const float* grad_variance,
+                          int B, int Vt, int C, int h, int w, int D, float* grad_feats, void* stream);
+int rmvd_mvs_regress_bwd(const float* cost, const float* depth_values, const float* grad_depth, int B, int D, int h, int w,
+                         float* grad_cost, void* stream);
 
 /*
  * Depth-slab softargmax.  Step 1 on each rank: partials over planes [d_begin,d_end) of a

@@ -9,7 +9,8 @@ reference ``file:line`` it follows.
 Added for the "next" rows of SURVEY.md 8(f): ``planesweep_correlation_backward`` (what autograd returns through
 ``TorchCorr.forward``, pinned by ``tools/make_bwd_golden.py``), ``vismvsnet`` (``blocks/utils.py:71-189``, pinned by
 ``tools/make_vis_golden.py``) and ``cvpmvsnet`` (``blocks/cvp_mvsnet_components.py:192-245, :375-457``, pinned by
-``tools/make_cvp_golden.py``).
+``tools/make_cvp_golden.py``), and ``mvs_variance_backward`` / ``mvs_regress_backward`` (autograd through ``mvsnet.py:123-141``,
+pinned by ``tools/make_mvs_bwd_golden.py``).
 
 Who may import it: ``tests/``, ``__graft_entry__.smoke()`` and the
 ``cpu_baseline`` / ``--impl reference`` legs of ``bench.py`` -- there only as the
@@ -44,6 +45,8 @@ from .mvsnet import (  # noqa: F401
     homo_warp,
     mvs_variance,
     mvs_regress,
+    mvs_variance_backward,
+    mvs_regress_backward,
     softargmax_partials,
     softargmax_combine,
     softargmax_confidence_part,

@@ -141,6 +141,49 @@ def mvs_variance(feats, proj_mats, depth_values):
     return (vsq / Vf - mean * mean).astype(np.float32)  # :135
 
 
+def mvs_variance_backward(feats, proj_mats, depth_values, grad_variance):
+    """Gradient of ``sum <grad_variance, mvs_variance(feats, ...)>`` with respect to ``feats`` -- what autograd returns in the
+    reference through homo_warp's grid_sample (utils.py:262) and mvsnet.py:123-136: ``d var / d x_v = (2 / V) (x_v - mean)``;
+    a source view receives it through the transpose of its bilinear gather (zeros padding: no gradient from corners outside)."""
+    feats = _f32(feats)
+    proj_mats = _f32(proj_mats)
+    g = _f32(grad_variance)
+    B, V, C, h, w = feats.shape
+    D = depth_values.shape[1]
+    warped = [None] + [homo_warp(feats[:, v], proj_mats[:, v], proj_mats[:, 0], depth_values) for v in range(1, V)]
+    ref = np.broadcast_to(feats[:, 0][:, :, None], (B, C, D, h, w))
+    mean = (ref + sum(warped[1:])) / F32(V)
+    out = np.zeros_like(feats, dtype=np.float64)
+    out[:, 0] = (2.0 / V * g * (ref - mean)).sum(axis=2)
+    for v in range(1, V):
+        gx = (2.0 / V) * g.astype(np.float64) * (warped[v] - mean)      # [B,C,D,h,w]
+        ix, iy = homo_warp_coords(proj_mats[:, v], proj_mats[:, 0], depth_values, h, w)
+        for bi in range(B):
+            b = _bilinear_from_unnormalized(ix[bi], iy[bi], h, w)
+            x0 = np.clip(b["ix0"], 0, w - 1).astype(np.int64)
+            x1 = np.clip(b["ix0"] + 1, 0, w - 1).astype(np.int64)
+            y0 = np.clip(b["iy0"], 0, h - 1).astype(np.int64)
+            y1 = np.clip(b["iy0"] + 1, 0, h - 1).astype(np.int64)
+            flat = out[bi, v].reshape(C, h * w)
+            for key, yy, xx in (("nw", y0, x0), ("ne", y0, x1), ("sw", y1, x0), ("se", y1, x1)):
+                wgt = np.where(b["in_" + key], np.nan_to_num(b[key], nan=0.0, posinf=0.0, neginf=0.0), 0.0).astype(np.float64)
+                idx = (yy * w + xx).reshape(-1)
+                contrib = (gx[bi] * wgt[None]).reshape(C, -1)
+                for c in range(C):
+                    np.add.at(flat[c], idx, contrib[c])
+    return out.astype(np.float32)
+
+
+def mvs_regress_backward(cost_reg, depth_values, grad_depth):
+    """Gradient of ``sum <grad_depth, depth>`` with respect to ``cost_reg`` for ``depth = sum_d softmax(cost)_d * depth_d``
+    (mvsnet.py:140-141): ``g * p_d * (depth_d - depth)``."""
+    p = _softmax(cost_reg, 1).astype(np.float64)
+    B, D, h, w = p.shape
+    dv = _f32(depth_values).reshape(B, D, 1, 1).astype(np.float64)
+    depth = np.sum(p * dv, axis=1, keepdims=True)
+    return (_f32(grad_depth)[:, None].astype(np.float64) * p * (dv - depth)).astype(np.float32)
+
+
 def _softmax(x, axis):
     x = _f32(x)
     m = x.max(axis=axis, keepdims=True)

@@ -83,9 +83,8 @@ def planesweep_correlation(feat_key, intrinsics_key, feat_sources, source_to_key
 def mvs_variance(feats, proj_mats, depth_values, device=None, return_torch=False):
     """mvsnet.py:123-136 + homo_warp (utils.py:222-268) on stock torch ops (CPU by default, see planesweep_correlation)."""
     dev = torch.device("cpu" if device is None else device)
-    feats = torch.from_numpy(np.ascontiguousarray(feats)).to(dev)
-    proj = torch.from_numpy(np.ascontiguousarray(proj_mats)).to(dev)
-    depth = torch.from_numpy(np.ascontiguousarray(depth_values)).to(dev)
+    as_t = lambda a: a.to(dev) if torch.is_tensor(a) else torch.from_numpy(np.ascontiguousarray(a)).to(dev)  # noqa: E731  (tensors keep their graph)
+    feats, proj, depth = as_t(feats), as_t(proj_mats), as_t(depth_values)
     B, V, C, H, W = feats.shape
     D = depth.shape[1]
     ys, xs = torch.meshgrid(torch.arange(H, dtype=torch.float32, device=dev), torch.arange(W, dtype=torch.float32, device=dev),

@@ -5,7 +5,7 @@ import subprocess
 
 CSRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc")
 LIB = os.path.join(CSRC, "librmvd_b200.so")
-SOURCES = ("psweep.cu", "psweep_band.cu", "psweep_ws.cu", "psweep_push.cu", "psweep_bwd.cu", "mvs.cu", "mvs_var.cu", "fusion.cu", "vis.cu", "hostpipe.cu")
+SOURCES = ("psweep.cu", "psweep_band.cu", "psweep_ws.cu", "psweep_push.cu", "psweep_bwd.cu", "mvs.cu", "mvs_var.cu", "mvs_bwd.cu", "fusion.cu", "vis.cu", "hostpipe.cu")
 HEADERS = ("common.cuh", "psweep.cuh", "mvs_coord.cuh", os.path.join("..", "..", "include", "rmvd_b200.h"))
 NVCC_FLAGS = ["-O3", "-std=c++17", "--threads", "0", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-pthread", "-shared"]

@@ -1,5 +1,6 @@
 """Drop-in for the hot-path functions of ``rmvd/models/blocks/utils.py`` and the in-model cost-volume code of
-``rmvd/models/mvsnet.py`` on top of the sm_100a C ABI (``include/rmvd_b200.h``).  Forward only, no fallback.
+``rmvd/models/mvsnet.py`` on top of the sm_100a C ABI (``include/rmvd_b200.h``).  No fallback; forward only except
+``mvs_variance_volume`` / ``mvs_regress`` (the two steps MVSNet trains through).
 
 ``homo_warp`` (utils.py:222-268), ``depth_regression`` (:271-274), ``soft_argmin`` (:51-64), ``entropy`` (:67-68)
 keep the reference signatures; ``mvs_variance_volume`` and ``mvs_regress`` are the fused forms of
@@ -40,9 +41,62 @@ def homo_warp(src_feat, src_proj, ref_proj_inv, depth_values, return_indices=Fal
     return (out, ix0, iy0) if return_indices else out
 
 
+class _VarianceFunction(torch.autograd.Function):
+    """Differentiable ``mvs_variance_volume`` with respect to the feature maps (rmvd_mvs_variance_bwd): what autograd does in the
+    reference through homo_warp's grid_sample and the variance expression (mvsnet.py:123-136)."""
+
+    @staticmethod
+    def forward(ctx, feats, proj_mats, depth_values):
+        with torch.no_grad():
+            out = mvs_variance_volume(feats, proj_mats, depth_values)
+        ctx.save_for_backward(feats, proj_mats, depth_values)
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        feats, proj_mats, depth_values = ctx.saved_tensors
+        f, pm, dv, g = map(_f32c, (feats, proj_mats, depth_values, grad_out))
+        B, V, C, h, w = f.shape
+        grad = torch.empty_like(f)
+        st = _lib.load().rmvd_mvs_variance_bwd(_lib.ptr(f), _lib.ptr(pm), _lib.ptr(dv), _lib.ptr(g), B, V, C, h, w, dv.shape[1],
+                                               _lib.ptr(grad), _lib.stream_ptr())
+        _lib.check(st, "rmvd_mvs_variance_bwd")
+        return grad, None, None
+
+
+class _RegressFunction(torch.autograd.Function):
+    """Differentiable expected depth of ``mvs_regress`` with respect to the regularised cost (rmvd_mvs_regress_bwd); confidence and
+    indices carry no gradient (the reference computes them under no_grad, mvsnet.py:143-158)."""
+
+    @staticmethod
+    def forward(ctx, cost_reg, depth_values):
+        with torch.no_grad():
+            out = mvs_regress(cost_reg, depth_values)
+        ctx.save_for_backward(cost_reg, depth_values)
+        ctx.mark_non_differentiable(out["confidence"], out["depth_index"], out["expected_index"])
+        return out["depth"], out["confidence"], out["depth_index"], out["expected_index"]
+
+    @staticmethod
+    def backward(ctx, grad_depth, *_):
+        cost_reg, depth_values = ctx.saved_tensors
+        c, dv, g = map(_f32c, (cost_reg, depth_values, grad_depth))
+        B, D, h, w = c.shape
+        grad = torch.empty_like(c)
+        st = _lib.load().rmvd_mvs_regress_bwd(_lib.ptr(c), _lib.ptr(dv), _lib.ptr(g), B, D, h, w, _lib.ptr(grad), _lib.stream_ptr())
+        _lib.check(st, "rmvd_mvs_regress_bwd")
+        return grad, None
+
+
+def _needs_grad(*tensors):
+    return torch.is_grad_enabled() and any(isinstance(t, torch.Tensor) and t.requires_grad for t in tensors)
+
+
 def mvs_variance_volume(feats, proj_mats, depth_values, plane_range=None):
     """mvsnet.py:123-136 fused with homo_warp: ``feats [B,V,C,h,w]`` (view 0 = key), ``proj_mats [B,V,4,4]`` (view 0
-    already inverted), ``depth_values [B,D]`` -> variance ``[B,C,D,h,w]`` (or the ``plane_range`` slab of D)."""
+    already inverted), ``depth_values [B,D]`` -> variance ``[B,C,D,h,w]`` (or the ``plane_range`` slab of D).
+    Differentiable with respect to ``feats`` (full plane range only)."""
+    if _needs_grad(feats) and plane_range is None and not _needs_grad(proj_mats, depth_values):
+        return _VarianceFunction.apply(feats, proj_mats, depth_values)
     _forward_only("mvs_variance_volume", feats, proj_mats, depth_values)
     feats, proj_mats, depth_values = map(_f32c, (feats, proj_mats, depth_values))
     B, V, C, h, w = feats.shape
@@ -60,7 +114,10 @@ def mvs_variance_volume(feats, proj_mats, depth_values, plane_range=None):
 
 def mvs_regress(cost_reg, depth_values, return_prob=False):
     """mvsnet.py:140-160 in one pass: ``cost_reg [B,D,h,w]`` (pre-softmax), ``depth_values [B,D]`` ->
-    dict(depth, confidence, depth_index (int64), expected_index[, prob])."""
+    dict(depth, confidence, depth_index (int64), expected_index[, prob]).  ``depth`` is differentiable with respect to ``cost_reg``."""
+    if _needs_grad(cost_reg) and not return_prob and not _needs_grad(depth_values):
+        depth, conf, didx, eidx = _RegressFunction.apply(cost_reg, depth_values)
+        return dict(depth=depth, confidence=conf, depth_index=didx, expected_index=eidx)
     _forward_only("mvs_regress", cost_reg, depth_values)
     cost_reg, depth_values = _f32c(cost_reg), _f32c(depth_values)
     B, D, h, w = cost_reg.shape

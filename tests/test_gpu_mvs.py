@@ -271,3 +271,65 @@ def test_depth_regression_and_entropy_follow_the_reference_for_any_input(cuda_li
         bu.depth_regression(cu(p).requires_grad_(True), cu(dv))
     with torch.no_grad():
         bu.depth_regression(cu(p).requires_grad_(True), cu(dv))
+
+
+@pytest.mark.parametrize("case", cases.mvs_cases(include_large=False), ids=lambda c: c["name"])
+def test_mvs_backward_matches_reference_autograd(cuda_lib, case):
+    """Training direction of the MVSNet path: autograd through blocks.utils.mvs_variance_volume / mvs_regress (rmvd_mvs_variance_bwd,
+    rmvd_mvs_regress_bwd) against gradients frozen from the UNMODIFIED reference functions under CPU autograd
+    (tools/make_mvs_bwd_golden.py) and against the numpy oracle.  Tolerance 1e-4 of max|grad| (float atomics sum in any order)."""
+    import os
+    from robustmvd_b200.blocks import utils as bu
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", f"mvsbwd_{case['name']}.npz"))
+    g_var, g_depth = cases.mvs_upstream_grads(case)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
+    feats = t(case["feats"]).requires_grad_(True)
+    var = bu.mvs_variance_volume(feats, t(case["proj"]), t(case["depth"]))
+    (gf,) = torch.autograd.grad((var * t(g_var)).sum(), [feats])
+    cost = t(case["cost"]).requires_grad_(True)
+    reg = bu.mvs_regress(cost, t(case["depth"]))
+    assert not reg["confidence"].requires_grad and reg["depth"].requires_grad
+    (gc,) = torch.autograd.grad((reg["depth"] * t(g_depth)).sum(), [cost])
+    for got, key, ora in ((gf, "grad_feats", oracle.mvs_variance_backward(case["feats"], case["proj"], case["depth"], g_var)),
+                          (gc, "grad_cost", oracle.mvs_regress_backward(case["cost"], case["depth"], g_depth))):
+        got = got.cpu().numpy()
+        assert np.abs(got - g[key]).max() <= 1e-4 * np.abs(g[key]).max(), key
+        assert np.abs(got - ora).max() <= 1e-4 * np.abs(ora).max(), key
+    # forward values of the differentiable wrappers are the forward-only ones
+    with torch.no_grad():
+        assert torch.equal(var, bu.mvs_variance_volume(feats.detach(), t(case["proj"]), t(case["depth"])))
+
+
+def test_mvs_backward_at_a_larger_shape_against_torch_autograd(cuda_lib):
+    """DTU-quarter shape (56 x 76, C = 32, 5 views, 48 planes): the CUDA backward against torch's own autograd through the reference's
+    operator sequence run on the same device (oracle/torch_cpu.py with device='cuda': grid_sample + the variance expression)."""
+    from oracle import torch_cpu
+    from robustmvd_b200.blocks import utils as bu
+    case = cases.mvs_cases(include_large=True)[-1]
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
+    proj, depth = t(case["proj"]), t(case["depth"])
+    gen = torch.Generator(device="cuda").manual_seed(7)
+    feats = t(case["feats"]).requires_grad_(True)
+    var = bu.mvs_variance_volume(feats, proj, depth)
+    g_var = torch.randn(var.shape, device="cuda", generator=gen)
+    (gf,) = torch.autograd.grad((var * g_var).sum(), [feats])
+    feats2 = t(case["feats"]).requires_grad_(True)
+    var2 = torch_cpu.mvs_variance(feats2, proj, depth, device="cuda", return_torch=True)
+    (gf2,) = torch.autograd.grad((var2 * g_var).sum(), [feats2])
+    assert float((gf - gf2).abs().max()) <= 2e-4 * float(gf2.abs().max())
+
+
+def test_mvsnet_trains_through_the_cuda_path(cuda_lib):
+    """``mvsnet_train`` under train=True: one forward + backward through FeatureNet -> variance volume (CUDA) -> CostRegNet ->
+    regression (CUDA) produces finite, non-zero gradients for the first and the last layer."""
+    import robustmvd_b200 as rb
+    torch.manual_seed(cases.MODEL_SEED)
+    model = rb.create_model("mvsnet_train", pretrained=False, num_gpus=1, train=True)
+    cases.prepare_model_for_case(model, "mvsnet_train")
+    sample = model.input_adapter(**syn.model_sample(64, 96, 2, seed=13, batch=1, depth_range=(2.0, 40.0)))
+    pred, _ = model(**sample)
+    pred["depth"].mean().backward()
+    grads = {k: p.grad for k, p in model.named_parameters() if p.grad is not None}
+    first = next(k for k in grads if k.startswith("feature"))
+    assert len(grads) > 10 and all(bool(torch.isfinite(v).all()) for v in grads.values())
+    assert float(grads[first].abs().max()) > 0 and float(grads["cost_regularization.prob.weight"].abs().max()) > 0

@@ -173,3 +173,15 @@ def test_torchcorr_border_padding_oracle_matches_golden():
             assert np.array_equal(mask.astype(np.uint8), g[f"mask_{nm}_{wm}"])
             ref = g[f"corr_{nm}_{wm}"]
             assert np.abs(corr - ref).max() <= 1e-5 * np.abs(ref).max()
+
+
+@pytest.mark.parametrize("case", cases.mvs_cases(include_large=False), ids=lambda c: c["name"])
+def test_mvs_backward_oracle_matches_reference_autograd(case):
+    """oracle.mvs_variance_backward / mvs_regress_backward against gradients frozen from the unmodified reference functions under
+    CPU autograd (tools/make_mvs_bwd_golden.py)."""
+    g = load_golden("mvsbwd", case["name"])
+    g_var, g_depth = cases.mvs_upstream_grads(case)
+    a = oracle.mvs_variance_backward(case["feats"], case["proj"], case["depth"], g_var)
+    b = oracle.mvs_regress_backward(case["cost"], case["depth"], g_depth)
+    assert np.abs(a - g["grad_feats"]).max() <= 2e-6 * np.abs(g["grad_feats"]).max()
+    assert np.abs(b - g["grad_cost"]).max() <= 2e-6 * np.abs(g["grad_cost"]).max()

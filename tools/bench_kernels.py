@@ -125,6 +125,16 @@ def main():
     add("mvs_variance_cfg3", lambda: bu.mvs_variance_volume(feats, proj, depth),
         4 * c3["C"] * P3 * c3["V"] + 4 * c3["C"] * c3["D"] * P3, c3["D"] * P3, "voxels")
     add("mvs_regress_cfg3", lambda: bu.mvs_regress(cost, depth), 4 * c3["D"] * P3 + 8 * P3, c3["D"] * P3, "voxels")
+    # training direction of the MVSNet path (rmvd_mvs_variance_bwd / rmvd_mvs_regress_bwd) at cfg3
+    featsg = feats.clone().requires_grad_(True)
+    varg = bu.mvs_variance_volume(featsg, proj, depth)
+    gvar = torch.randn_like(varg)
+    add("mvs_variance_bwd_cfg3", lambda: torch.autograd.grad(varg, featsg, gvar, retain_graph=True),
+        2 * 4 * c3["C"] * P3 * c3["V"] + 4 * c3["C"] * c3["D"] * P3, c3["D"] * P3, "voxels")
+    costg = cost.clone().requires_grad_(True)
+    depg = bu.mvs_regress(costg, depth)["depth"]
+    gdep = torch.randn_like(depg)
+    add("mvs_regress_bwd_cfg3", lambda: torch.autograd.grad(depg, costg, gdep, retain_graph=True), 8 * c3["D"] * P3 + 8 * P3, c3["D"] * P3, "voxels")
     add("homo_warp_cfg3", lambda: bu.homo_warp(feats[:, 1], proj[:, 1], proj[:, 0], depth),
         4 * c3["C"] * P3 + 4 * c3["C"] * c3["D"] * P3, c3["D"] * P3, "voxels")
     add("soft_argmin_cfg3", lambda: bu.soft_argmin(cost, 1), 8 * c3["D"] * P3, c3["D"] * P3, "voxels")

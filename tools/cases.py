@@ -160,6 +160,18 @@ def mvs_cases(include_large=True):
     return cases
 
 
+def mvs_upstream_grads(case):
+    """Upstream gradients of the MVSNet backward cases (tools/make_mvs_bwd_golden.py, tests/test_gpu_mvs.py): for the variance
+    volume ``[B,C,D,h,w]`` (a tenth of the entries exactly zero) and the regressed depth ``[B,h,w]``, from the case's shapes."""
+    B, V, C, h, w = case["feats"].shape
+    D = case["depth"].shape[1]
+    rng = np.random.default_rng(1000 + B * 131 + C * 17 + D)
+    g_var = rng.standard_normal((B, C, D, h, w), dtype=np.float32)
+    g_var[rng.random(g_var.shape) < 0.1] = 0.0
+    g_depth = rng.standard_normal((B, h, w), dtype=np.float32)
+    return g_var, g_depth
+
+
 # ---------------------------------------------------------------------------------------------------------
 # model-level cases (tools/make_model_golden.py, tests/test_gpu_models.py)
 # ---------------------------------------------------------------------------------------------------------
