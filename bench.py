@@ -260,6 +260,24 @@ def secondary_records(torch, dev, peaks, with_cpu):
     cpu_var, cpu_reg = time_cpu_mvs() if with_cpu else (None, None)
     cold, warm = _cold_warm(torch, lambda: bu.mvs_variance_volume(feats, proj, depth), flush, reps=5)
     ab = 4 * c3["C"] * P * c3["V"] + 4 * c3["C"] * c3["D"] * P
+    # stock PyTorch on the same B200 running the reference's operator sequence (the bar for every kernel)
+    from oracle import torch_cpu
+
+    def stock(fn, reps):
+        try:
+            with torch.no_grad():
+                ref = fn()
+                c, _ = _cold_warm(torch, fn, flush, reps=reps)
+            return ref, c
+        except Exception as e:  # noqa: BLE001
+            return None, repr(e)[:200]
+    ref_var, stock_var_ms = stock(lambda: torch_cpu.mvs_variance(feats, proj, depth, device=dev, return_torch=True), 3)
+    stock_var = {"what": "oracle/torch_cpu.mvs_variance with device='cuda': grid_sample per view + the variance expression (mvsnet.py:123-136)",
+                 "ms_cold": stock_var_ms}
+    if ref_var is not None:
+        ours = bu.mvs_variance_volume(feats, proj, depth)
+        stock_var["max_abs_diff_over_max"] = float((ours - ref_var).abs().max() / ref_var.abs().max())
+        del ours, ref_var
     # e2e: pinned host features in, variance volume back in pinned host memory
     h_feats = torch.from_numpy(m["feats"]).pin_memory()
     h_var = torch.empty((1, c3["C"], c3["D"], c3["h"], c3["w"]), dtype=torch.float32).pin_memory()
@@ -279,9 +297,14 @@ def secondary_records(torch, dev, peaks, with_cpu):
                              "algorithmic_bytes_per_launch": ab, "timing": "ms_cold"},
                 "e2e": {"value": c3["D"] * P / (ms_e2e * 1e-3), "unit": "voxels/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h_feats.numel() * 4,
                         "d2h_bytes_per_step": h_var.numel() * 4, "api": "blocks.utils.mvs_variance_volume from pinned host features, volume copied back"},
-                "cpu_baseline": cpu_var})
+                "torch_gpu_baseline": stock_var, "cpu_baseline": cpu_var})
     cold, warm = _cold_warm(torch, lambda: bu.mvs_regress(cost, depth), flush)
     ab = 4 * c3["D"] * P + 8 * P
+    ref_reg, stock_reg_ms = stock(lambda: torch_cpu.mvs_regress(cost, depth, device=dev, return_torch=True), 5)
+    stock_reg = {"what": "oracle/torch_cpu.mvs_regress with device='cuda': softmax, two weighted sums, pad + avg_pool3d, gather (mvsnet.py:140-160)",
+                 "ms_cold": stock_reg_ms}
+    if ref_reg is not None:
+        stock_reg["depth_max_rel_diff"] = float(((bu.mvs_regress(cost, depth)["depth"] - ref_reg[0]).abs() / ref_reg[0].abs()).max())
     h_cost = torch.from_numpy(m["cost"]).pin_memory()
     h_depth = torch.empty((1, c3["h"], c3["w"]), dtype=torch.float32).pin_memory()
 
@@ -300,7 +323,7 @@ def secondary_records(torch, dev, peaks, with_cpu):
                              "algorithmic_bytes_per_launch": ab, "timing": "ms_cold"},
                 "e2e": {"value": P / (ms_e2e * 1e-3), "unit": "pixels/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h_cost.numel() * 4,
                         "d2h_bytes_per_step": h_depth.numel() * 4, "api": "blocks.utils.mvs_regress from a pinned host cost volume, depth copied back"},
-                "cpu_baseline": cpu_reg})
+                "torch_gpu_baseline": stock_reg, "cpu_baseline": cpu_reg})
     return out
 
 

@@ -108,15 +108,18 @@ def mvs_variance(feats, proj_mats, depth_values, device=None, return_torch=False
     return out if return_torch else out.cpu().numpy()
 
 
-def mvs_regress(cost, depth_values, device=None):
-    """softmax + depth_regression + 4-bin confidence (mvsnet.py:140-160, utils.py:271-274) on stock torch ops.  numpy in/out."""
+def mvs_regress(cost, depth_values, device=None, return_torch=False):
+    """softmax + depth_regression + 4-bin confidence (mvsnet.py:140-160, utils.py:271-274) on stock torch ops.  numpy in/out
+    (tensors in / out with return_torch)."""
     dev = torch.device("cpu" if device is None else device)
-    cost = torch.from_numpy(np.ascontiguousarray(cost)).to(dev)
-    depth = torch.from_numpy(np.ascontiguousarray(depth_values)).to(dev)
+    as_t = lambda a: a.to(dev) if torch.is_tensor(a) else torch.from_numpy(np.ascontiguousarray(a)).to(dev)  # noqa: E731
+    cost, depth = as_t(cost), as_t(depth_values)
     prob = F.softmax(cost, dim=1)
     d = torch.sum(prob * depth.view(*depth.shape, 1, 1), 1)
     D = cost.shape[1]
     p4 = 4 * F.avg_pool3d(F.pad(prob.unsqueeze(1), pad=(0, 0, 0, 0, 1, 2)), (4, 1, 1), stride=1, padding=0).squeeze(1)
     idx = torch.sum(prob * torch.arange(D, device=dev, dtype=torch.float32).view(1, D, 1, 1), 1).long()
     conf = torch.gather(p4, 1, idx.unsqueeze(1)).squeeze(1)
+    if return_torch:
+        return d, conf
     return d.cpu().numpy(), conf.cpu().numpy()
