@@ -9,8 +9,8 @@
  *   - all tensors float32, contiguous, NCHW unless stated; pointers are DEVICE pointers unless the name
  *     ends in `_host` or the comment says "host array";
  *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*), re-entrant, and holds no
- *     global mutable state; scratch memory is passed in by the caller (`workspace`) -- the one exception is
- *     rmvd_psweep_corr_fwd_static, which says so;
+ *     global mutable state; scratch memory is passed in by the caller (`workspace`) -- the exceptions say so:
+ *     rmvd_psweep_corr_fwd_static (static device scratch) and rmvd_host_expand_mask[_async] (host worker pool);
  *   - return value: 0 ok, <0 invalid argument (RMVD_E_*), >0 a cudaError_t; nothing throws across the ABI;
  *   - there is no CPU fallback: without a CUDA device the calls return a cudaError_t.
  */
