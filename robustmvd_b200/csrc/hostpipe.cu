@@ -6,6 +6,7 @@
 // float32 device-to-host copy of the mask.  No counterpart in the reference (it keeps the tensors on one device).
 #include <cuda_runtime.h>
 #include <emmintrin.h>
+#include <unistd.h>
 
 #include <condition_variable>
 #include <cstdint>
@@ -72,9 +73,23 @@ class ExpandPool {
     std::lock_guard<std::mutex> job(job_mutex_);
     {
       std::unique_lock<std::mutex> lk(m_);
-      while ((int)workers_.size() < (int)parts - 1) {
-        const int id = (int)workers_.size();
-        workers_.emplace_back([this, id] { worker(id); });
+      if (pid_ != getpid()) {                          // forked child: the parent's worker threads do not exist here
+        for (auto& t : workers_) t.detach();
+        workers_.clear();
+        pid_ = getpid();
+      }
+      try {
+        while ((int)workers_.size() < (int)parts - 1) {
+          const int id = (int)workers_.size();
+          workers_.emplace_back([this, id] { worker(id); });
+        }
+      } catch (...) {                                  // no more threads to be had: nothing throws across the C ABI, fewer parts do
+        parts = workers_.size() + 1;
+      }
+      if (parts == 1) {
+        lk.unlock();
+        expand_range(src, dst, n);
+        return;
       }
       src_ = src; dst_ = dst; n_ = n; parts_ = (int)parts; pending_ = (int)parts - 1;
       ++generation_;
@@ -119,6 +134,7 @@ class ExpandPool {
   size_t n_ = 0;
   int parts_ = 0, pending_ = 0;
   unsigned long long generation_ = 0;
+  pid_t pid_ = getpid();
 };
 
 struct ExpandJob {

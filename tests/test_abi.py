@@ -95,6 +95,27 @@ def test_host_mask_expansion(lib):
                 assert np.array_equal(d, s.astype(np.float32)) and np.all(dst[:off] == 7) and np.all(dst[off + n:] == 7)
 
 
+def test_host_mask_expansion_survives_fork(lib):
+    """The worker pool belongs to the process that created it: a forked child (e.g. a data-loader worker) builds its own."""
+    import numpy as np
+    n = 1 << 20
+    src = (np.arange(n) % 3 == 0).astype(np.uint8)
+    dst = np.empty(n, np.float32)
+    assert lib.rmvd_host_expand_mask(ctypes.c_void_p(src.ctypes.data), ctypes.c_void_p(dst.ctypes.data), n, 4) == 0
+    pid = os.fork()
+    if pid == 0:
+        ok = 1
+        try:
+            out = np.empty(n, np.float32)
+            rc = lib.rmvd_host_expand_mask(ctypes.c_void_p(src.ctypes.data), ctypes.c_void_p(out.ctypes.data), n, 4)
+            ok = 0 if rc == 0 and np.array_equal(out, src.astype(np.float32)) else 1
+        finally:
+            os._exit(ok)
+    _, status = os.waitpid(pid, 0)
+    assert os.WIFEXITED(status) and os.WEXITSTATUS(status) == 0
+    assert np.array_equal(dst, src.astype(np.float32))
+
+
 def test_missing_library_fails_loudly(monkeypatch, tmp_path):
     monkeypatch.setattr(_lib, "_lib", None)
     monkeypatch.setattr(_build, "LIB", str(tmp_path / "nope.so"))
