@@ -538,7 +538,7 @@ def run_ours(args):
 
     chunks = [int(c) for c in str(args.e2e_chunk).split(',')]
     pipe = HostPlanesweepPipeline(dev, block, chunk_frames=chunks, compact_mask=True,      # mask over PCIe as bytes, expanded on the host
-                                  mask_threads=args.e2e_mask_threads or None)
+                                  mask_threads=args.e2e_mask_threads or None, mask_transport=args.e2e_mask_transport)
     pipe_f32 = HostPlanesweepPipeline(dev, block, chunk_frames=chunks, compact_mask=False)  # mask over PCIe as float32
 
     def step_e2e():   # pinned host features in, corr + mask back in pinned host memory; returns after the last byte landed
@@ -630,7 +630,8 @@ def run_ours(args):
         achieved = ab / (ms_launch * 1e-3) / 1e9
         h2d = 4 * frames * CFG["C"] * P * (1 + CFG["V"])
         d2h_f32 = 2 * 4 * frames * CFG["V"] * CFG["S"] * P
-        d2h = (4 + 1) * frames * CFG["V"] * CFG["S"] * P       # corr float32 + mask as bytes
+        mask_bits = 1 if args.e2e_mask_transport == "bits" else 8
+        d2h = (4 * 8 + mask_bits) * frames * CFG["V"] * CFG["S"] * P // 8   # corr float32 + mask as bytes (or bits)
         line = base_line(args, frames, world)
         line.update({
             "impl": "ours", "value": voxels(frames) * world / (ms_step * 1e-3), "ms_per_step": ms_step,
@@ -640,8 +641,10 @@ def run_ours(args):
                     "h2d_gbs_per_rank": h2d / ms_e2e / 1e6, "d2h_gbs_per_rank": d2h / ms_e2e / 1e6,
                     "ms_per_step_blocking": ms_e2e_blocking,
                     "value_blocking": voxels(frames) * world / (ms_e2e_blocking * 1e-3),
-                    "mask_transport": "u8 over PCIe (rmvd_mask_pack_u8) + host expansion to float32 (rmvd_host_expand_mask_async, "
-                                      "%d worker threads) inside the timed region" % pipe_threads,
+                    "mask_transport": "%s over PCIe (rmvd_mask_pack_%s) + host expansion to float32 (rmvd_host_expand_mask%s_async, "
+                                      "%d worker threads) inside the timed region" % (
+                                          (("one bit per element", "bits", "_bits") if args.e2e_mask_transport == "bits" else ("u8", "u8", ""))
+                                          + (pipe_threads,)),
                     "host_mask_bit_identical_to_float32_copy": e2e_mask_equal,
                     "float32_mask_transport": {"ms_per_step": ms_e2e_f32, "value": voxels(frames) * world / (ms_e2e_f32 * 1e-3),
                                                "d2h_bytes_per_step": d2h_f32, "h2d_gbs_per_rank": h2d / ms_e2e_f32 / 1e6,
@@ -691,6 +694,7 @@ def main():
     ap.add_argument("--frames", type=int, default=16, help="frames per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true", help="headline line only (no secondary / baseline / sweep / slab records)")
+    ap.add_argument("--e2e-mask-transport", default="u8", choices=("bits", "u8"), help="compact mask transport of the e2e leg (bits measured slower)")
     ap.add_argument("--e2e-mask-threads", type=int, default=0, help="worker threads of the host-side mask expansion (0 = pipeline default)")
     ap.add_argument("--e2e-chunk", default="2", help="frames per chunk of the host pipeline (e2e leg); a,b,c = schedule, last repeats")
     args = ap.parse_args()

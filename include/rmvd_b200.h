@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define RMVD_ABI_VERSION 6
+#define RMVD_ABI_VERSION 7
 #define RMVD_MAX_PEERS 8      /* ranks of one depth-slab communicator (GPUs of one NVSwitch box) */
 
 #define RMVD_OK 0
@@ -202,6 +202,11 @@ int rmvd_psweep_corr_fwd_act(const float* pre_key, const float* const* pre_src, 
 int rmvd_mask_pack_u8(const float* mask, uint8_t* packed, size_t n, void* stream);
 int rmvd_host_expand_mask(const uint8_t* packed_host, float* mask_host, size_t n, int threads);
 int rmvd_host_expand_mask_async(const uint8_t* packed_host, float* mask_host, size_t n, int threads, void* stream);
+/* The same three with ONE BIT per element (word j, bit i = element 32 j + i; ceil(n / 32) words; little-endian host): an eighth of
+ * the bytes again -- what pipeline.HostPlanesweepPipeline uses by default. */
+int rmvd_mask_pack_bits(const float* mask, uint32_t* packed, size_t n, void* stream);
+int rmvd_host_expand_mask_bits(const uint32_t* packed_host, float* mask_host, size_t n, int threads);
+int rmvd_host_expand_mask_bits_async(const uint32_t* packed_host, float* mask_host, size_t n, int threads, void* stream);
 
 /*
  * Backward of rmvd_psweep_corr_fwd with respect to the feature maps.  The reference obtains it from

@@ -34,6 +34,18 @@ __global__ void __launch_bounds__(256) mask_pack_kernel(const float* __restrict_
   }
 }
 
+// one bit per element: word j, bit i = mask[32 j + i] != 0 (a warp reads 128 contiguous bytes and writes one word per trip)
+__global__ void __launch_bounds__(256) mask_pack_bits_kernel(const float* __restrict__ mask, unsigned* __restrict__ out, size_t words, size_t n) {
+  const int lane = threadIdx.x & 31;
+  const size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((size_t)gridDim.x * blockDim.x) >> 5;
+  for (size_t j = warp; j < words; j += nwarps) {
+    const size_t i = j * 32 + lane;
+    const float m = i < n ? __ldcs(mask + i) : 0.f;
+    const unsigned bits = __ballot_sync(0xffffffffu, m != 0.f);
+    if (lane == 0) out[j] = bits;
+  }
+}
+
 // dst[i] = (float)src[i] for src in {0, 1} (any byte value converts exactly); streaming stores where dst is 16-byte aligned
 void expand_range(const uint8_t* src, float* dst, size_t n) {
   size_t i = 0;
@@ -51,6 +63,36 @@ void expand_range(const uint8_t* src, float* dst, size_t n) {
   _mm_sfence();
 }
 
+// dst[i] = bit i of the packed words (i in [0, n), n counted from a byte boundary of `src`): one table entry of eight floats per byte
+struct BitLut {
+  alignas(16) float f[256][8];
+  BitLut() {
+    for (int b = 0; b < 256; ++b)
+      for (int k = 0; k < 8; ++k) f[b][k] = (float)((b >> k) & 1);
+  }
+};
+
+void expand_bits_range(const uint8_t* src, float* dst, size_t n) {
+  static const BitLut lut;
+  const bool aligned = (reinterpret_cast<uintptr_t>(dst) & 15u) == 0;
+  size_t i = 0;
+  if (aligned) {
+    for (; i + 8 <= n; i += 8) {
+      const float* e = lut.f[src[i >> 3]];
+      _mm_stream_ps(dst + i, _mm_load_ps(e));
+      _mm_stream_ps(dst + i + 4, _mm_load_ps(e + 4));
+    }
+  } else {
+    for (; i + 8 <= n; i += 8) {
+      const float* e = lut.f[src[i >> 3]];
+      _mm_storeu_ps(dst + i, _mm_load_ps(e));
+      _mm_storeu_ps(dst + i + 4, _mm_load_ps(e + 4));
+    }
+  }
+  for (; i < n; ++i) dst[i] = (float)((src[i >> 3] >> (i & 7)) & 1);
+  _mm_sfence();
+}
+
 // Worker pool of the expansion: created on first use, at most kMaxWorkers threads, one job at a time (jobs arrive from one CUDA
 // callback thread or from synchronous callers; a mutex serialises them).
 constexpr int kMaxWorkers = 32;
@@ -62,14 +104,14 @@ class ExpandPool {
     return *p;
   }
 
-  void run(const uint8_t* src, float* dst, size_t n, int threads) {
+  void run(const uint8_t* src, float* dst, size_t n, int threads, bool bits = false) {
     if (threads < 1) threads = 1;
     if (threads > kMaxWorkers) threads = kMaxWorkers;
     const size_t min_part = (size_t)1 << 16;   // below 64 K elements per part a thread hand-off costs more than it saves
     size_t parts = (n + min_part - 1) / min_part;
     if (parts < 1) parts = 1;
     if (parts > (size_t)threads) parts = (size_t)threads;
-    if (parts == 1) { expand_range(src, dst, n); return; }
+    if (parts == 1) { bits ? expand_bits_range(src, dst, n) : expand_range(src, dst, n); return; }
     std::lock_guard<std::mutex> job(job_mutex_);
     {
       std::unique_lock<std::mutex> lk(m_);
@@ -88,10 +130,10 @@ class ExpandPool {
       }
       if (parts == 1) {
         lk.unlock();
-        expand_range(src, dst, n);
+        bits ? expand_bits_range(src, dst, n) : expand_range(src, dst, n);
         return;
       }
-      src_ = src; dst_ = dst; n_ = n; parts_ = (int)parts; pending_ = (int)parts - 1;
+      src_ = src; dst_ = dst; n_ = n; bits_ = bits; parts_ = (int)parts; pending_ = (int)parts - 1;
       ++generation_;
     }
     cv_.notify_all();
@@ -103,9 +145,11 @@ class ExpandPool {
  private:
   void part(int k) {
     // parts are multiples of 16 elements so that every part but the first keeps the destination's alignment phase
-    const size_t per = ((n_ + parts_ - 1) / parts_ + 15) & ~(size_t)15;
+    const size_t per = ((n_ + parts_ - 1) / parts_ + 15) & ~(size_t)15;       // multiple of 16: whole bytes of a bit-packed source too
     const size_t b = per * k, e = b + per < n_ ? b + per : n_;
-    if (b < e) expand_range(src_ + b, dst_ + b, e - b);
+    if (b >= e) return;
+    if (bits_) expand_bits_range(src_ + (b >> 3), dst_ + b, e - b);
+    else expand_range(src_ + b, dst_ + b, e - b);
   }
 
   void worker(int id) {
@@ -132,6 +176,7 @@ class ExpandPool {
   const uint8_t* src_ = nullptr;
   float* dst_ = nullptr;
   size_t n_ = 0;
+  bool bits_ = false;
   int parts_ = 0, pending_ = 0;
   unsigned long long generation_ = 0;
   pid_t pid_ = getpid();
@@ -142,11 +187,12 @@ struct ExpandJob {
   float* dst;
   size_t n;
   int threads;
+  bool bits;
 };
 
 void CUDART_CB expand_callback(void* p) {
   ExpandJob* j = static_cast<ExpandJob*>(p);
-  ExpandPool::get().run(j->src, j->dst, j->n, j->threads);
+  ExpandPool::get().run(j->src, j->dst, j->n, j->threads, j->bits);
   delete j;
 }
 
@@ -175,7 +221,34 @@ extern "C" int rmvd_host_expand_mask(const uint8_t* packed_host, float* mask_hos
 extern "C" int rmvd_host_expand_mask_async(const uint8_t* packed_host, float* mask_host, size_t n, int threads, void* stream) {
   if (!packed_host || !mask_host) return RMVD_E_NULL;
   if (n == 0) return RMVD_OK;
-  rmvd::ExpandJob* j = new (std::nothrow) rmvd::ExpandJob{packed_host, mask_host, n, threads};
+  rmvd::ExpandJob* j = new (std::nothrow) rmvd::ExpandJob{packed_host, mask_host, n, threads, false};
+  if (!j) return (int)cudaErrorMemoryAllocation;
+  const cudaError_t e = cudaLaunchHostFunc((cudaStream_t)stream, rmvd::expand_callback, j);
+  if (e != cudaSuccess) delete j;
+  return (int)e;
+}
+
+extern "C" int rmvd_mask_pack_bits(const float* mask, uint32_t* packed, size_t n, void* stream) {
+  if (!mask || !packed) return RMVD_E_NULL;
+  if (n == 0) return RMVD_OK;
+  const size_t words = (n + 31) / 32;
+  size_t blocks = (words + 7) / 8;                     // 8 warps per CTA, one word per warp and trip
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  rmvd::mask_pack_bits_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(mask, packed, words, n);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int rmvd_host_expand_mask_bits(const uint32_t* packed_host, float* mask_host, size_t n, int threads) {
+  if (!packed_host || !mask_host) return RMVD_E_NULL;
+  if (n == 0) return RMVD_OK;
+  rmvd::ExpandPool::get().run(reinterpret_cast<const uint8_t*>(packed_host), mask_host, n, threads, true);
+  return RMVD_OK;
+}
+
+extern "C" int rmvd_host_expand_mask_bits_async(const uint32_t* packed_host, float* mask_host, size_t n, int threads, void* stream) {
+  if (!packed_host || !mask_host) return RMVD_E_NULL;
+  if (n == 0) return RMVD_OK;
+  rmvd::ExpandJob* j = new (std::nothrow) rmvd::ExpandJob{reinterpret_cast<const uint8_t*>(packed_host), mask_host, n, threads, true};
   if (!j) return (int)cudaErrorMemoryAllocation;
   const cudaError_t e = cudaLaunchHostFunc((cudaStream_t)stream, rmvd::expand_callback, j);
   if (e != cudaSuccess) delete j;

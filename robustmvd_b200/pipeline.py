@@ -14,7 +14,10 @@ i and the steady-state cost of a batch is the longer of its two PCIe directions.
 0.0 and 1.0 (planesweep_corr.py:99-102, :189-191) and is half of the device-to-host bytes.  ``rmvd_mask_pack_u8`` packs it on the
 device, the bytes land in a pinned staging ring, and ``rmvd_host_expand_mask_async`` -- a host function queued on a fourth stream,
 running on the library's worker threads -- writes the float32 values into ``out_mask``; the host buffer ends up bit-identical to
-the plain float32 copy (``compact_mask=False``).
+the plain float32 copy (``compact_mask=False``).  ``mask_transport="bits"`` sends one BIT per element (``rmvd_mask_pack_bits`` /
+``rmvd_host_expand_mask_bits_async``; per-view element counts that are not multiples of 32 fall back to bytes): an eighth of the
+mask bytes again, but measured slower end to end on the B200 box (9.0-9.9 ms against 8.6-8.8 ms per 16-frame step), so bytes are
+the default.
 """
 import ctypes
 import os
@@ -38,9 +41,11 @@ def _default_mask_threads():
 
 
 class HostPlanesweepPipeline:
-    def __init__(self, device, block=None, chunk_frames=2, compact_mask=True, mask_threads=None):
+    def __init__(self, device, block=None, chunk_frames=2, compact_mask=True, mask_threads=None, mask_transport="u8"):
         self.device = torch.device(device)
         self.compact_mask = bool(compact_mask)
+        assert mask_transport in ("bits", "u8")
+        self.mask_transport = mask_transport
         self.mask_threads = int(mask_threads) if mask_threads else _default_mask_threads()
         self.s_exp = torch.cuda.Stream(self.device)      # carries the host-side mask expansion (host functions only)
         self._stage = [None] * 4                          # pinned byte staging ring: [tensor, event after its expansion]
@@ -151,7 +156,12 @@ class HostPlanesweepPipeline:
                                              feat_sources=[f[n0:n1] for f in d_src],
                                              source_to_key_transforms=[t[n0:n1] for t in source_to_key_transforms],
                                              out=(ring[1], ring[2]), **kw)
-                if self.compact_mask:
+                per_view = ring[2][0].numel()
+                bits = self.compact_mask and self.mask_transport == "bits" and per_view % 32 == 0
+                if bits:        # view v's words start at byte v * per_view / 8 of the chunk's byte buffer (ring[4] is sized for bytes)
+                    _lib.check(lib.rmvd_mask_pack_bits(_lib.ptr(ring[2]), _lib.ptr(ring[4]), ring[2].numel(), _lib.stream_ptr()),
+                               "rmvd_mask_pack_bits")
+                elif self.compact_mask:
                     _lib.check(lib.rmvd_mask_pack_u8(_lib.ptr(ring[2]), _lib.ptr(ring[4]), ring[2].numel(), _lib.stream_ptr()),
                                "rmvd_mask_pack_u8")
                 ev_cmp.record(self.s_cmp)
@@ -162,7 +172,10 @@ class HostPlanesweepPipeline:
                     out_corr[v, n0:n1].copy_(ring[1][v], non_blocking=True)
                     if not self.compact_mask:
                         out_mask[v, n0:n1].copy_(ring[2][v], non_blocking=True)
-                if self.compact_mask:
+                if bits:
+                    nb = ring[2].numel() // 8
+                    stage[0].view(-1)[:nb].copy_(ring[4].view(-1)[:nb], non_blocking=True)
+                elif self.compact_mask:
                     stage[0].copy_(ring[4], non_blocking=True)
                 ring[3] = torch.cuda.Event()
                 ring[3].record(self.s_out)
@@ -171,9 +184,14 @@ class HostPlanesweepPipeline:
                     self.s_exp.wait_event(ring[3])
                     for v in range(V):
                         dst = out_mask[v, n0:n1]
-                        _lib.check(lib.rmvd_host_expand_mask_async(ctypes.c_void_p(stage[0][v].data_ptr()), ctypes.c_void_p(dst.data_ptr()),
-                                                                   dst.numel(), self.mask_threads, _lib.stream_ptr()),
-                                   "rmvd_host_expand_mask_async")
+                        if bits:
+                            _lib.check(lib.rmvd_host_expand_mask_bits_async(
+                                ctypes.c_void_p(stage[0].data_ptr() + v * (per_view // 8)), ctypes.c_void_p(dst.data_ptr()), dst.numel(),
+                                self.mask_threads, _lib.stream_ptr()), "rmvd_host_expand_mask_bits_async")
+                        else:
+                            _lib.check(lib.rmvd_host_expand_mask_async(ctypes.c_void_p(stage[0][v].data_ptr()), ctypes.c_void_p(dst.data_ptr()),
+                                                                       dst.numel(), self.mask_threads, _lib.stream_ptr()),
+                                       "rmvd_host_expand_mask_async")
                     stage[1] = torch.cuda.Event()
                     stage[1].record(self.s_exp)
             self._cmp_done[slot] = ev_cmp

@@ -95,6 +95,23 @@ def test_host_mask_expansion(lib):
                 assert np.array_equal(d, s.astype(np.float32)) and np.all(dst[:off] == 7) and np.all(dst[off + n:] == 7)
 
 
+def test_host_mask_bit_expansion(lib):
+    """rmvd_host_expand_mask_bits: one bit per element (numpy packbits, little bit order) -> float32, any alignment and thread count."""
+    import numpy as np
+    rng = np.random.default_rng(4)
+    for n in (1, 7, 8, 31, 32, 33, 3 * 65536 + 5, 1 << 21):
+        m = rng.random(n) < 0.5
+        packed = np.packbits(m, bitorder="little")
+        pad = np.zeros((len(packed) + 3) // 4 * 4, np.uint8)
+        pad[:len(packed)] = packed
+        for off in (0, 1):
+            for threads in (1, 3, 8):
+                dst = np.full(n + 8, 7.0, np.float32)
+                d = dst[off:off + n]
+                assert lib.rmvd_host_expand_mask_bits(ctypes.c_void_p(pad.ctypes.data), ctypes.c_void_p(d.ctypes.data), n, threads) == 0
+                assert np.array_equal(d, m.astype(np.float32)) and np.all(dst[:off] == 7) and np.all(dst[off + n:] == 7)
+
+
 def test_host_mask_expansion_survives_fork(lib):
     """The worker pool belongs to the process that created it: a forked child (e.g. a data-loader worker) builds its own."""
     import numpy as np

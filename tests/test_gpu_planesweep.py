@@ -207,7 +207,7 @@ def test_shared_reciprocal_division_is_exact(cuda_lib):
     assert float((q1 - q2).abs().max()) == 0.0
 
 
-@pytest.mark.parametrize("compact", [True, False])
+@pytest.mark.parametrize("compact", ["bits", "u8", False])
 def test_host_pipeline_equals_direct_call(cuda_lib, compact):
     """HostPlanesweepPipeline (chunked H2D / kernels / D2H on three streams) returns the block's outputs bit for bit, with the
     mask sent as bytes and expanded on the host (compact_mask=True) or as float32."""
@@ -223,7 +223,8 @@ def test_host_pipeline_equals_direct_call(cuda_lib, compact):
     hk = torch.from_numpy(inp["feat_key"]).pin_memory()
     hs = [torch.from_numpy(f).pin_memory() for f in inp["feat_sources"]]
     out = torch.zeros((2, V, N, S, 24, 40), dtype=torch.float32).pin_memory()
-    pipe = HostPlanesweepPipeline(dev, PlanesweepCorrelation(), chunk_frames=2, compact_mask=compact, mask_threads=3)
+    pipe = HostPlanesweepPipeline(dev, PlanesweepCorrelation(), chunk_frames=2, compact_mask=bool(compact), mask_threads=3,
+                                  mask_transport=compact or "bits")
     for _ in range(2):   # second call reuses the persistent device buffers
         out.fill_(7.0)
         pipe.run(hk, Kk, hs, Ts, out[0], out[1], **kw)
@@ -234,7 +235,7 @@ def test_host_pipeline_equals_direct_call(cuda_lib, compact):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("compact", [True, False])
+@pytest.mark.parametrize("compact", ["bits", "u8", False])
 def test_host_pipeline_stream_of_batches(cuda_lib, compact):
     """run(wait=False) per batch + finish(): consecutive batches overlap (double-buffered device inputs) and every batch
     still equals the direct call on its own inputs."""
@@ -244,7 +245,7 @@ def test_host_pipeline_stream_of_batches(cuda_lib, compact):
     N, V, S, B = 3, 2, 40, 5
     kw = dict(num_sampling_points=S, min_depth=0.4, max_depth=1000.0)
     dev = torch.device("cuda:0")
-    pipe = HostPlanesweepPipeline(dev, PlanesweepCorrelation(), chunk_frames=[1, 2], compact_mask=compact)
+    pipe = HostPlanesweepPipeline(dev, PlanesweepCorrelation(), chunk_frames=[1, 2], compact_mask=bool(compact), mask_transport=compact or "bits")
     batches = []
     for b in range(B):
         inp = syn.planesweep_inputs(24, 40, 64, V, n=N, seed=200 + b)
@@ -313,6 +314,17 @@ def test_mask_pack_and_host_expand(cuda_lib):
         torch.cuda.synchronize()
         assert torch.equal(dst, m.cpu()) and float(host[0]) == 7.0 and bool((host[1 + n:] == 7.0).all())
         assert bool((packed[n:] == 9).all())
+        # one bit per element
+        words = (n + 31) // 32
+        pb = torch.full((words + 1,), -1, dtype=torch.int32, device="cuda")
+        _lib.check(cuda_lib.rmvd_mask_pack_bits(_lib.ptr(m), _lib.ptr(pb), n, _lib.stream_ptr()), "pack bits")
+        sb = torch.empty(words + 1, dtype=torch.int32).pin_memory()
+        sb.copy_(pb, non_blocking=True)
+        host.fill_(7.0)
+        _lib.check(cuda_lib.rmvd_host_expand_mask_bits_async(ctypes.c_void_p(sb.data_ptr()), ctypes.c_void_p(dst.data_ptr()), n, 4,
+                                                             _lib.stream_ptr()), "expand bits")
+        torch.cuda.synchronize()
+        assert torch.equal(dst, m.cpu()) and float(host[0]) == 7.0 and bool((host[1 + n:] == 7.0).all()) and int(pb[words]) == -1
 
 
 def test_cfg4_full_size_against_reference_golden(cuda_lib):
