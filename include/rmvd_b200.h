@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define RMVD_ABI_VERSION 7
+#define RMVD_ABI_VERSION 8
 #define RMVD_MAX_PEERS 8      /* ranks of one depth-slab communicator (GPUs of one NVSwitch box) */
 
 #define RMVD_OK 0
@@ -236,6 +236,18 @@ int rmvd_psweep_warp_fwd(const float* feat_src, const float* intrinsics_key, con
                          const float* src_to_key, const float* invdepths, const int64_t* inv_stride_host,
                          int N, int C, int h, int w, int hs, int ws, int S, int s_begin, int s_end,
                          int normalize_mode, float* warped, float* mask, int out_S, int out_s0, void* stream);
+
+/*
+ * Backward of rmvd_psweep_warp_fwd with respect to the source feature map (training direction of WarpOnlyCorr; the reference gets it
+ * from autograd through grid_sample and `* warping_mask`, planesweep_corr.py:131-138).  normalize_mode RMVD_NORM_NONE or
+ * RMVD_NORM_DIM (the L2-normalised variants are differentiated by the caller around a RMVD_NORM_NONE call).  Same geometry arguments
+ * as the forward call; grad_warped [N,out_S,C,h,w] (plane s read at out_s0 + s - s_begin), grad_src [N,C,hs,ws] (zeroed by the call,
+ * float atomics).  Sampling positions carry no gradient.
+ */
+int rmvd_psweep_warp_bwd(const float* intrinsics_key, const float* intrinsics_src, const float* src_to_key,
+                         const float* invdepths, const int64_t* inv_stride_host, int N, int C, int h, int w, int hs, int ws,
+                         int S, int s_begin, int s_end, int normalize_mode, const float* grad_warped, int out_S, int out_s0,
+                         float* grad_src, void* stream);
 
 /*
  * The state the reference block keeps after forward(): sampling points of one source view (planesweep_corr.py:489-512) --

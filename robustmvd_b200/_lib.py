@@ -10,7 +10,7 @@ from ctypes import c_char_p, c_float, c_int, c_int64, c_size_t, c_void_p, POINTE
 from . import _build
 
 _lib = None
-ABI_VERSION = 7
+ABI_VERSION = 8
 
 EXPORTS = (
     "rmvd_abi_version", "rmvd_status_string", "rmvd_psweep_workspace_bytes", "rmvd_psweep_corr_fwd",
@@ -22,7 +22,7 @@ EXPORTS = (
     "rmvd_homo_warp_fwd", "rmvd_mvs_regress_fwd", "rmvd_softargmax_partial", "rmvd_softargmax_combine",
     "rmvd_softargmax_confidence", "rmvd_softargmax_slab_fused", "rmvd_soft_argmin_fwd", "rmvd_volume_reduce_fwd", "rmvd_view_fusion_fwd", "rmvd_homography_groupcorr_fwd", "rmvd_homography_warp_fwd", "rmvd_vis_cost_volume_fwd", "rmvd_cvp_proj_cost_fwd", "rmvd_cvp_projections", "rmvd_debug_div_check",
     "rmvd_mask_pack_u8", "rmvd_host_expand_mask", "rmvd_host_expand_mask_async",
-    "rmvd_mask_pack_bits", "rmvd_host_expand_mask_bits", "rmvd_host_expand_mask_bits_async", "rmvd_psweep_corr_fwd_act", "rmvd_mvs_variance_bwd", "rmvd_mvs_regress_bwd",
+    "rmvd_mask_pack_bits", "rmvd_host_expand_mask_bits", "rmvd_host_expand_mask_bits_async", "rmvd_psweep_corr_fwd_act", "rmvd_psweep_warp_bwd", "rmvd_mvs_variance_bwd", "rmvd_mvs_regress_bwd",
 )
 
 
@@ -82,6 +82,7 @@ def _declare(lib):
         [P, P, c_int, c_int, P, c_size_t, P]
     lib.rmvd_mvs_variance_bwd.argtypes = [P, P, P, P] + [c_int] * 6 + [P, P]
     lib.rmvd_mvs_regress_bwd.argtypes = [P, P, P] + [c_int] * 4 + [P, P]
+    lib.rmvd_psweep_warp_bwd.argtypes = [P, P, P, P, PL] + [c_int] * 10 + [P, c_int, c_int, P, P]
     lib.rmvd_mask_pack_u8.argtypes = [P, P, c_size_t, P]
     lib.rmvd_host_expand_mask.argtypes = [P, P, c_size_t, c_int]
     lib.rmvd_host_expand_mask_async.argtypes = [P, P, c_size_t, c_int, P]

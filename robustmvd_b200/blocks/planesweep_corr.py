@@ -204,6 +204,31 @@ class TorchCorr(nn.Module):
 _INVDEPTH_CACHE = {}
 
 
+class _WarpFunction(torch.autograd.Function):
+    """Autograd node of one view of the warp-only block (``warp_only=True``, normalisation off): forward = the block's own
+    ``rmvd_psweep_warp_fwd`` call, backward = ``rmvd_psweep_warp_bwd``; the 0/1 mask output is not differentiable."""
+
+    @staticmethod
+    def forward(ctx, block, args, view, feat_src):
+        corrs, masks, inv = block._forward_impl(feat_key=args["feat_key"], feat_sources=[feat_src], norm_mode=NORM_NONE,
+                                                intrinsics_key=args["intrinsics_key"],
+                                                source_to_key_transforms=[args["source_to_key_transforms"][view]],
+                                                intrinsics_sources=None if args["intrinsics_sources"] is None else [args["intrinsics_sources"][view]],
+                                                **args["sampling"])
+        ctx.block, ctx.args, ctx.view, ctx.inv = block, args, view, inv
+        block._inv_last = inv
+        ctx.src_shape = tuple(feat_src.shape)
+        ctx.mark_non_differentiable(masks[0])
+        return corrs[0], masks[0]
+
+    @staticmethod
+    def backward(ctx, grad_warped, _grad_mask):
+        a, v = ctx.args, ctx.view
+        Ks = a["intrinsics_key"] if a["intrinsics_sources"] is None else a["intrinsics_sources"][v]
+        return (None, None, None, ctx.block._warp_backward_impl(grad_warped, ctx.src_shape, a["feat_key"].shape, a["intrinsics_key"], Ks,
+                                                                a["source_to_key_transforms"][v], ctx.inv, a["sampling"].get("plane_range")))
+
+
 class _CorrFunction(torch.autograd.Function):
     """Autograd node of the correlation (``warp_only=False``): forward = ``rmvd_psweep_corr_fwd``, backward =
     ``rmvd_psweep_corr_bwd``; the 0/1 mask output is not differentiable."""
@@ -421,6 +446,11 @@ class PlanesweepCorrelation(nn.Module):
             return self._forward_impl(feat_key, intrinsics_key, feat_sources, source_to_key_transforms,
                                       intrinsics_sources, num_sampling_points, min_depth, max_depth, sampling_invdepths,
                                       sampling_type, plane_range, debug, out, act=(float(fused_leaky_relu), key_activated_out))
+        if self.warp_only and torch.is_grad_enabled() and any(f.requires_grad for f in feat_sources):
+            return self._forward_warp_only_with_grad(feat_key, intrinsics_key, list(feat_sources), source_to_key_transforms, intrinsics_sources,
+                                                     dict(num_sampling_points=num_sampling_points, min_depth=min_depth, max_depth=max_depth,
+                                                          sampling_invdepths=sampling_invdepths, sampling_type=sampling_type,
+                                                          plane_range=plane_range))
         if not needs_grad:
             return self._forward_impl(feat_key, intrinsics_key, feat_sources, source_to_key_transforms,
                                       intrinsics_sources, num_sampling_points, min_depth, max_depth, sampling_invdepths,
@@ -440,6 +470,56 @@ class PlanesweepCorrelation(nn.Module):
         self.corrs = list(corr.unbind(0))
         self.masks = list(mask.unbind(0))
         return self.corrs, self.masks, self._inv
+
+    def _forward_warp_only_with_grad(self, feat_key, intrinsics_key, feat_sources, source_to_key_transforms, intrinsics_sources, sampling):
+        """``warp_only=True`` for inputs that require grad (WarpOnlyCorr.forward, :107-140): per view one un-normalised kernel call as an
+        autograd node (rmvd_psweep_warp_fwd / rmvd_psweep_warp_bwd); the L2 normalisations run as torch ops around it -- "before" on the
+        source map (:128-129), "after" / True on the warped map (:135-136; the kernel's output is already multiplied by the 0 / 1 mask,
+        which the normalisation maps to itself)."""
+        mode = _warp_norm_mode(self.normalize)
+        args = dict(feat_key=feat_key.detach(), intrinsics_key=intrinsics_key, source_to_key_transforms=list(source_to_key_transforms),
+                    intrinsics_sources=None if intrinsics_sources is None else list(intrinsics_sources), sampling=sampling)
+        corrs, masks, inv, coeffs, points = [], [], None, [], []
+        for v, f in enumerate(feat_sources):
+            if mode == NORM_BEFORE:
+                f = f / (torch.linalg.norm(f, dim=1, keepdim=True) + 1e-9)
+            if f.requires_grad:
+                warped, mask = _WarpFunction.apply(self, args, v, f)
+                inv = self._inv_last
+            else:
+                c, m, inv = self._forward_impl(feat_key=args["feat_key"], feat_sources=[f], norm_mode=NORM_NONE, intrinsics_key=intrinsics_key,
+                                               source_to_key_transforms=[args["source_to_key_transforms"][v]],
+                                               intrinsics_sources=None if args["intrinsics_sources"] is None else [args["intrinsics_sources"][v]],
+                                               **sampling)
+                warped, mask = c[0], m[0]
+            if mode == NORM_AFTER:
+                warped = warped / (torch.linalg.norm(warped, dim=2, keepdim=True) + 1e-9)
+            corrs.append(warped)
+            masks.append(mask)
+            coeffs += self.coeffs
+            points += self.sampling_points
+        self.corrs, self.masks, self.coeffs, self.sampling_points = corrs, masks, coeffs, points
+        return self.corrs, self.masks, inv
+
+    @torch.no_grad()
+    def _warp_backward_impl(self, grad_warped, src_shape, key_shape, intrinsics_key, intrinsics_source, source_to_key_transform, inv, plane_range):
+        dev = grad_warped.device
+        N, C, hs, ws = src_shape
+        h, w = key_shape[2], key_shape[3]
+        inv_c = _f32c(inv)
+        S = inv_c.shape[1]
+        s0, s1 = (0, S) if plane_range is None else plane_range
+        g = _f32c(grad_warped)
+        assert g.shape == (N, s1 - s0, C, h, w)
+        Kk = _calib(intrinsics_key, N, 3, dev, "intrinsics_key")
+        Ks = _calib(intrinsics_source, N, 3, dev, "intrinsics_sources")
+        T = _calib(source_to_key_transform, N, 4, dev, "source_to_key_transforms")
+        grad = torch.empty((N, C, hs, ws), dtype=torch.float32, device=dev)
+        st = _lib.load().rmvd_psweep_warp_bwd(_lib.ptr(Kk), _lib.ptr(Ks), _lib.ptr(T), _lib.ptr(inv_c), _lib.i64_array(_inv_strides(inv_c, N)),
+                                              N, C, h, w, hs, ws, S, s0, s1, NORM_NONE, _lib.ptr(g), s1 - s0, 0, _lib.ptr(grad),
+                                              _lib.stream_ptr())
+        _lib.check(st, "rmvd_psweep_warp_bwd")
+        return grad
 
     @torch.no_grad()
     def _backward_impl(self, grad_corr, feat_key, feat_sources, intrinsics_key, source_to_key_transforms,
@@ -592,8 +672,8 @@ class PlanesweepCorrelation(nn.Module):
                 mask = torch.empty((N, Sl, h, w), dtype=torch.float32, device=dev)
                 st = lib.rmvd_psweep_warp_fwd(
                     _lib.ptr(srcs[v]), _lib.ptr(Kk), _lib.ptr(Ks[v]), _lib.ptr(Ts[v]), _lib.ptr(inv_c), ist, N, C, h,
-                    w, hs[v], ws[v], S, s0, s1, _warp_norm_mode(self.normalize), _lib.ptr(warped), _lib.ptr(mask),
-                    Sl, 0, _lib.stream_ptr())
+                    w, hs[v], ws[v], S, s0, s1, _warp_norm_mode(self.normalize) if norm_mode is None else norm_mode, _lib.ptr(warped),
+                    _lib.ptr(mask), Sl, 0, _lib.stream_ptr())
                 _lib.check(st, "rmvd_psweep_warp_fwd")
                 self.corrs.append(warped)
                 self.masks.append(mask)

@@ -731,6 +731,76 @@ extern "C" int rmvd_psweep_warp_fwd(const float* feat_src, const float* intrinsi
   return (int)cudaGetLastError();
 }
 
+// Backward of psweep_warp_kernel for normalize False / "dim" (training direction of WarpOnlyCorr, planesweep_corr.py:107-140: autograd
+// through grid_sample and `* warping_mask`): thread = (plane, pixel), same locate as the forward; per channel the upstream gradient
+// times the 0 / 1 mask goes to the four corner texels with their bilinear weights (zeros padding: corners outside weigh 0) by float
+// atomics -- adjacent pixels hit adjacent texels.  Sampling positions carry no gradient.
+struct WarpBwdArgs {
+  const float* Kk; const float* Ks; const float* T; const float* invd;
+  long long ist[4];
+  int N, C, h, w, hs, ws, S, s_begin, s_end, out_S, out_s0;
+  const float* grad_warped;   // [N,out_S,C,h,w]
+  float* grad_src;            // [N,C,hs,ws], zero on entry
+};
+
+__global__ void __launch_bounds__(256) psweep_warp_bwd_kernel(const WarpBwdArgs A) {
+  const int P = A.h * A.w;
+  const int Sl = A.s_end - A.s_begin;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int n = blockIdx.y;
+  if (idx >= (long long)Sl * P) return;
+  const int sl = (int)(idx / P), p = (int)(idx - (long long)sl * P);
+  const int s = A.s_begin + sl;
+  const int yi = p / A.w, xi = p - yi * A.w;
+  const Epi E = epi_from_calib(A.Kk + n * 9, A.Ks + n * 9, A.T + n * 16, A.h, A.w, A.hs, A.ws);
+  const EpiPix ep = epi_pixel(E, xi, yi);
+  const float d = A.invd[n * A.ist[0] + s * A.ist[1] + yi * A.ist[2] + xi * A.ist[3]];
+  float us, vs;
+  bool geom;
+  epi_sample(E, ep, d, us, vs, geom);
+  const int hs = A.hs, ws = A.ws;
+  const Bilinear b = bilinear_setup(pix_to_unnorm(us, ws), pix_to_unnorm(vs, hs), hs, ws);
+  if (!sampling_mask(b.msum)) return;                    // warped * warping_mask: no gradient through masked samples
+  const int x0 = sat_index(b.x0f, ws), y0 = sat_index(b.y0f, hs);
+  const int x0c = clampi(x0, 0, ws - 1), x1c = clampi(x0 + 1, 0, ws - 1);
+  const int y0c = clampi(y0, 0, hs - 1), y1c = clampi(y0 + 1, 0, hs - 1);
+  const int o[4] = {y0c * ws + x0c, y0c * ws + x1c, y1c * ws + x0c, y1c * ws + x1c};
+  const float wq[4] = {b.nw, b.ne, b.sw, b.se};
+  const int Ps = hs * ws;
+  const size_t so = (size_t)n * A.out_S + A.out_s0 + sl;
+  const float* g = A.grad_warped + so * A.C * P + p;
+  float* gs = A.grad_src + (size_t)n * A.C * Ps;
+  for (int c = 0; c < A.C; ++c) {
+    const float gv = __ldcs(g + (size_t)c * P);
+    if (gv == 0.f) continue;
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      if (wq[q] != 0.f) atomicAdd(gs + (size_t)c * Ps + o[q], gv * wq[q]);
+  }
+}
+
+extern "C" int rmvd_psweep_warp_bwd(const float* intrinsics_key, const float* intrinsics_src, const float* src_to_key,
+                                    const float* invdepths, const int64_t* inv_stride, int N, int C, int h, int w, int hs, int ws,
+                                    int S, int s_begin, int s_end, int normalize_mode, const float* grad_warped, int out_S, int out_s0,
+                                    float* grad_src, void* stream) {
+  if (!intrinsics_key || !intrinsics_src || !src_to_key || !invdepths || !inv_stride || !grad_warped || !grad_src) return RMVD_E_NULL;
+  if (N <= 0 || C <= 0 || h <= 0 || w <= 0 || S <= 0 || hs <= 0 || ws <= 0 || out_S <= 0 || N > 65535) return RMVD_E_SHAPE;
+  if (s_begin < 0 || s_end > S || s_begin > s_end || out_s0 < 0 || out_s0 + (s_end - s_begin) > out_S) return RMVD_E_RANGE;
+  if (normalize_mode != RMVD_NORM_NONE && normalize_mode != RMVD_NORM_DIM) return RMVD_E_MODE;   // L2-normalised variants: the caller differentiates
+  const cudaError_t e = cudaMemsetAsync(grad_src, 0, (size_t)N * C * hs * ws * sizeof(float), (cudaStream_t)stream);
+  if (e != cudaSuccess) return (int)e;
+  if (s_begin == s_end) return RMVD_OK;
+  WarpBwdArgs A{};
+  A.Kk = intrinsics_key; A.Ks = intrinsics_src; A.T = src_to_key; A.invd = invdepths;
+  for (int k = 0; k < 4; ++k) A.ist[k] = inv_stride[k];
+  A.N = N; A.C = C; A.h = h; A.w = w; A.hs = hs; A.ws = ws; A.S = S; A.s_begin = s_begin; A.s_end = s_end;
+  A.out_S = out_S; A.out_s0 = out_s0; A.grad_warped = grad_warped; A.grad_src = grad_src;
+  const long long tot = (long long)(s_end - s_begin) * h * w;
+  dim3 grid((unsigned)((tot + 255) / 256), N);
+  psweep_warp_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(A);
+  return (int)cudaGetLastError();
+}
+
 extern "C" int rmvd_warp_grid_fwd(const float* x, const float* grid, int K, int C, int hs, int ws, int ho, int wo,
                                   int padding_border, int x_repeat, float* out, float* mask, void* stream) {
   if (!x || !grid || !out || !mask) return RMVD_E_NULL;

@@ -177,3 +177,30 @@ def test_backward_rejects_unsupported_mode(cuda_lib):
     rc = cuda_lib.rmvd_psweep_corr_bwd(one, arr, one, arr, arr, one, st, 1, 8, 4, 4, 1, ints, ints, 4, 0, 4, 2, one, 4, 0,
                                        one, arr, one, 1 << 20, None)
     assert rc == -3   # RMVD_E_MODE: L2-normalised inputs are differentiated around a NORM_NONE call
+
+
+@pytest.mark.parametrize("case", cases.warp_backward_cases(), ids=lambda c: c["name"])
+def test_warp_only_backward_matches_reference_autograd(cuda_lib, case):
+    """Training direction of the warp-only block (WarpOnlyCorr, planesweep_corr.py:107-140): autograd through
+    PlanesweepCorrelation(warp_only=True) -- rmvd_psweep_warp_fwd / rmvd_psweep_warp_bwd, the L2 normalisations as torch ops around
+    them -- against gradients frozen from the UNMODIFIED reference block under CPU autograd (tools/make_warp_bwd_golden.py).
+    Tolerance 1e-4 of max|grad| per tensor; the forward values equal the forward-only call."""
+    import os
+    from robustmvd_b200.blocks.planesweep_corr import PlanesweepCorrelation
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", f"warpbwd_{case['name']}.npz"))
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
+    blk = PlanesweepCorrelation(warp_only=True, normalize=case["normalize"])
+    srcs = [t(f).requires_grad_(True) for f in case["feat_sources"]]
+    kw = dict(feat_key=t(case["feat_key"]), intrinsics_key=t(case["intrinsics_key"]),
+              source_to_key_transforms=[t(x) for x in case["transforms"]], **case["kwargs"])
+    warped, masks, _ = blk(feat_sources=srcs, **kw)
+    assert all(wv.requires_grad for wv in warped) and not any(m.requires_grad for m in masks)
+    ups = [t(u) for u in cases.warp_upstream_grads(case, tuple(warped[0].shape))]
+    grads = torch.autograd.grad(sum((wv * u).sum() for wv, u in zip(warped, ups)), srcs)
+    for v, got in enumerate(grads):
+        ref = g[f"grad_src_{v}"]
+        assert np.abs(got.cpu().numpy() - ref).max() <= 1e-4 * np.abs(ref).max(), v
+    with torch.no_grad():
+        w0, m0, _ = PlanesweepCorrelation(warp_only=True, normalize=case["normalize"])(feat_sources=[s.detach() for s in srcs], **kw)
+    for a, b, ma, mb in zip(warped, w0, masks, m0):
+        assert torch.equal(ma, mb) and float((a.detach() - b).abs().max()) <= 1e-5 * float(b.abs().max())

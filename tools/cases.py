@@ -160,6 +160,23 @@ def mvs_cases(include_large=True):
     return cases
 
 
+def warp_backward_cases():
+    """Warp-only block (WarpOnlyCorr) under autograd: tools/make_warp_bwd_golden.py, tests/test_gpu_planesweep_bwd.py."""
+    out = []
+    for name, normalize, seed, (h, w, C, V, n) in (("plain", False, 71, (10, 14, 6, 2, 2)), ("before", "before", 72, (9, 13, 5, 2, 1)),
+                                                   ("after", "after", 73, (8, 12, 7, 1, 2)), ("dim_c32", "dim", 74, (12, 20, 32, 2, 1))):
+        inp = syn.planesweep_inputs(h, w, C, V, n=n, seed=seed)
+        out.append(dict(name=name, normalize=normalize, feat_key=inp["feat_key"], feat_sources=inp["feat_sources"],
+                        intrinsics_key=inp["intrinsics_key"], transforms=inp["transforms"],
+                        kwargs=dict(num_sampling_points=12, min_depth=0.4, max_depth=1000.0)))
+    return out
+
+
+def warp_upstream_grads(case, shape):
+    rng = np.random.default_rng(5000 + int(np.prod(shape)) % 9973)
+    return [rng.standard_normal(shape, dtype=np.float32) for _ in case["feat_sources"]]
+
+
 def mvs_upstream_grads(case):
     """Upstream gradients of the MVSNet backward cases (tools/make_mvs_bwd_golden.py, tests/test_gpu_mvs.py): for the variance
     volume ``[B,C,D,h,w]`` (a tenth of the entries exactly zero) and the regressed depth ``[B,h,w]``, from the case's shapes."""
